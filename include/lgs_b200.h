@@ -1,0 +1,191 @@
+/*
+ * lgs_b200.h -- C ABI of the B200 lattice Gaussian sampler (liblgs_b200.so).
+ *
+ * The reference (NickQrumpton/lattice-gaussian-mcmc) is pure Python and has no FFI layer: its boundary for this
+ * path is the class surface exported by src/samplers/__init__.py:3-7.  Each entry point below names the
+ * reference method it replaces; INTEGRATION.md shows the ctypes stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative LGS_E_* code; nothing throws across the ABI;
+ *     lgs_last_error() gives the text of the last failure on a handle (or of the last lgs_create()).
+ *   - one handle per CUDA device; calls on one handle are serialised by the caller; handles are independent.
+ *   - `*_dev` pointers are device memory on the handle's device (e.g. a torch tensor's data_ptr());
+ *     `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Calls are asynchronous
+ *     with respect to the host unless the name ends in `_host`.
+ *   - `*_host` entry points take ordinary host buffers and perform the host<->device copies themselves
+ *     (this is what the reference-facing Python classes and bench.py's `e2e` figure go through).
+ *   - matrices are row-major.  The basis has COLUMNS = basis vectors, as the reference samplers use it
+ *     (src/samplers/klein.py:59 `np.linalg.qr(self.lattice.basis)`, :218 `self.lattice.basis @ x`).
+ *   - there is no CPU fallback: without a CUDA device lgs_create() fails with LGS_E_CUDA.
+ */
+#ifndef LGS_B200_H
+#define LGS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define LGS_API __attribute__((visibility("default")))
+#else
+#define LGS_API
+#endif
+
+#define LGS_ABI_VERSION 1
+
+enum {
+    LGS_OK = 0,
+    LGS_E_INVALID = -1, /* bad argument (n <= 0, sigma <= 0, NULL pointer, ...) */
+    LGS_E_CUDA = -2,    /* CUDA runtime error; text in lgs_last_error() */
+    LGS_E_NOMEM = -3,   /* device allocation failed */
+    LGS_E_STATE = -4,   /* call not valid in the current chain state */
+    LGS_E_FALLBACK = -5 /* replay: a draw hit the reference's no-uniform fallback (klein.py:176-179) */
+};
+
+/* 1-D sampler used for each coordinate */
+enum {
+    LGS_SAMPLEZ_TABLE = 0, /* the reference's normalised table + inverse CDF (klein.py:101-179), same arithmetic order */
+    LGS_SAMPLEZ_FAST = 1   /* same distribution, recurrence-built weights walked outward from round(mean) */
+};
+
+/* importance weight used by the IMHK accept step */
+enum {
+    LGS_WEIGHT_REFERENCE = 0, /* imhk.py:102-124 as written: log rho(v) - compute_log_density(v) (a constant +- 1e-14) */
+    LGS_WEIGHT_EXACT = 1      /* Wang-Ling: w(x) = prod_i rho_{sigma_i, m_i(x)}(Z), the table normalisers */
+};
+
+/* which kernels carry the contraction work */
+enum {
+    LGS_PATH_AUTO = 0,
+    LGS_PATH_ORDERED = 1, /* one thread per sample, reference summation order (bit-faithful conditional means) */
+    LGS_PATH_BLOCKED = 2  /* panel-blocked back-substitution + lattice-point contraction on FP64 DMMA */
+};
+
+typedef struct lgs_handle lgs_handle;
+
+/* Host-side description of one sampler.  Replaces the state RefinedKleinSampler.__init__ /
+ * _precompute_qr_stable build (src/samplers/klein.py:26-79): the QR factor is computed on the host by the
+ * caller (numpy/LAPACK, as the reference does) and uploaded once. */
+typedef struct {
+    int32_t n;            /* lattice dimension */
+    const double *R;      /* [n*n] upper-triangular factor, rows sign-fixed to a positive diagonal (klein.py:68-72) */
+    const double *B;      /* [n*n] basis, columns are basis vectors */
+    const double *t;      /* [n]   Q^T center (klein.py:75) */
+    const double *center; /* [n]   center c */
+    double sigma;         /* > 0 (base.py:74) */
+    int32_t precision;    /* window half-width in conditional sigmas (klein.py:26, default 10) */
+    int32_t max_range;    /* window cap, reference constant 1000 (klein.py:122); 0 = 1000 */
+    int32_t device;       /* CUDA device ordinal */
+    int32_t path;         /* LGS_PATH_* */
+} lgs_desc;
+
+LGS_API int lgs_abi_version(void);
+
+/* RefinedKleinSampler.__init__ (klein.py:26-54) / IMHKSampler.__init__ (imhk.py:32-66): upload R, B, t, c. */
+LGS_API int lgs_create(const lgs_desc *desc, lgs_handle **out);
+LGS_API void lgs_destroy(lgs_handle *h);
+LGS_API const char *lgs_last_error(const lgs_handle *h); /* h may be NULL: last lgs_create() failure */
+
+/* number of uniforms one Klein sample consumes in replay mode: coordinates with sigma_i >= 1e-10 (klein.py:201) */
+LGS_API int lgs_uniforms_per_sample(const lgs_handle *h);
+
+/*
+ * KleinSampler.sample(S) (klein.py:324-337 -> sample_single 181-220), native RNG.
+ * Sample s uses Philox4x32-10 with key = seed and counter = (first_sample_id + s, draw pair, 0): the output does
+ * not depend on how [0, S) is split over calls, streams or GPUs.
+ *   V_dev    [S*n] lattice points B x, or NULL
+ *   X_dev    [S*n] integer coefficient vectors x, or NULL
+ *   logq_dev [S]   Klein log-density of each sample as compute_log_density returns it (klein.py:222-271), or NULL
+ */
+LGS_API int lgs_klein_sample(lgs_handle *h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez,
+                     double *V_dev, int64_t *X_dev, double *logq_dev, void *stream);
+
+/*
+ * The same with the reference's recorded uniform stream: sample s consumes
+ * U_dev[s*ups .. (s+1)*ups), ups = lgs_uniforms_per_sample(), in coordinate order i = n-1 .. 0 -- i.e.
+ * np.random.RandomState(seed).random_sample(S*ups) reproduces np.random.seed(seed); sampler.sample(S).
+ * Always uses LGS_SAMPLEZ_TABLE.  fallback_count_dev (int32[1], may be NULL) counts draws that took the
+ * reference's no-uniform fallback.
+ */
+LGS_API int lgs_klein_replay(lgs_handle *h, int64_t S, const double *U_dev, double *V_dev, int64_t *X_dev,
+                     double *logq_dev, int32_t *fallback_count_dev, void *stream);
+
+/* Host-buffer forms (pageable or pinned host memory; copies inside; synchronous). */
+LGS_API int lgs_klein_sample_host(lgs_handle *h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez,
+                          double *V_host, int64_t *X_host, double *logq_host);
+LGS_API int lgs_klein_replay_host(lgs_handle *h, int64_t S, const double *U_host, double *V_host, int64_t *X_host,
+                          double *logq_host, int32_t *fallback_count_host);
+
+/*
+ * RefinedKleinSampler.compute_log_density (klein.py:222-271) for S points given by their integer coefficient
+ * vectors X[S*n] (the reference recovers them from the point with an O(n^3) solve + round, klein.py:230-231; the
+ * host wrapper does the same before calling this).  logq[S].
+ */
+LGS_API int lgs_klein_logdensity(lgs_handle *h, int64_t S, const int64_t *X_dev, double *logq_dev, void *stream);
+LGS_API int lgs_klein_logdensity_host(lgs_handle *h, int64_t S, const int64_t *X_host, double *logq_host);
+
+/*
+ * IMHK chains.  A handle owns one set of `chains` independent Markov chains (IMHKSampler objects,
+ * imhk.py:19-66).  lgs_imhk_reset() discards their state; the next run initialises each chain lazily with one
+ * Klein sample exactly as _initialize_chain does (imhk.py:126-139).
+ * Native RNG: chain k uses Philox key = seed, counter = (first_chain_id + k, draw pair, step index).
+ */
+LGS_API int lgs_imhk_reset(lgs_handle *h, int64_t chains, uint64_t seed, uint64_t first_chain_id);
+
+/*
+ * IMHKSampler.sample(keep, thin) (imhk.py:196-229) preceded by `burn_in` discarded steps
+ * (the README / src/core/base_sampler.py:45-76 form sample(n_samples, burn_in, thin)):
+ * every chain performs burn_in + keep*thin step()s (imhk.py:141-177) and its state is stored after each
+ * thin-th step of the last keep*thin.
+ *   V_dev      [chains*keep*n] kept states as lattice points (chain-major), or NULL
+ *   X_dev      [chains*keep*n] kept states as coefficient vectors, or NULL
+ * Burn-in and thinning happen inside the kernel; only kept states are written.
+ */
+LGS_API int lgs_imhk_run(lgs_handle *h, int64_t burn_in, int64_t keep, int64_t thin, int samplez, int weight_mode,
+                 double *V_dev, int64_t *X_dev, void *stream);
+
+/*
+ * Replay form: chain k consumes U_dev[k*stride ...): [ups for the initial state, only if the chain is not yet
+ * initialised] then per step [ups for the proposal, 1 for the accept test].
+ *   accept_dev [chains*steps] accept bit per step, or NULL;  steps = burn_in + keep*thin
+ *   logw_dev   [chains*(steps+1)] log importance weight of the state at entry and of every proposal, or NULL
+ */
+LGS_API int lgs_imhk_replay(lgs_handle *h, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
+                    const double *U_dev, int64_t stride, double *V_dev, int64_t *X_dev, uint8_t *accept_dev,
+                    double *logw_dev, int32_t *fallback_count_dev, void *stream);
+
+/*
+ * Chain statistics and state (IMHKSampler.accepted_proposals / total_proposals / current_state /
+ * current_coeffs / current_log_weight, imhk.py:54-61).  Device buffers, any may be NULL.
+ *   counts_dev [chains*2] (accepted, total) per chain
+ *   X_dev [chains*n], V_dev [chains*n], logw_dev [chains]
+ */
+LGS_API int lgs_imhk_get_state(lgs_handle *h, int64_t *counts_dev, int64_t *X_dev, double *V_dev, double *logw_dev,
+                       void *stream);
+/* sum over chains of (accepted, total), copied to the host: the two numbers acceptance_rate is made of */
+LGS_API int lgs_imhk_counts_host(lgs_handle *h, int64_t *accepted, int64_t *total);
+
+/* Host-buffer forms of the IMHK entry points (copies inside; synchronous).  Any output may be NULL. */
+LGS_API int lgs_imhk_run_host(lgs_handle *h, int64_t burn_in, int64_t keep, int64_t thin, int samplez, int weight_mode,
+                      double *V_host, int64_t *X_host);
+LGS_API int lgs_imhk_replay_host(lgs_handle *h, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
+                         const double *U_host, int64_t stride, double *V_host, int64_t *X_host, uint8_t *accept_host,
+                         double *logw_host, int32_t *fallback_count_host);
+LGS_API int lgs_imhk_get_state_host(lgs_handle *h, int64_t *counts_host, int64_t *X_host, double *V_host,
+                            double *logw_host);
+
+/*
+ * Marginal histograms for src/diagnostics/convergence_diag.py:15-72 (compute_tvd) on device-resident samples:
+ * for each tracked coordinate d in dims[], counts of floor((V[s, d] - lo) / width) over [0, nbins), values
+ * outside are dropped into the first / last bin.  hist_dev is int64[n_dims*nbins] and is ACCUMULATED into, so
+ * per-rank results can be all-reduced (sum) afterwards.
+ */
+LGS_API int lgs_histogram(lgs_handle *h, const double *V_dev, int64_t S, const int32_t *dims_host, int32_t n_dims,
+                  double lo, double width, int32_t nbins, int64_t *hist_dev, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LGS_B200_H */

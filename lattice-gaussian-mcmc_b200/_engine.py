@@ -1,0 +1,156 @@
+"""One lgs_handle (include/lgs_b200.h) behind a small Python object.
+
+Host forms take/return numpy arrays (what the reference-facing classes use); device forms take raw device pointers
+(`tensor.data_ptr()` of torch CUDA tensors) and a CUDA stream handle, for callers that keep samples resident on the
+GPU (bench.py, the multi-GPU driver).  No sampling happens in Python and nothing here falls back to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import _capi
+from ._capi import PATH, SAMPLEZ, WEIGHT, LgsDesc, c_f64p, check, lib
+
+
+def precompute_qr(basis: np.ndarray, center: np.ndarray):
+    """RefinedKleinSampler._precompute_qr_stable (klein.py:56-79): LAPACK Householder QR of the column basis, rows of
+    R (and columns of Q) flipped so that diag(R) > 0, center carried into the Q frame.  Host-side, once."""
+    Q, R = np.linalg.qr(basis, mode="reduced")
+    n = basis.shape[0]
+    for i in range(n):
+        if R[i, i] < 0:
+            R[i, :] *= -1
+            Q[:, i] *= -1
+    t = Q.T @ center
+    return Q, R, t
+
+
+def _ptr(a, typ=ctypes.c_void_p):
+    return None if a is None else a.ctypes.data_as(typ)
+
+
+class Engine:
+    def __init__(self, R, B, t, center, sigma, precision=10, max_range=1000, device=0, path="auto"):
+        self.n = int(R.shape[0])
+        # keep the uploads alive until lgs_create returns (it copies)
+        R = np.ascontiguousarray(R, dtype=np.float64)
+        B = np.ascontiguousarray(B, dtype=np.float64)
+        t = np.ascontiguousarray(t, dtype=np.float64)
+        center = np.ascontiguousarray(center, dtype=np.float64)
+        desc = LgsDesc(self.n, _ptr(R, c_f64p), _ptr(B, c_f64p), _ptr(t, c_f64p), _ptr(center, c_f64p),
+                       float(sigma), int(precision), int(max_range), int(device), PATH[path])
+        h = ctypes.c_void_p()
+        self._lib = lib()
+        self._h = None
+        check(None, self._lib.lgs_create(ctypes.byref(desc), ctypes.byref(h)))
+        self._h = h
+        self.device = int(device)
+        self.ups = int(self._lib.lgs_uniforms_per_sample(self._h))
+        self.chains = 0
+
+    def close(self):
+        if getattr(self, "_h", None) is not None:
+            self._lib.lgs_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ Klein, host buffers
+    def klein_sample(self, S, seed, first_id, samplez="fast", want_v=True, want_x=False, want_logq=False):
+        S = int(S)
+        V = np.empty((S, self.n), dtype=np.float64) if want_v else None
+        X = np.empty((S, self.n), dtype=np.int64) if want_x else None
+        lq = np.empty(S, dtype=np.float64) if want_logq else None
+        check(self._h, self._lib.lgs_klein_sample_host(self._h, S, int(seed) & (2**64 - 1), int(first_id),
+                                                       SAMPLEZ[samplez], _ptr(V), _ptr(X), _ptr(lq)))
+        return V, X, lq
+
+    def klein_replay(self, U, S, want_v=True, want_x=False, want_logq=False):
+        S = int(S)
+        U = np.ascontiguousarray(U, dtype=np.float64)
+        if U.size < S * self.ups:
+            raise ValueError(f"uniform stream too short: need {S * self.ups}, got {U.size}")
+        V = np.empty((S, self.n), dtype=np.float64) if want_v else None
+        X = np.empty((S, self.n), dtype=np.int64) if want_x else None
+        lq = np.empty(S, dtype=np.float64) if want_logq else None
+        fb = np.zeros(1, dtype=np.int32)
+        check(self._h, self._lib.lgs_klein_replay_host(self._h, S, _ptr(U), _ptr(V), _ptr(X), _ptr(lq), _ptr(fb)))
+        return V, X, lq, int(fb[0])
+
+    def klein_logdensity(self, X):
+        X = np.ascontiguousarray(X, dtype=np.int64).reshape(-1, self.n)
+        out = np.empty(X.shape[0], dtype=np.float64)
+        check(self._h, self._lib.lgs_klein_logdensity_host(self._h, X.shape[0], _ptr(X), _ptr(out)))
+        return out
+
+    # ------------------------------------------------------------------ IMHK, host buffers
+    def imhk_reset(self, chains, seed, first_chain_id=0):
+        check(self._h, self._lib.lgs_imhk_reset(self._h, int(chains), int(seed) & (2**64 - 1), int(first_chain_id)))
+        self.chains = int(chains)
+
+    def imhk_run(self, burn_in, keep, thin, samplez="fast", weight="reference", want_v=True, want_x=False):
+        C = self.chains
+        V = np.empty((C, keep, self.n), dtype=np.float64) if want_v else None
+        X = np.empty((C, keep, self.n), dtype=np.int64) if want_x else None
+        check(self._h, self._lib.lgs_imhk_run_host(self._h, int(burn_in), int(keep), int(thin), SAMPLEZ[samplez],
+                                                   WEIGHT[weight], _ptr(V), _ptr(X)))
+        return V, X
+
+    def imhk_replay(self, U, stride, burn_in, keep, thin, weight="reference", want_v=True, want_x=False):
+        C = self.chains
+        steps = int(burn_in) + int(keep) * int(thin)
+        U = np.ascontiguousarray(U, dtype=np.float64)
+        if U.size < C * stride:
+            raise ValueError("uniform stream too short")
+        V = np.empty((C, keep, self.n), dtype=np.float64) if want_v else None
+        X = np.empty((C, keep, self.n), dtype=np.int64) if want_x else None
+        acc = np.empty((C, steps), dtype=np.uint8)
+        lw = np.empty((C, steps + 1), dtype=np.float64)
+        fb = np.zeros(1, dtype=np.int32)
+        check(self._h, self._lib.lgs_imhk_replay_host(self._h, int(burn_in), int(keep), int(thin), WEIGHT[weight],
+                                                      _ptr(U), int(stride), _ptr(V), _ptr(X), _ptr(acc), _ptr(lw),
+                                                      _ptr(fb)))
+        return {"V": V, "X": X, "accept": acc, "logw": lw, "fallbacks": int(fb[0])}
+
+    def imhk_state(self):
+        C = self.chains
+        counts = np.empty((C, 2), dtype=np.int64)
+        X = np.empty((C, self.n), dtype=np.int64)
+        V = np.empty((C, self.n), dtype=np.float64)
+        lw = np.empty(C, dtype=np.float64)
+        check(self._h, self._lib.lgs_imhk_get_state_host(self._h, _ptr(counts), _ptr(X), _ptr(V), _ptr(lw)))
+        return counts, X, V, lw
+
+    def imhk_counts(self):
+        a, t = ctypes.c_int64(0), ctypes.c_int64(0)
+        check(self._h, self._lib.lgs_imhk_counts_host(self._h, ctypes.byref(a), ctypes.byref(t)))
+        return int(a.value), int(t.value)
+
+    # ------------------------------------------------------------------ device-pointer forms
+    def klein_sample_dev(self, S, seed, first_id, samplez="fast", V=0, X=0, logq=0, stream=0):
+        check(self._h, self._lib.lgs_klein_sample(self._h, int(S), int(seed) & (2**64 - 1), int(first_id),
+                                                  SAMPLEZ[samplez], V or None, X or None, logq or None,
+                                                  stream or None))
+
+    def klein_replay_dev(self, S, U, V=0, X=0, logq=0, fallback=0, stream=0):
+        check(self._h, self._lib.lgs_klein_replay(self._h, int(S), U, V or None, X or None, logq or None,
+                                                  fallback or None, stream or None))
+
+    def imhk_run_dev(self, burn_in, keep, thin, samplez="fast", weight="reference", V=0, X=0, stream=0):
+        check(self._h, self._lib.lgs_imhk_run(self._h, int(burn_in), int(keep), int(thin), SAMPLEZ[samplez],
+                                              WEIGHT[weight], V or None, X or None, stream or None))
+
+    def imhk_state_dev(self, counts=0, X=0, V=0, logw=0, stream=0):
+        check(self._h, self._lib.lgs_imhk_get_state(self._h, counts or None, X or None, V or None, logw or None,
+                                                    stream or None))
+
+    def histogram_dev(self, V, S, dims, lo, width, nbins, hist, stream=0):
+        dims = np.ascontiguousarray(dims, dtype=np.int32)
+        check(self._h, self._lib.lgs_histogram(self._h, V, int(S), dims.ctypes.data_as(_capi.c_i32p), dims.size,
+                                               float(lo), float(width), int(nbins), hist, stream or None))

@@ -1,0 +1,470 @@
+// C ABI of liblgs_b200.so (include/lgs_b200.h): handle management, per-sampler constants, dispatch.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "lgs_internal.h"
+
+using namespace lgs;
+
+namespace {
+
+thread_local std::string g_create_err;
+
+int fail(lgs_handle* h, int code, const std::string& msg) {
+    if (h) h->err = msg; else g_create_err = msg;
+    return code;
+}
+
+int cuda_fail(lgs_handle* h, cudaError_t e, const char* where) {
+    std::string msg = std::string(where) + ": " + cudaGetErrorString(e);
+    int code = (e == cudaErrorMemoryAllocation) ? LGS_E_NOMEM : LGS_E_CUDA;
+    return fail(h, code, msg);
+}
+
+#define LGS_CUDA(h, call)                                        \
+    do {                                                         \
+        cudaError_t e__ = (call);                                \
+        if (e__ != cudaSuccess) return cuda_fail(h, e__, #call); \
+    } while (0)
+
+struct ArenaBuilder {
+    std::vector<uint8_t> bytes;
+    size_t add(const void* src, size_t nbytes) {
+        size_t off = (bytes.size() + 255) & ~size_t(255);
+        bytes.resize(off + nbytes);
+        if (src) memcpy(bytes.data() + off, src, nbytes);
+        return off;
+    }
+};
+
+int ensure_stage(lgs_handle* h, size_t nbytes) {
+    if (h->stage_cap >= nbytes) return LGS_OK;
+    if (h->stage_dev) cudaFree(h->stage_dev);
+    h->stage_dev = nullptr;
+    h->stage_cap = 0;
+    LGS_CUDA(h, cudaMalloc(&h->stage_dev, nbytes));
+    h->stage_cap = nbytes;
+    return LGS_OK;
+}
+
+void free_chains(ChainSet& cs) {
+    cudaFree(cs.Xbuf); cudaFree(cs.Vbuf); cudaFree(cs.logw); cudaFree(cs.cur); cudaFree(cs.init);
+    cudaFree(cs.counts); cudaFree(cs.step_no);
+    cs = ChainSet{};
+}
+
+inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+}  // namespace
+
+extern "C" {
+
+int lgs_abi_version(void) { return LGS_ABI_VERSION; }
+
+const char* lgs_last_error(const lgs_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+
+int lgs_create(const lgs_desc* d, lgs_handle** out) {
+    if (!d || !out) return fail(nullptr, LGS_E_INVALID, "lgs_create: NULL argument");
+    *out = nullptr;
+    if (d->n <= 0) return fail(nullptr, LGS_E_INVALID, "lgs_create: n must be positive");
+    if (!(d->sigma > 0.0)) return fail(nullptr, LGS_E_INVALID, "lgs_create: Standard deviation must be positive");
+    if (!d->R || !d->B || !d->t || !d->center) return fail(nullptr, LGS_E_INVALID, "lgs_create: NULL matrix");
+    int max_range = d->max_range > 0 ? d->max_range : 1000;
+    if (max_range > 2000) return fail(nullptr, LGS_E_INVALID, "lgs_create: max_range > 2000 unsupported");
+    int precision = d->precision > 0 ? d->precision : 10;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, LGS_E_CUDA, std::string("lgs_create: no CUDA device (there is no CPU fallback): ") +
+                                             cudaGetErrorString(e));
+    if (d->device < 0 || d->device >= ndev) return fail(nullptr, LGS_E_INVALID, "lgs_create: bad device ordinal");
+    e = cudaSetDevice(d->device);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaSetDevice");
+
+    const int n = d->n;
+    const double sigma = d->sigma;
+    std::vector<double> rdiag(n), sig(n), lognorm(n), inv2s2(n), q(n), sq(n), znorm(n), eps1(n);
+    std::vector<uint8_t> mode(n);
+    std::vector<int> uidx(n), kind(n), dmax(n);
+    const double log_2pi = std::log(2.0 * M_PI);
+    for (int i = 0; i < n; i++) {
+        double rii = d->R[(size_t)i * n + i];
+        if (rii == 0.0 || !std::isfinite(rii)) return fail(nullptr, LGS_E_INVALID, "lgs_create: singular R");
+        rdiag[i] = rii;
+        double s = sigma / std::fabs(rii);
+        lognorm[i] = 0.5 * log_2pi + std::log(s);  // klein.py:262, unclamped sigma_i
+        mode[i] = s < 1e-10 ? 1 : 0;               // klein.py:201
+        if (s > 1e10) s = std::fmin(s, 1e6);       // klein.py:205-208
+        sig[i] = s;
+        inv2s2[i] = 1.0 / (2.0 * s * s);
+        q[i] = std::exp(-1.0 / (s * s));
+        sq[i] = std::exp(-inv2s2[i]);
+        znorm[i] = s * std::sqrt(2.0 * M_PI);
+        eps1[i] = 2.0 * std::exp(-2.0 * M_PI * M_PI * s * s);
+        double rf = (s < 0.1) ? (double)(precision > 3 ? precision : 3) : (double)precision;
+        double half = rf * s;
+        bool truncated = 2.0 * half >= (double)(max_range - 1);
+        if (truncated) {
+            kind[i] = 2;
+            dmax[i] = max_range / 2;
+        } else {
+            dmax[i] = (int)std::ceil(half) + 1;
+            if (precision < 9 || s < 1.0) kind[i] = 2;
+            else if (s < 1.45) kind[i] = 1;
+            else kind[i] = 0;
+        }
+    }
+    int ups = 0;
+    for (int i = n - 1; i >= 0; i--) {
+        uidx[i] = ups;
+        if (!mode[i]) ups++;
+    }
+
+    ArenaBuilder ab;
+    size_t oR = ab.add(d->R, sizeof(double) * (size_t)n * n);
+    size_t oB = ab.add(d->B, sizeof(double) * (size_t)n * n);
+    size_t ot = ab.add(d->t, sizeof(double) * n);
+    size_t oc = ab.add(d->center, sizeof(double) * n);
+    size_t ord = ab.add(rdiag.data(), sizeof(double) * n);
+    size_t osg = ab.add(sig.data(), sizeof(double) * n);
+    size_t oln = ab.add(lognorm.data(), sizeof(double) * n);
+    size_t omo = ab.add(mode.data(), n);
+    size_t oui = ab.add(uidx.data(), sizeof(int) * n);
+    size_t o1 = ab.add(inv2s2.data(), sizeof(double) * n);
+    size_t o2 = ab.add(q.data(), sizeof(double) * n);
+    size_t o3 = ab.add(sq.data(), sizeof(double) * n);
+    size_t o4 = ab.add(znorm.data(), sizeof(double) * n);
+    size_t o5 = ab.add(eps1.data(), sizeof(double) * n);
+    size_t o6 = ab.add(kind.data(), sizeof(int) * n);
+    size_t o7 = ab.add(dmax.data(), sizeof(int) * n);
+
+    lgs_handle* h = new lgs_handle();
+    h->device = d->device;
+    h->n = n;
+    h->path = d->path;
+    e = cudaMalloc(&h->arena, ab.bytes.size());
+    if (e != cudaSuccess) { delete h; return cuda_fail(nullptr, e, "cudaMalloc(arena)"); }
+    e = cudaMemcpy(h->arena, ab.bytes.data(), ab.bytes.size(), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(h->arena); delete h; return cuda_fail(nullptr, e, "cudaMemcpy(arena)"); }
+    uint8_t* base = (uint8_t*)h->arena;
+    DeviceCtx& c = h->ctx;
+    c.n = n;
+    c.npad = (n + 31) / 32 * 32;
+    c.precision = precision;
+    c.max_range = max_range;
+    c.ups = ups;
+    c.sigma = sigma;
+    c.two_sigma2 = 2.0 * (sigma * sigma);
+    c.inv_2sigma2 = 1.0 / c.two_sigma2;
+    c.R = (const double*)(base + oR);
+    c.B = (const double*)(base + oB);
+    c.t = (const double*)(base + ot);
+    c.center = (const double*)(base + oc);
+    c.rdiag = (const double*)(base + ord);
+    c.sig = (const double*)(base + osg);
+    c.lognorm = (const double*)(base + oln);
+    c.mode = (const uint8_t*)(base + omo);
+    c.uidx = (const int*)(base + oui);
+    c.fz_inv2s2 = (const double*)(base + o1);
+    c.fz_q = (const double*)(base + o2);
+    c.fz_sq = (const double*)(base + o3);
+    c.fz_znorm = (const double*)(base + o4);
+    c.fz_eps1 = (const double*)(base + o5);
+    c.fz_kind = (const int*)(base + o6);
+    c.fz_dmax = (const int*)(base + o7);
+    *out = h;
+    return LGS_OK;
+}
+
+void lgs_destroy(lgs_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    free_chains(h->chains);
+    cudaFree(h->scratch.Xw);
+    cudaFree(h->stage_dev);
+    cudaFree(h->arena);
+    delete h;
+}
+
+int lgs_uniforms_per_sample(const lgs_handle* h) { return h ? h->ctx.ups : LGS_E_INVALID; }
+
+int lgs_klein_sample(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez, double* V_dev,
+                     int64_t* X_dev, double* logq_dev, void* stream) {
+    if (!h) return LGS_E_INVALID;
+    if (S < 0) return fail(h, LGS_E_INVALID, "lgs_klein_sample: S < 0");
+    if (samplez != LGS_SAMPLEZ_TABLE && samplez != LGS_SAMPLEZ_FAST)
+        return fail(h, LGS_E_INVALID, "lgs_klein_sample: unknown samplez");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    RngSpec rng{nullptr, 0, seed, first_sample_id};
+    LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, S, rng, samplez, V_dev, X_dev, logq_dev, nullptr,
+                                     (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+int lgs_klein_replay(lgs_handle* h, int64_t S, const double* U_dev, double* V_dev, int64_t* X_dev, double* logq_dev,
+                     int32_t* fallback_count_dev, void* stream) {
+    if (!h) return LGS_E_INVALID;
+    if (S < 0 || (S > 0 && !U_dev)) return fail(h, LGS_E_INVALID, "lgs_klein_replay: bad arguments");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    if (fallback_count_dev) LGS_CUDA(h, cudaMemsetAsync(fallback_count_dev, 0, sizeof(int32_t), (cudaStream_t)stream));
+    RngSpec rng{U_dev, h->ctx.ups, 0, 0};
+    LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, S, rng, LGS_SAMPLEZ_TABLE, V_dev, X_dev, logq_dev,
+                                     fallback_count_dev, (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uint64_t seed, uint64_t first_id,
+                             int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host) {
+    if (!h) return LGS_E_INVALID;
+    if (S < 0) return fail(h, LGS_E_INVALID, "S < 0");
+    if (S == 0) return LGS_OK;
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    const size_t n = h->n;
+    size_t bV = V_host ? align256(sizeof(double) * S * n) : 0;
+    size_t bX = X_host ? align256(sizeof(int64_t) * S * n) : 0;
+    size_t bq = logq_host ? align256(sizeof(double) * S) : 0;
+    size_t bU = U_host ? align256(sizeof(double) * S * h->ctx.ups) : 0;
+    size_t bf = 256;
+    int rc = ensure_stage(h, bV + bX + bq + bU + bf);
+    if (rc) return rc;
+    uint8_t* p = (uint8_t*)h->stage_dev;
+    double* dV = V_host ? (double*)p : nullptr; p += bV;
+    int64_t* dX = X_host ? (int64_t*)p : nullptr; p += bX;
+    double* dq = logq_host ? (double*)p : nullptr; p += bq;
+    double* dU = U_host ? (double*)p : nullptr; p += bU;
+    int32_t* dfb = (int32_t*)p;
+    if (U_host) {
+        LGS_CUDA(h, cudaMemcpy(dU, U_host, sizeof(double) * S * h->ctx.ups, cudaMemcpyHostToDevice));
+        rc = lgs_klein_replay(h, S, dU, dV, dX, dq, dfb, nullptr);
+    } else {
+        rc = lgs_klein_sample(h, S, seed, first_id, samplez, dV, dX, dq, nullptr);
+    }
+    if (rc) return rc;
+    if (V_host) LGS_CUDA(h, cudaMemcpy(V_host, dV, sizeof(double) * S * n, cudaMemcpyDeviceToHost));
+    if (X_host) LGS_CUDA(h, cudaMemcpy(X_host, dX, sizeof(int64_t) * S * n, cudaMemcpyDeviceToHost));
+    if (logq_host) LGS_CUDA(h, cudaMemcpy(logq_host, dq, sizeof(double) * S, cudaMemcpyDeviceToHost));
+    if (fb_host && U_host) LGS_CUDA(h, cudaMemcpy(fb_host, dfb, sizeof(int32_t), cudaMemcpyDeviceToHost));
+    LGS_CUDA(h, cudaDeviceSynchronize());
+    return LGS_OK;
+}
+
+int lgs_klein_sample_host(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez,
+                          double* V_host, int64_t* X_host, double* logq_host) {
+    return klein_host_common(h, S, nullptr, seed, first_sample_id, samplez, V_host, X_host, logq_host, nullptr);
+}
+
+int lgs_klein_replay_host(lgs_handle* h, int64_t S, const double* U_host, double* V_host, int64_t* X_host,
+                          double* logq_host, int32_t* fallback_count_host) {
+    if (S > 0 && !U_host) return fail(h, LGS_E_INVALID, "lgs_klein_replay_host: NULL uniform stream");
+    return klein_host_common(h, S, U_host, 0, 0, LGS_SAMPLEZ_TABLE, V_host, X_host, logq_host, fallback_count_host);
+}
+
+int lgs_klein_logdensity(lgs_handle* h, int64_t S, const int64_t* X_dev, double* logq_dev, void* stream) {
+    if (!h) return LGS_E_INVALID;
+    if (S < 0 || (S > 0 && (!X_dev || !logq_dev))) return fail(h, LGS_E_INVALID, "lgs_klein_logdensity: bad arguments");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    LGS_CUDA(h, launch_klein_logdensity(h->ctx, S, X_dev, logq_dev, (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+int lgs_klein_logdensity_host(lgs_handle* h, int64_t S, const int64_t* X_host, double* logq_host) {
+    if (!h) return LGS_E_INVALID;
+    if (S < 0 || (S > 0 && (!X_host || !logq_host))) return fail(h, LGS_E_INVALID, "lgs_klein_logdensity_host: bad arguments");
+    if (S == 0) return LGS_OK;
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    size_t bX = align256(sizeof(int64_t) * S * h->n);
+    int rc = ensure_stage(h, bX + sizeof(double) * S);
+    if (rc) return rc;
+    int64_t* dX = (int64_t*)h->stage_dev;
+    double* dq = (double*)((uint8_t*)h->stage_dev + bX);
+    LGS_CUDA(h, cudaMemcpy(dX, X_host, sizeof(int64_t) * S * h->n, cudaMemcpyHostToDevice));
+    rc = lgs_klein_logdensity(h, S, dX, dq, nullptr);
+    if (rc) return rc;
+    LGS_CUDA(h, cudaMemcpy(logq_host, dq, sizeof(double) * S, cudaMemcpyDeviceToHost));
+    return LGS_OK;
+}
+
+int lgs_imhk_reset(lgs_handle* h, int64_t chains, uint64_t seed, uint64_t first_chain_id) {
+    if (!h) return LGS_E_INVALID;
+    if (chains <= 0) return fail(h, LGS_E_INVALID, "lgs_imhk_reset: chains must be positive");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    ChainSet& cs = h->chains;
+    if (cs.chains != chains) {
+        free_chains(cs);
+        size_t buf = sizeof(double) * 2 * (size_t)h->n * chains;
+        LGS_CUDA(h, cudaMalloc(&cs.Xbuf, buf));
+        LGS_CUDA(h, cudaMalloc(&cs.Vbuf, buf));
+        LGS_CUDA(h, cudaMalloc(&cs.logw, sizeof(double) * chains));
+        LGS_CUDA(h, cudaMalloc(&cs.cur, sizeof(int32_t) * chains));
+        LGS_CUDA(h, cudaMalloc(&cs.init, sizeof(int32_t) * chains));
+        LGS_CUDA(h, cudaMalloc(&cs.counts, sizeof(int64_t) * 2 * chains));
+        LGS_CUDA(h, cudaMalloc(&cs.step_no, sizeof(int64_t) * chains));
+        cs.chains = chains;
+    }
+    cs.seed = seed;
+    cs.first_id = first_chain_id;
+    LGS_CUDA(h, cudaMemset(cs.Xbuf, 0, sizeof(double) * 2 * (size_t)h->n * chains));
+    LGS_CUDA(h, cudaMemset(cs.Vbuf, 0, sizeof(double) * 2 * (size_t)h->n * chains));
+    LGS_CUDA(h, cudaMemset(cs.logw, 0, sizeof(double) * chains));
+    LGS_CUDA(h, cudaMemset(cs.cur, 0, sizeof(int32_t) * chains));
+    LGS_CUDA(h, cudaMemset(cs.init, 0, sizeof(int32_t) * chains));
+    LGS_CUDA(h, cudaMemset(cs.counts, 0, sizeof(int64_t) * 2 * chains));
+    LGS_CUDA(h, cudaMemset(cs.step_no, 0, sizeof(int64_t) * chains));
+    return LGS_OK;
+}
+
+static int imhk_check(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin) {
+    if (!h) return LGS_E_INVALID;
+    if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
+    if (burn_in < 0 || keep < 0 || thin < 1) return fail(h, LGS_E_INVALID, "imhk: need burn_in >= 0, keep >= 0, thin >= 1");
+    return LGS_OK;
+}
+
+int lgs_imhk_run(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int samplez, int weight_mode,
+                 double* V_dev, int64_t* X_dev, void* stream) {
+    int rc = imhk_check(h, burn_in, keep, thin);
+    if (rc) return rc;
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    RngSpec rng{nullptr, 0, h->chains.seed, h->chains.first_id};
+    LGS_CUDA(h, launch_imhk_ordered(h->ctx, h->chains, burn_in, keep, thin, rng, samplez, weight_mode, V_dev, X_dev,
+                                    nullptr, nullptr, nullptr, (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+int lgs_imhk_replay(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode, const double* U_dev,
+                    int64_t stride, double* V_dev, int64_t* X_dev, uint8_t* accept_dev, double* logw_dev,
+                    int32_t* fallback_count_dev, void* stream) {
+    int rc = imhk_check(h, burn_in, keep, thin);
+    if (rc) return rc;
+    if (!U_dev) return fail(h, LGS_E_INVALID, "lgs_imhk_replay: NULL uniform stream");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    if (fallback_count_dev) LGS_CUDA(h, cudaMemsetAsync(fallback_count_dev, 0, sizeof(int32_t), (cudaStream_t)stream));
+    RngSpec rng{U_dev, stride, 0, 0};
+    LGS_CUDA(h, launch_imhk_ordered(h->ctx, h->chains, burn_in, keep, thin, rng, LGS_SAMPLEZ_TABLE, weight_mode, V_dev,
+                                    X_dev, accept_dev, logw_dev, fallback_count_dev, (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+int lgs_imhk_get_state(lgs_handle* h, int64_t* counts_dev, int64_t* X_dev, double* V_dev, double* logw_dev,
+                       void* stream) {
+    if (!h) return LGS_E_INVALID;
+    if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    LGS_CUDA(h, launch_imhk_get_state(h->ctx, h->chains, counts_dev, X_dev, V_dev, logw_dev, (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+static int imhk_host_common(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int samplez, int weight_mode,
+                            const double* U_host, int64_t stride, double* V_host, int64_t* X_host,
+                            uint8_t* accept_host, double* logw_host, int32_t* fb_host) {
+    int rc = imhk_check(h, burn_in, keep, thin);
+    if (rc) return rc;
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    const size_t n = h->n;
+    const int64_t C = h->chains.chains;
+    const int64_t steps = burn_in + keep * thin;
+    size_t bV = V_host ? align256(sizeof(double) * C * keep * n) : 0;
+    size_t bX = X_host ? align256(sizeof(int64_t) * C * keep * n) : 0;
+    size_t bA = accept_host ? align256((size_t)C * steps) : 0;
+    size_t bW = logw_host ? align256(sizeof(double) * C * (steps + 1)) : 0;
+    size_t bU = U_host ? align256(sizeof(double) * C * stride) : 0;
+    rc = ensure_stage(h, bV + bX + bA + bW + bU + 256);
+    if (rc) return rc;
+    uint8_t* p = (uint8_t*)h->stage_dev;
+    double* dV = V_host ? (double*)p : nullptr; p += bV;
+    int64_t* dX = X_host ? (int64_t*)p : nullptr; p += bX;
+    uint8_t* dA = accept_host ? p : nullptr; p += bA;
+    double* dW = logw_host ? (double*)p : nullptr; p += bW;
+    double* dU = U_host ? (double*)p : nullptr; p += bU;
+    int32_t* dfb = (int32_t*)p;
+    if (U_host) {
+        LGS_CUDA(h, cudaMemcpy(dU, U_host, sizeof(double) * C * stride, cudaMemcpyHostToDevice));
+        rc = lgs_imhk_replay(h, burn_in, keep, thin, weight_mode, dU, stride, dV, dX, dA, dW, dfb, nullptr);
+    } else {
+        rc = lgs_imhk_run(h, burn_in, keep, thin, samplez, weight_mode, dV, dX, nullptr);
+    }
+    if (rc) return rc;
+    if (V_host && keep) LGS_CUDA(h, cudaMemcpy(V_host, dV, sizeof(double) * C * keep * n, cudaMemcpyDeviceToHost));
+    if (X_host && keep) LGS_CUDA(h, cudaMemcpy(X_host, dX, sizeof(int64_t) * C * keep * n, cudaMemcpyDeviceToHost));
+    if (accept_host && steps) LGS_CUDA(h, cudaMemcpy(accept_host, dA, (size_t)C * steps, cudaMemcpyDeviceToHost));
+    if (logw_host) LGS_CUDA(h, cudaMemcpy(logw_host, dW, sizeof(double) * C * (steps + 1), cudaMemcpyDeviceToHost));
+    if (fb_host && U_host) LGS_CUDA(h, cudaMemcpy(fb_host, dfb, sizeof(int32_t), cudaMemcpyDeviceToHost));
+    LGS_CUDA(h, cudaDeviceSynchronize());
+    return LGS_OK;
+}
+
+int lgs_imhk_run_host(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int samplez, int weight_mode,
+                      double* V_host, int64_t* X_host) {
+    return imhk_host_common(h, burn_in, keep, thin, samplez, weight_mode, nullptr, 0, V_host, X_host, nullptr, nullptr,
+                            nullptr);
+}
+
+int lgs_imhk_replay_host(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
+                         const double* U_host, int64_t stride, double* V_host, int64_t* X_host, uint8_t* accept_host,
+                         double* logw_host, int32_t* fallback_count_host) {
+    if (!U_host) return h ? fail(h, LGS_E_INVALID, "lgs_imhk_replay_host: NULL uniform stream") : LGS_E_INVALID;
+    return imhk_host_common(h, burn_in, keep, thin, LGS_SAMPLEZ_TABLE, weight_mode, U_host, stride, V_host, X_host,
+                            accept_host, logw_host, fallback_count_host);
+}
+
+int lgs_imhk_get_state_host(lgs_handle* h, int64_t* counts_host, int64_t* X_host, double* V_host, double* logw_host) {
+    if (!h) return LGS_E_INVALID;
+    if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    const size_t n = h->n;
+    const int64_t C = h->chains.chains;
+    size_t bc = align256(sizeof(int64_t) * 2 * C), bX = align256(sizeof(int64_t) * C * n);
+    size_t bV = align256(sizeof(double) * C * n), bw = align256(sizeof(double) * C);
+    int rc = ensure_stage(h, bc + bX + bV + bw);
+    if (rc) return rc;
+    uint8_t* p = (uint8_t*)h->stage_dev;
+    int64_t* dc = (int64_t*)p; p += bc;
+    int64_t* dX = (int64_t*)p; p += bX;
+    double* dV = (double*)p; p += bV;
+    double* dw = (double*)p;
+    rc = lgs_imhk_get_state(h, dc, dX, dV, dw, nullptr);
+    if (rc) return rc;
+    if (counts_host) LGS_CUDA(h, cudaMemcpy(counts_host, dc, sizeof(int64_t) * 2 * C, cudaMemcpyDeviceToHost));
+    if (X_host) LGS_CUDA(h, cudaMemcpy(X_host, dX, sizeof(int64_t) * C * n, cudaMemcpyDeviceToHost));
+    if (V_host) LGS_CUDA(h, cudaMemcpy(V_host, dV, sizeof(double) * C * n, cudaMemcpyDeviceToHost));
+    if (logw_host) LGS_CUDA(h, cudaMemcpy(logw_host, dw, sizeof(double) * C, cudaMemcpyDeviceToHost));
+    return LGS_OK;
+}
+
+int lgs_imhk_counts_host(lgs_handle* h, int64_t* accepted, int64_t* total) {
+    if (!h || !accepted || !total) return LGS_E_INVALID;
+    if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    int rc = ensure_stage(h, 256);
+    if (rc) return rc;
+    LGS_CUDA(h, launch_reduce_counts(h->chains, (int64_t*)h->stage_dev, nullptr));
+    int64_t out[2];
+    LGS_CUDA(h, cudaMemcpy(out, h->stage_dev, sizeof(out), cudaMemcpyDeviceToHost));
+    *accepted = out[0];
+    *total = out[1];
+    return LGS_OK;
+}
+
+int lgs_histogram(lgs_handle* h, const double* V_dev, int64_t S, const int32_t* dims_host, int32_t n_dims, double lo,
+                  double width, int32_t nbins, int64_t* hist_dev, void* stream) {
+    if (!h) return LGS_E_INVALID;
+    if (!V_dev || !dims_host || !hist_dev || n_dims <= 0 || nbins <= 0 || !(width > 0.0))
+        return fail(h, LGS_E_INVALID, "lgs_histogram: bad arguments");
+    for (int i = 0; i < n_dims; i++)
+        if (dims_host[i] < 0 || dims_host[i] >= h->n) return fail(h, LGS_E_INVALID, "lgs_histogram: dim out of range");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    int32_t* dims_dev = nullptr;
+    LGS_CUDA(h, cudaMalloc(&dims_dev, sizeof(int32_t) * n_dims));
+    cudaError_t e = cudaMemcpyAsync(dims_dev, dims_host, sizeof(int32_t) * n_dims, cudaMemcpyHostToDevice,
+                                    (cudaStream_t)stream);
+    if (e == cudaSuccess)
+        e = launch_histogram(h->ctx, V_dev, S, dims_dev, n_dims, lo, width, nbins, hist_dev, (cudaStream_t)stream);
+    cudaStreamSynchronize((cudaStream_t)stream);
+    cudaFree(dims_dev);
+    if (e != cudaSuccess) return cuda_fail(h, e, "lgs_histogram");
+    return LGS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,269 @@
+// Device-side building blocks shared by the ordered and the blocked kernels:
+// Philox4x32-10 counter RNG, the reference-order table SampleZ, and the fast SampleZ.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace lgs {
+
+// ---------------------------------------------------------------------------------------------------------
+// Per-sampler constants living in device memory (built once by lgs_create()).
+// ---------------------------------------------------------------------------------------------------------
+struct DeviceCtx {
+    int n;            // lattice dimension
+    int npad;         // n rounded up to the panel width of the blocked path
+    int precision;    // window factor (klein.py:26)
+    int max_range;    // 1000 (klein.py:122)
+    int ups;          // uniforms per sample in replay mode
+    double sigma;
+    double inv_2sigma2;     // 1 / (2 sigma^2)   (base.py:144 divides by 2*sigma**2; kept as a divisor below)
+    double two_sigma2;      // 2 * sigma**2
+    const double* R;        // [n*n] row-major
+    const double* B;        // [n*n] row-major, columns = basis vectors
+    const double* t;        // [n]
+    const double* center;   // [n]
+    const double* rdiag;    // [n] R_ii
+    const double* sig;      // [n] conditional sigma_i = sigma/|R_ii|, clamped as klein.py:205-208
+    const double* lognorm;  // [n] 0.5*log(2*pi) + log(sigma_i)   (klein.py:262), computed on the host in numpy
+    const uint8_t* mode;    // [n] 0 = sample, 1 = round (sigma_i < 1e-10, klein.py:201-204)
+    const int* uidx;        // [n] index of coordinate i's uniform inside one sample's replay stream
+    // fast SampleZ constants per coordinate
+    const double* fz_inv2s2;  // 1/(2 sigma_i^2)
+    const double* fz_q;       // exp(-1/sigma_i^2)
+    const double* fz_sq;      // exp(-1/(2 sigma_i^2))
+    const double* fz_znorm;   // sigma_i*sqrt(2 pi)
+    const double* fz_eps1;    // 2*exp(-2 pi^2 sigma_i^2)   (first theta-series correction)
+    const int* fz_kind;       // 0 analytic Z, 1 analytic Z + one cosine term, 2 summed Z (small sigma_i or truncated window)
+    const int* fz_dmax;       // walk bound on each side of round(mean)
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al. 2011).  key = 64-bit seed, counter = (id_lo, id_hi, c2, c3).
+// ---------------------------------------------------------------------------------------------------------
+struct Philox {
+    uint32_t k0, k1;
+    __device__ __forceinline__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
+
+    __device__ __forceinline__ uint4 operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
+        uint32_t a = k0, b = k1;
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+            uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+            uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
+            c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+            a += 0x9E3779B9u; b += 0xBB67AE85u;
+        }
+        return make_uint4(c0, c1, c2, c3);
+    }
+};
+
+// 53-bit uniform in [0,1) from two 32-bit words, the same bit recipe numpy's random_sample uses
+__device__ __forceinline__ double u53(uint32_t a, uint32_t b) {
+    return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) * (1.0 / 9007199254740992.0);
+}
+
+// Uniform for draw number k (k = 0 for coordinate n-1, ... as the reference consumes them) of unit `id`
+// in stream `tag` (0 = Klein sample / IMHK initial state, s>=1 = proposal of IMHK step s).
+__device__ __forceinline__ double philox_uniform(const Philox& g, uint64_t id, uint32_t k, uint32_t tag) {
+    uint4 w = g((uint32_t)id, (uint32_t)(id >> 32), k >> 1, tag);
+    return (k & 1) ? u53(w.z, w.w) : u53(w.x, w.y);
+}
+constexpr uint32_t kAcceptDraw = 0xFFFFFFFEu;  // draw index of the accept/reject uniform of a step
+
+// ---------------------------------------------------------------------------------------------------------
+// numpy pairwise summation over a generated sequence f(lo) .. f(lo+n-1)  (np.sum order; see the oracle).
+// ---------------------------------------------------------------------------------------------------------
+template <class F>
+__device__ __noinline__ double pw_leaf(const F& f, int lo, int n) {
+    if (n < 8) {
+        double res = 0.0;
+        for (int i = 0; i < n; i++) res = __dadd_rn(res, f(lo + i));
+        return res;
+    }
+    double r0 = f(lo), r1 = f(lo + 1), r2 = f(lo + 2), r3 = f(lo + 3);
+    double r4 = f(lo + 4), r5 = f(lo + 5), r6 = f(lo + 6), r7 = f(lo + 7);
+    int i;
+    for (i = 8; i < n - (n % 8); i += 8) {
+        r0 = __dadd_rn(r0, f(lo + i));     r1 = __dadd_rn(r1, f(lo + i + 1));
+        r2 = __dadd_rn(r2, f(lo + i + 2)); r3 = __dadd_rn(r3, f(lo + i + 3));
+        r4 = __dadd_rn(r4, f(lo + i + 4)); r5 = __dadd_rn(r5, f(lo + i + 5));
+        r6 = __dadd_rn(r6, f(lo + i + 6)); r7 = __dadd_rn(r7, f(lo + i + 7));
+    }
+    double res = __dadd_rn(__dadd_rn(__dadd_rn(r0, r1), __dadd_rn(r2, r3)),
+                           __dadd_rn(__dadd_rn(r4, r5), __dadd_rn(r6, r7)));
+    for (; i < n; i++) res = __dadd_rn(res, f(lo + i));
+    return res;
+}
+
+template <int D, class F>
+__device__ __forceinline__ double pw_sum(const F& f, int lo, int n) {
+    if constexpr (D == 0) {
+        return pw_leaf(f, lo, n);
+    } else {
+        if (n <= 128) return pw_leaf(f, lo, n);
+        int n2 = n / 2;
+        n2 -= n2 % 8;
+        double a = pw_sum<D - 1>(f, lo, n2);
+        double b = pw_sum<D - 1>(f, lo + n2, n - n2);
+        return __dadd_rn(a, b);
+    }
+}
+constexpr int kPwDepth = 4;  // enough for tables of up to 2048 entries (reference cap: 1001)
+
+// ---------------------------------------------------------------------------------------------------------
+// Reference-order table SampleZ  (klein.py:101-179 + numpy choice + scipy logsumexp; mirrors
+// oracle/lgs_oracle.c:table_build/samplez_table but recomputes entries instead of storing them).
+// Returns true when a uniform was consumed.
+// ---------------------------------------------------------------------------------------------------------
+struct TableWindow {
+    long long lower;
+    int len;
+};
+
+__device__ __forceinline__ TableWindow table_window(double mean, double sigma, int precision, int max_range) {
+    double rf = (sigma < 0.1) ? (double)(precision > 3 ? precision : 3) : (double)precision;
+    double w = __dmul_rn(rf, sigma);
+    long long lower = (long long)floor(__dsub_rn(mean, w));
+    long long upper = (long long)ceil(__dadd_rn(mean, w));
+    if (upper - lower > max_range) {
+        long long c = __double2ll_rn(mean);  // round half to even, as np.round
+        lower = c - max_range / 2;
+        upper = c + max_range / 2;
+    }
+    TableWindow tw;
+    tw.lower = lower;
+    tw.len = (int)(upper - lower + 1);
+    return tw;
+}
+
+struct LogpGen {  // unnormalised log-probability of support point lower + k
+    double lower, mean, sigma;
+    __device__ __forceinline__ double operator()(int k) const {
+        double z = __ddiv_rn(__dsub_rn(__dadd_rn(lower, (double)k), mean), sigma);
+        return __dmul_rn(-0.5, __dmul_rn(z, z));
+    }
+};
+struct ShiftExpGen {  // exp(a_k - a_max) with the maxima removed (scipy _logsumexp)
+    LogpGen lp;
+    double a_max;
+    __device__ __forceinline__ double operator()(int k) const {
+        double a = lp(k);
+        return (a == a_max) ? 0.0 : exp(__dsub_rn(a, a_max));
+    }
+};
+struct PlainExpGen {
+    LogpGen lp;
+    __device__ __forceinline__ double operator()(int k) const { return exp(lp(k)); }
+};
+struct ProbGen {  // exp(logp_k - lse)
+    LogpGen lp;
+    double lse;
+    __device__ __forceinline__ double operator()(int k) const { return exp(__dsub_rn(lp(k), lse)); }
+};
+
+// log-sum-exp of the window, scipy order.  Also usable on its own for the exact importance weight.
+__device__ __forceinline__ double table_lse(const LogpGen& lp, int len) {
+    double a_max = -INFINITY;
+    for (int k = 0; k < len; k++) a_max = fmax(a_max, lp(k));
+    double m = 0.0;
+    for (int k = 0; k < len; k++) m += (lp(k) == a_max) ? 1.0 : 0.0;
+    ShiftExpGen se{lp, a_max};
+    double s = pw_sum<kPwDepth>(se, 0, len);
+    if (s != 0.0) s = __ddiv_rn(s, m);
+    double lse = __dadd_rn(__dadd_rn(log1p(s), log(m)), a_max);
+    if (!isfinite(lse)) {
+        PlainExpGen pe{lp};
+        lse = log(pw_sum<kPwDepth>(pe, 0, len));
+    }
+    return lse;
+}
+
+__device__ __forceinline__ bool samplez_table(double mean, double sigma, int precision, int max_range, double u,
+                                              long long* out) {
+    TableWindow tw = table_window(mean, sigma, precision, max_range);
+    LogpGen lp{(double)tw.lower, mean, sigma};
+    double lse = table_lse(lp, tw.len);
+    ProbGen pg{lp, lse};
+    double tot = pw_sum<kPwDepth>(pg, 0, tw.len);
+    // cdf = cumsum(p / tot); cdf /= cdf[-1]
+    double run = 0.0;
+    bool bad = false;
+    for (int k = 0; k < tw.len; k++) {
+        double p = __ddiv_rn(pg(k), tot);
+        bad |= !(p >= 0.0);
+        run = (k == 0) ? p : __dadd_rn(run, p);
+    }
+    if (bad) {
+        *out = __double2ll_rn(mean);
+        return false;
+    }
+    double last = run;
+    // searchsorted(cdf, u, side='right') == number of entries <= u (cdf is non-decreasing)
+    int idx = 0;
+    run = 0.0;
+    for (int k = 0; k < tw.len; k++) {
+        double p = __ddiv_rn(pg(k), tot);
+        run = (k == 0) ? p : __dadd_rn(run, p);
+        if (__ddiv_rn(run, last) <= u) idx = k + 1; else break;
+    }
+    if (idx >= tw.len) idx = tw.len - 1;
+    *out = tw.lower + idx;
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Fast SampleZ: same distribution D_{Z, sigma_i, mean} restricted to the reference window, inverse transform
+// over the ordering c0, c0+1, c0-1, c0+2, ... (c0 = round(mean)), weights by the two-term recurrence
+//   rho(c0+d+1)/rho(c0+d) = r_d,  r_{d+1} = r_d * exp(-1/sigma_i^2),
+// normaliser from the theta-series identity  sum_k rho(k) = sigma sqrt(2 pi) (1 + 2 e^{-2 pi^2 sigma^2} cos(2 pi m) + ...)
+// when sigma_i is large enough for the omitted terms to be < 1e-17, otherwise summed.
+// Returns the draw and, through *zsum, the window mass sum_k rho_{sigma_i,mean}(k) (used by LGS_WEIGHT_EXACT).
+// ---------------------------------------------------------------------------------------------------------
+struct FastZ {
+    double inv2s2, q, sq, znorm, eps1;
+    int kind, dmax;
+};
+
+__device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, double u, double* zsum) {
+    double c0 = rint(mean);
+    double delta = c0 - mean;                     // in [-0.5, 0.5]
+    double w0 = exp(-delta * delta * c.inv2s2);   // rho(c0)
+    double e1 = exp(-2.0 * delta * c.inv2s2);     // rho(c0+1)/rho(c0) = e1 * sq ; rho(c0-1)/rho(c0) = sq / e1
+    double ru = e1 * c.sq;
+    double rd = c.sq / e1;
+    double Z;
+    if (c.kind == 0) {
+        Z = c.znorm;
+    } else if (c.kind == 1) {
+        Z = c.znorm * (1.0 + c.eps1 * (double)cospif(2.0f * (float)delta));
+    } else {
+        // summed normaliser over the (possibly truncated) window
+        double su = w0, wu = w0, wd = w0, a = ru, b = rd;
+        for (int d = 1; d <= c.dmax; d++) {
+            wu *= a; a *= c.q;
+            wd *= b; b *= c.q;
+            su += wu + wd;
+        }
+        Z = su;
+    }
+    *zsum = Z;
+    double target = u * Z;
+    double cum = w0;
+    long long x = (long long)c0;
+    if (target < cum) return x;
+    double wu = w0, wd = w0;
+    int d = 1;
+    for (; d <= c.dmax; d++) {
+        wu *= ru; ru *= c.q;
+        cum += wu;
+        if (target < cum) return x + d;
+        wd *= rd; rd *= c.q;
+        cum += wd;
+        if (target < cum) return x - d;
+    }
+    // u*Z beyond the accumulated mass (rounding, ~1e-16): the last point visited
+    return x - c.dmax;
+}
+
+}  // namespace lgs

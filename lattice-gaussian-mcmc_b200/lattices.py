@@ -1,0 +1,115 @@
+"""Host-side lattice objects (numpy only).
+
+The reference's lattice classes need SageMath and three of them are not valid UTF-8, so they
+cannot be imported; what the samplers actually consume is a four-attribute duck type:
+`basis` (columns are basis vectors as klein.py:59,218 use it), `dimension`, `min_gram_schmidt_norm`,
+`smoothing_parameter()`, plus `name` for __repr__.  `SimpleLattice` supplies exactly that, following the formulas of
+the reference's src/lattices/simple.py:39-82 (row Gram-Schmidt) and src/lattices/base.py (smoothing bound).
+The constructors below restate the reference's *formulas* for the shapes BASELINE.json names:
+
+  identity_lattice(n)            src/lattices/identity.py:33-52      B = I_n
+  qary_lattice(A, q)             src/lattices/qary.py:131-164        [[q I, A], [0, I]]  (columns generate {x: x1 = A x2 mod q})
+  dd_lattice(n, seed)            SURVEY.md appendix A.5              randint(-3,4) + 2n I   (the dimension-sweep family)
+  random_int_lattice(n, seed)    klein_scaling_analysis.py:83-86     randint(0,51), seed 0+n  (input of the LLL runs)
+  ntru_lattice(...)              src/lattices/ntru.py:482-537        [[rot(g), -rot(f)], [rot(G), -rot(F)]], see ntru.py here
+
+Everything here is host setup that runs once per sampler; nothing in this file is on the sampling path.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def row_gram_schmidt_norms(basis: np.ndarray) -> np.ndarray:
+    """||b*_i|| of the ROWS of `basis` (the reference's SimpleLattice convention, simple.py:39-58), via QR."""
+    b = np.asarray(basis, dtype=np.float64)
+    r = np.linalg.qr(b.T, mode="r")
+    return np.abs(np.diag(r))
+
+
+def column_gram_schmidt_norms(basis: np.ndarray) -> np.ndarray:
+    """||b*_i|| of the COLUMNS of `basis`: |R_ii| of the factor the samplers use (klein.py:59)."""
+    r = np.linalg.qr(np.asarray(basis, dtype=np.float64), mode="r")
+    return np.abs(np.diag(r))
+
+
+class SimpleLattice:
+    """The lattice duck type the samplers read (src/lattices/simple.py:17-82, src/lattices/base.py:16-120)."""
+
+    def __init__(self, basis, name: str = "SimpleLattice"):
+        b = np.array(basis, dtype=np.float64)
+        if b.ndim != 2 or b.shape[0] != b.shape[1]:
+            raise ValueError("basis must be a square matrix")
+        self._basis = np.ascontiguousarray(b)
+        self.dimension = b.shape[0]
+        self.name = name
+        self._gs_norms = row_gram_schmidt_norms(self._basis)
+
+    @property
+    def basis(self) -> np.ndarray:
+        return self._basis
+
+    def get_basis(self) -> np.ndarray:
+        return self._basis
+
+    def get_dimension(self) -> int:
+        return self.dimension
+
+    @property
+    def min_gram_schmidt_norm(self) -> float:
+        return float(np.min(self._gs_norms))
+
+    @property
+    def max_gram_schmidt_norm(self) -> float:
+        return float(np.max(self._gs_norms))
+
+    def get_gram_schmidt_norms(self):
+        return [float(x) for x in self._gs_norms]
+
+    def smoothing_parameter(self, epsilon: float = 0.01) -> float:
+        """eta_eps(L) <= max||b*_i|| sqrt(ln(2n(1+1/eps))/pi)  (the bound lattices/base.py uses)."""
+        n = self.dimension
+        return float(np.max(self._gs_norms) * np.sqrt(np.log(2 * n * (1 + 1 / epsilon)) / np.pi))
+
+    def __repr__(self):
+        return f"{self.name}(n={self.dimension})"
+
+
+def identity_lattice(n: int) -> SimpleLattice:
+    return SimpleLattice(np.eye(n), name=f"IdentityLattice(Z^{n})")
+
+
+def dd_basis(n: int, seed: int) -> np.ndarray:
+    rng = np.random.RandomState(seed)
+    return (rng.randint(-3, 4, size=(n, n)) + 2 * n * np.eye(n)).astype(np.float64)
+
+
+def dd_lattice(n: int, seed: int | None = None) -> SimpleLattice:
+    return SimpleLattice(dd_basis(n, n if seed is None else seed), name=f"DiagDominant(n={n})")
+
+
+def random_int_basis(n: int, seed: int | None = None) -> np.ndarray:
+    """The unreduced input of the reference's scaling runs (klein_scaling_analysis.py:83-86)."""
+    np_rng = np.random.RandomState(0 + n if seed is None else seed)
+    return np_rng.randint(0, 51, size=(n, n)).astype(np.float64)
+
+
+def qary_basis(A: np.ndarray, q: int) -> np.ndarray:
+    """[[q I_k, A], [0, I_m]] with A of shape (k, m): columns generate {(x1, x2): x1 = A x2 (mod q)}."""
+    A = np.asarray(A, dtype=np.float64)
+    k, m = A.shape
+    top = np.hstack([q * np.eye(k), A])
+    bot = np.hstack([np.zeros((m, k)), np.eye(m)])
+    return np.vstack([top, bot])
+
+
+def qary_lattice(n: int = 256, m: int = 512, q: int = 3329, seed: int = 0) -> SimpleLattice:
+    """BASELINE config C3: q-ary LWE lattice, n = 256 secret dims, m = 512 total dims, q = 3329."""
+    A = np.random.RandomState(seed).randint(0, q, size=(m - n, n))
+    return SimpleLattice(qary_basis(A, q), name=f"QaryLattice(n={n}, m={m}, q={q})")
+
+
+def lattice_from_rows(rows: np.ndarray, name: str = "SimpleLattice") -> SimpleLattice:
+    """Wrap a row-basis the way the reference's scripts do: the matrix is handed to the sampler unchanged
+    (klein_scaling_analysis.py:175), i.e. the sampler then treats its columns as the basis."""
+    return SimpleLattice(rows, name=name)
