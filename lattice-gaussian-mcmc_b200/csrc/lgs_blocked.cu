@@ -1,0 +1,440 @@
+// Blocked path: the throughput implementation of Klein's sampler (klein.py:181-220) for a batch of samples.
+//
+// Coordinates are cut into blocks of kPB = 32.  For each block, from the last coordinate to the first:
+//   1. contraction  C[rows of the block, s] = t - R[rows, done] * X[done, s]   (all samples s at once)
+//      -- a dense fp64 GEMM on the DMMA pipe (mma.sync m16n8k8 f64), operands staged with cp.async;
+//   2. panel kernel: one thread per sample walks the 32 coordinates of the block serially (the in-block triangle of
+//      R sits in the constant bank as kernel parameters), drawing x_i ~ D_{Z, sigma_i, c_i} with the fast SampleZ and
+//      Philox, and accumulates the Klein log-density terms.
+// Two 32-blocks share one 64-row contraction over the already finished coordinates (halves the re-reads of X);
+// the second block of a pair gets the first block's contribution from a small 32x32 contraction.
+// Finally the lattice points V = X B^T are one more dense GEMM whose epilogue writes the reference's row-major
+// [S, n] layout (klein.py:218,322).
+//
+// Data layout (HBM): X is coordinate-major, X[i * ld + s], one fp64 per (coordinate, sample); rows of the block being
+// processed hold the running centers C until the panel kernel overwrites them with the integers it draws.
+#include "lgs_internal.h"
+
+#include <cmath>
+#include <vector>
+
+namespace lgs {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------
+// panel kernel
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kPanelThreads = 128;
+
+__device__ __noinline__ double samplez_fast_call(double mean, double inv2s2, double q, double sq, double znorm,
+                                                 double eps1, int kind, int dmax, double u, double* zsum) {
+    FastZ fz{inv2s2, q, sq, znorm, eps1, kind, dmax};
+    return (double)samplez_fast(mean, fz, u, zsum);
+}
+
+template <bool WANT_LZ>
+__global__ void __launch_bounds__(kPanelThreads)
+klein_panel_kernel(const __grid_constant__ PanelParams P, double* __restrict__ X, int64_t ld, int i0, int64_t S,
+                   uint64_t seed, uint64_t first_id, uint32_t tag, const int64_t* __restrict__ tag_dev, int first,
+                   double* __restrict__ lp, double* __restrict__ d2, double* __restrict__ lz) {
+    const int64_t s = (int64_t)blockIdx.x * kPanelThreads + threadIdx.x;
+    if (s >= S) return;
+    double c[kPB];
+#pragma unroll
+    for (int k = 0; k < kPB; k++) c[k] = X[(size_t)(i0 + k) * ld + s];
+    double lpa = 0.0, d2a = 0.0, lza = 0.0;
+    if (!first) {
+        lpa = lp[s];
+        d2a = d2[s];
+        if (WANT_LZ) lza = lz[s];
+    }
+    if (tag_dev) tag = (uint32_t)(*tag_dev);
+    const Philox gen(seed);
+    const uint64_t id = first_id + (uint64_t)s;
+    uint4 w = make_uint4(0, 0, 0, 0);
+    int wpair = -1;
+#pragma unroll
+    for (int i = kPB - 1; i >= 0; i--) {
+        const double mean = c[i] * P.inv_r[i];
+        double x;
+        if (P.mode[i]) {
+            x = rint(mean);
+        } else {
+            const int k = P.uidx[i];
+            if ((k >> 1) != wpair) {
+                wpair = k >> 1;
+                w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, tag);
+            }
+            const double u = (k & 1) ? u53(w.z, w.w) : u53(w.x, w.y);
+            double zs;
+            x = samplez_fast_call(mean, P.inv2s2[i], P.q[i], P.sq[i], P.znorm[i], P.eps1[i], P.kind[i], P.dmax[i], u,
+                                  &zs);
+            if (WANT_LZ) lza += log(zs);
+        }
+        X[(size_t)(i0 + i) * ld + s] = x;
+        const double dl = x - mean;
+        const double dl2 = dl * dl;
+        lpa = fma(dl2, P.inv2s2[i], lpa);
+        d2a = fma(dl2, P.r2[i], d2a);
+#pragma unroll
+        for (int k = 0; k < i; k++) c[k] = fma(P.nrt[i * kPB + k], x, c[k]);
+    }
+    lp[s] = lpa;
+    d2[s] = d2a;
+    if (WANT_LZ) lz[s] = lza;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// DMMA contraction kernel:   D[m, s] = sum_{k in [k0, k1)} A[r0 + m, k] * X[k, s]
+//   MODE_PANEL : X[r0 + m, s]  = tvec[r0 + m] - D      (start the centers of a block)
+//   MODE_ACCUM : X[r0 + m, s] -= D                      (add a finished block's contribution)
+//   MODE_POINT : V[s * ldv + r0 + m] = D                (lattice points, row-major per sample)
+// CTA tile BM x 128 samples, warps 32 x 32, k-tile 16, kStages-deep cp.async pipeline.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int MODE_PANEL = 0, MODE_ACCUM = 1, MODE_POINT = 2;
+constexpr int kBN = 128, kBK = 16, kStages = 4;
+constexpr int kLdA = kBK + 4;   // 20 doubles: conflict-free LDS.64 for the A fragments (row stride = 4 mod 16)
+constexpr int kLdB = kBN + 4;   // 132 doubles: same for the B fragments
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+__device__ __forceinline__ void dmma_16x8x8(double (&d)[4], const double (&a)[4], const double (&b)[2]) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+        : "+d"(d[0]), "+d"(d[1]), "+d"(d[2]), "+d"(d[3])
+        : "d"(a[0]), "d"(a[1]), "d"(a[2]), "d"(a[3]), "d"(b[0]), "d"(b[1]));
+}
+
+template <int BM>
+struct GemmSmem {
+    double A[kStages][BM][kLdA];
+    double B[kStages][kBK][kLdB];
+};
+
+template <int BM, int MODE>
+__global__ void __launch_bounds__(BM * 4)
+contract_kernel(const double* __restrict__ A, int64_t lda, double* __restrict__ X, int64_t ldx, int r0_base, int k0,
+                int k1, const double* __restrict__ tvec, int64_t S, double* __restrict__ V, int64_t ldv, int n_valid) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    GemmSmem<BM>& sm = *reinterpret_cast<GemmSmem<BM>*>(smem_raw);
+    constexpr int NT = BM * 4;
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int wm = warp >> 2, wn = warp & 3;
+    const int g = lane >> 2, t = lane & 3;
+    const int r0 = r0_base + blockIdx.x * BM;            // blockIdx.x: row tile (fastest, shares the X tile in L2)
+    const int64_t s0 = (int64_t)blockIdx.y * kBN;         // blockIdx.y: sample tile
+    const int nk = (k1 - k0) / kBK;
+
+    double acc[2][4][4];
+#pragma unroll
+    for (int a = 0; a < 2; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) acc[a][b][c] = 0.0;
+
+    auto load_tile = [&](int kt, int stage) {
+        const int kb = k0 + kt * kBK;
+        // A tile: BM rows x 8 chunks of 16 bytes
+#pragma unroll
+        for (int c = tid; c < BM * 8; c += NT) {
+            int row = c >> 3, ch = c & 7;
+            cp_async16(&sm.A[stage][row][ch * 2], A + (size_t)(r0 + row) * lda + kb + ch * 2);
+        }
+        // B tile: 16 rows x 64 chunks
+#pragma unroll
+        for (int c = tid; c < kBK * 64; c += NT) {
+            int row = c >> 6, ch = c & 63;
+            cp_async16(&sm.B[stage][row][ch * 2], X + (size_t)(kb + row) * ldx + s0 + ch * 2);
+        }
+    };
+
+#pragma unroll
+    for (int st = 0; st < kStages - 1; st++) {
+        if (st < nk) load_tile(st, st);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nk; kt++) {
+        cp_async_wait<kStages - 2>();
+        __syncthreads();
+        {
+            int nx = kt + kStages - 1;
+            if (nx < nk) load_tile(nx, nx % kStages);
+            cp_async_commit();
+        }
+        const int stage = kt % kStages;
+#pragma unroll
+        for (int kk = 0; kk < kBK; kk += 8) {
+            double af[2][4], bf[4][2];
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+                const double* ap = &sm.A[stage][wm * 32 + mt * 16 + g][kk + t];
+                af[mt][0] = ap[0];
+                af[mt][1] = ap[8 * kLdA];
+                af[mt][2] = ap[4];
+                af[mt][3] = ap[8 * kLdA + 4];
+            }
+#pragma unroll
+            for (int nt = 0; nt < 4; nt++) {
+                const double* bp = &sm.B[stage][kk + t][wn * 32 + nt * 8 + g];
+                bf[nt][0] = bp[0];
+                bf[nt][1] = bp[4 * kLdB];
+            }
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                for (int nt = 0; nt < 4; nt++) dmma_16x8x8(acc[mt][nt], af[mt], bf[nt]);
+        }
+    }
+    cp_async_wait<0>();
+
+    // epilogue: fragment (mt, nt): rows g / g+8 of the 16-row tile, columns 2t, 2t+1 of the 8-column tile
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int row = r0 + wm * 32 + mt * 16 + g + h * 8;
+#pragma unroll
+            for (int nt = 0; nt < 4; nt++) {
+                const int64_t col = s0 + wn * 32 + nt * 8 + t * 2;
+                const double v0 = acc[mt][nt][h * 2], v1 = acc[mt][nt][h * 2 + 1];
+                if (MODE == MODE_POINT) {
+                    if (row < n_valid) {
+                        if (col < S) V[(size_t)col * ldv + row] = v0;
+                        if (col + 1 < S) V[(size_t)(col + 1) * ldv + row] = v1;
+                    }
+                } else {
+                    double2* dst = reinterpret_cast<double2*>(X + (size_t)row * ldx + col);
+                    double2 o;
+                    if (MODE == MODE_PANEL) {
+                        const double tv = tvec[row];
+                        o.x = tv - v0;
+                        o.y = tv - v1;
+                    } else {
+                        o = *dst;
+                        o.x -= v0;
+                        o.y -= v1;
+                    }
+                    *dst = o;
+                }
+            }
+        }
+    }
+}
+
+// X (coordinate-major doubles) -> int64 [S, n] row-major, through a 32x32 shared-memory transpose
+__global__ void __launch_bounds__(256)
+export_coeffs_kernel(const double* __restrict__ X, int64_t ld, int n, int64_t S, int64_t* __restrict__ out) {
+    __shared__ double tile[32][33];
+    const int64_t s0 = (int64_t)blockIdx.x * 32;
+    const int i0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) {
+        int i = i0 + r;
+        int64_t s = s0 + tx;
+        tile[r][tx] = (i < n && s < S) ? X[(size_t)i * ld + s] : 0.0;
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        int64_t s = s0 + r;
+        int i = i0 + tx;
+        if (s < S && i < n) out[(size_t)s * n + i] = (int64_t)tile[tx][r];
+    }
+}
+
+__global__ void finish_logq_kernel(const double* __restrict__ lp, double sum_lognorm, int64_t S,
+                                   double* __restrict__ logq) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < S) logq[s] = -lp[s] - sum_lognorm;
+}
+
+template <int BM, int MODE>
+cudaError_t launch_contract(const double* A, int64_t lda, double* X, int64_t ldx, int r0, int rows, int k0, int k1,
+                            const double* tvec, int64_t S, double* V, int64_t ldv, int n_valid, cudaStream_t st) {
+    static bool configured = false;
+    const size_t smem = sizeof(GemmSmem<BM>);
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(contract_kernel<BM, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    dim3 grid((unsigned)(rows / BM), (unsigned)((S + kBN - 1) / kBN));
+    contract_kernel<BM, MODE><<<grid, BM * 4, smem, st>>>(A, lda, X, ldx, r0, k0, k1, tvec, S, V, ldv, n_valid);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------
+void blocked_free(BlockedCtx& bc) {
+    cudaFree(bc.Rp);
+    cudaFree(bc.Bp);
+    cudaFree(bc.tp);
+    for (auto& w : bc.work) {
+        cudaFree(w.X);
+        cudaFree(w.lp);
+        cudaFree(w.d2);
+        cudaFree(w.lz);
+        w = BlockedWork{};
+    }
+    bc.Rp = bc.Bp = bc.tp = nullptr;
+    bc.ready = false;
+}
+
+cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) {
+    const int n = d.n;
+    const int npad = (n + kPB - 1) / kPB * kPB;
+    const int mpad = (n + 63) / 64 * 64;
+    bc.n = n;
+    bc.npad = npad;
+    bc.mpad = mpad;
+    bc.two_sigma2 = 2.0 * d.sigma * d.sigma;
+    std::vector<double> Rp((size_t)npad * npad, 0.0), Bp((size_t)mpad * npad, 0.0), tp(npad, 0.0);
+    for (int i = 0; i < n; i++) {
+        for (int j = i; j < n; j++) Rp[(size_t)i * npad + j] = d.R[(size_t)i * n + j];
+        for (int j = 0; j < n; j++) Bp[(size_t)i * npad + j] = d.B[(size_t)i * n + j];
+        tp[i] = d.t[i];
+    }
+    for (int i = n; i < npad; i++) Rp[(size_t)i * npad + i] = 1.0;
+    bc.sum_lognorm = 0.0;
+    for (int i = 0; i < n; i++) bc.sum_lognorm += hc.lognorm[i];
+
+    bc.panels.assign(npad / kPB, PanelParams{});
+    for (int b = 0; b < npad / kPB; b++) {
+        PanelParams& P = bc.panels[b];
+        const int i0 = b * kPB;
+        for (int i = 0; i < kPB; i++) {
+            const int gi = i0 + i;
+            if (gi < n) {
+                for (int k = 0; k < i; k++) P.nrt[i * kPB + k] = -d.R[(size_t)(i0 + k) * n + gi];
+                P.inv_r[i] = 1.0 / hc.rdiag[gi];
+                P.r2[i] = hc.rdiag[gi] * hc.rdiag[gi];
+                P.inv2s2[i] = hc.inv2s2[gi];
+                P.q[i] = hc.q[gi];
+                P.sq[i] = hc.sq[gi];
+                P.znorm[i] = hc.znorm[gi];
+                P.eps1[i] = hc.eps1[gi];
+                P.kind[i] = hc.kind[gi];
+                P.dmax[i] = hc.dmax[gi];
+                P.uidx[i] = hc.uidx[gi];
+                P.mode[i] = hc.mode[gi];
+            } else {  // padding coordinate: center 0, R_ii = 1, rounded => x = 0, contributes nothing
+                P.inv_r[i] = 1.0;
+                P.mode[i] = 1;
+            }
+        }
+    }
+    cudaError_t e;
+    if ((e = cudaMalloc(&bc.Rp, sizeof(double) * Rp.size())) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&bc.Bp, sizeof(double) * Bp.size())) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&bc.tp, sizeof(double) * tp.size())) != cudaSuccess) return e;
+    if ((e = cudaMemcpy(bc.Rp, Rp.data(), sizeof(double) * Rp.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+    if ((e = cudaMemcpy(bc.Bp, Bp.data(), sizeof(double) * Bp.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+    if ((e = cudaMemcpy(bc.tp, tp.data(), sizeof(double) * tp.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+#define LGS_SMEM_ATTR(BM, MODE)                                                                                  \
+    if ((e = cudaFuncSetAttribute(contract_kernel<BM, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+                                  (int)sizeof(GemmSmem<BM>))) != cudaSuccess)                                   \
+        return e;
+    LGS_SMEM_ATTR(64, MODE_PANEL)
+    LGS_SMEM_ATTR(32, MODE_PANEL)
+    LGS_SMEM_ATTR(32, MODE_ACCUM)
+    LGS_SMEM_ATTR(64, MODE_POINT)
+#undef LGS_SMEM_ATTR
+    bc.ready = true;
+    return cudaSuccess;
+}
+
+static cudaError_t ensure_work(BlockedCtx& bc, BlockedWork& w, int64_t cap) {
+    if (w.cap >= cap) return cudaSuccess;
+    cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
+    w = BlockedWork{};
+    cudaError_t e;
+    if ((e = cudaMalloc(&w.X, sizeof(double) * (size_t)bc.npad * cap)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w.lp, sizeof(double) * cap)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w.d2, sizeof(double) * cap)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w.lz, sizeof(double) * cap)) != cudaSuccess) return e;
+    // columns past S of a partial tile feed the contractions (their results are never stored to V): keep them finite
+    if ((e = cudaMemset(w.X, 0, sizeof(double) * (size_t)bc.npad * cap)) != cudaSuccess) return e;
+    w.cap = cap;
+    return cudaSuccess;
+}
+
+// One batch of S <= w.cap Klein proposals into w.X (coefficients), w.lp, w.d2, w.lz.
+static cudaError_t klein_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64_t seed, uint64_t first_id,
+                               uint32_t tag, const int64_t* tag_dev, bool want_lz, cudaStream_t st) {
+    const int nb = bc.npad / kPB;
+    const int64_t ld = w.cap;
+    const int pblocks = (int)((S + kPanelThreads - 1) / kPanelThreads);
+    cudaError_t e;
+    auto panel = [&](int b, bool first) {
+        if (want_lz)
+            klein_panel_kernel<true><<<pblocks, kPanelThreads, 0, st>>>(bc.panels[b], w.X, ld, b * kPB, S, seed, first_id,
+                                                                        tag, tag_dev, first ? 1 : 0, w.lp, w.d2, w.lz);
+        else
+            klein_panel_kernel<false><<<pblocks, kPanelThreads, 0, st>>>(bc.panels[b], w.X, ld, b * kPB, S, seed,
+                                                                         first_id, tag, tag_dev, first ? 1 : 0, w.lp,
+                                                                         w.d2, w.lz);
+        return cudaGetLastError();
+    };
+    int b = nb - 1;
+    bool first = true;
+    if (nb & 1) {  // odd number of 32-blocks: the top one stands alone
+        if ((e = launch_contract<32, MODE_PANEL>(bc.Rp, bc.npad, w.X, ld, b * kPB, kPB, bc.npad, bc.npad, bc.tp, S,
+                                                 nullptr, 0, 0, st)) != cudaSuccess) return e;
+        if ((e = panel(b, first)) != cudaSuccess) return e;
+        first = false;
+        b--;
+    }
+    for (; b >= 1; b -= 2) {
+        const int lo = (b - 1) * kPB;  // first coordinate of the pair
+        // centers of both blocks from everything already drawn (coordinates >= lo + 64)
+        if ((e = launch_contract<64, MODE_PANEL>(bc.Rp, bc.npad, w.X, ld, lo, 64, lo + 64, bc.npad, bc.tp, S, nullptr,
+                                                 0, 0, st)) != cudaSuccess) return e;
+        if ((e = panel(b, first)) != cudaSuccess) return e;
+        first = false;
+        // the upper block's contribution to the lower block
+        if ((e = launch_contract<32, MODE_ACCUM>(bc.Rp, bc.npad, w.X, ld, lo, kPB, lo + kPB, lo + 64, bc.tp, S,
+                                                 nullptr, 0, 0, st)) != cudaSuccess) return e;
+        if ((e = panel(b - 1, false)) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
+                                 double* logq, cudaStream_t st) {
+    if (S <= 0) return cudaSuccess;
+    const int64_t kMaxBatch = 1 << 17;
+    int64_t cap = S < kMaxBatch ? (S + 127) / 128 * 128 : kMaxBatch;
+    BlockedWork& w = bc.work[0];
+    cudaError_t e = ensure_work(bc, w, cap);
+    if (e != cudaSuccess) return e;
+    for (int64_t s0 = 0; s0 < S; s0 += w.cap) {
+        const int64_t cnt = (S - s0) < w.cap ? (S - s0) : w.cap;
+        if ((e = klein_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, 0u, nullptr, false, st)) != cudaSuccess)
+            return e;
+        if (V) {
+            if ((e = launch_contract<64, MODE_POINT>(bc.Bp, bc.npad, w.X, w.cap, 0, bc.mpad, 0, bc.npad, nullptr, cnt,
+                                                     V + (size_t)s0 * bc.n, bc.n, bc.n, st)) != cudaSuccess) return e;
+        }
+        if (X) {
+            dim3 grid((unsigned)((cnt + 31) / 32), (unsigned)((bc.n + 31) / 32));
+            export_coeffs_kernel<<<grid, 256, 0, st>>>(w.X, w.cap, bc.n, cnt, X + (size_t)s0 * bc.n);
+        }
+        if (logq) finish_logq_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(w.lp, bc.sum_lognorm, cnt, logq + s0);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace lgs

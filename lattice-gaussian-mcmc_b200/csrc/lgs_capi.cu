@@ -85,9 +85,13 @@ int lgs_create(const lgs_desc* d, lgs_handle** out) {
 
     const int n = d->n;
     const double sigma = d->sigma;
-    std::vector<double> rdiag(n), sig(n), lognorm(n), inv2s2(n), q(n), sq(n), znorm(n), eps1(n);
-    std::vector<uint8_t> mode(n);
-    std::vector<int> uidx(n), kind(n), dmax(n);
+    HostConsts hc;
+    hc.rdiag.resize(n); hc.sig.resize(n); hc.lognorm.resize(n); hc.inv2s2.resize(n); hc.q.resize(n); hc.sq.resize(n);
+    hc.znorm.resize(n); hc.eps1.resize(n); hc.mode.resize(n); hc.uidx.resize(n); hc.kind.resize(n); hc.dmax.resize(n);
+    std::vector<double>&rdiag = hc.rdiag, &sig = hc.sig, &lognorm = hc.lognorm, &inv2s2 = hc.inv2s2, &q = hc.q,
+                       &sq = hc.sq, &znorm = hc.znorm, &eps1 = hc.eps1;
+    std::vector<uint8_t>& mode = hc.mode;
+    std::vector<int>&uidx = hc.uidx, &kind = hc.kind, &dmax = hc.dmax;
     const double log_2pi = std::log(2.0 * M_PI);
     for (int i = 0; i < n; i++) {
         double rii = d->R[(size_t)i * n + i];
@@ -174,6 +178,15 @@ int lgs_create(const lgs_desc* d, lgs_handle** out) {
     c.fz_eps1 = (const double*)(base + o5);
     c.fz_kind = (const int*)(base + o6);
     c.fz_dmax = (const int*)(base + o7);
+    if (d->path != LGS_PATH_ORDERED) {
+        e = blocked_init(h->blocked, *d, hc);
+        if (e != cudaSuccess) {
+            blocked_free(h->blocked);
+            cudaFree(h->arena);
+            delete h;
+            return cuda_fail(nullptr, e, "blocked_init");
+        }
+    }
     *out = h;
     return LGS_OK;
 }
@@ -182,6 +195,7 @@ void lgs_destroy(lgs_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     free_chains(h->chains);
+    blocked_free(h->blocked);
     cudaFree(h->scratch.Xw);
     cudaFree(h->stage_dev);
     cudaFree(h->arena);
@@ -197,6 +211,13 @@ int lgs_klein_sample(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_sam
     if (samplez != LGS_SAMPLEZ_TABLE && samplez != LGS_SAMPLEZ_FAST)
         return fail(h, LGS_E_INVALID, "lgs_klein_sample: unknown samplez");
     LGS_CUDA(h, cudaSetDevice(h->device));
+    if (samplez == LGS_SAMPLEZ_FAST && h->path != LGS_PATH_ORDERED && h->blocked.ready) {
+        LGS_CUDA(h, launch_klein_blocked(h->blocked, S, seed, first_sample_id, V_dev, X_dev, logq_dev,
+                                         (cudaStream_t)stream));
+        return LGS_OK;
+    }
+    if (h->path == LGS_PATH_BLOCKED)
+        return fail(h, LGS_E_INVALID, "lgs_klein_sample: the blocked path needs LGS_SAMPLEZ_FAST");
     RngSpec rng{nullptr, 0, seed, first_sample_id};
     LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, S, rng, samplez, V_dev, X_dev, logq_dev, nullptr,
                                      (cudaStream_t)stream));

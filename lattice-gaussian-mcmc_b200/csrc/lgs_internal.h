@@ -4,6 +4,8 @@
 #include <string>
 #include <cuda_runtime.h>
 
+#include <vector>
+
 #include "../../include/lgs_b200.h"
 #include "lgs_device.cuh"
 
@@ -32,6 +34,54 @@ struct ChainSet {
     int64_t* upos = nullptr;      // [chains] unused (replay positions are per call)
 };
 
+// ---- blocked (DMMA) path -------------------------------------------------------------------------------
+constexpr int kPB = 32;  // coordinates per panel-kernel block
+
+// Constants of one 32-coordinate block, passed by value as kernel parameters so that the in-block triangle of R
+// and the SampleZ constants are read from the constant bank (no shared-memory or global traffic in the serial loop).
+struct PanelParams {
+    double nrt[kPB * kPB];  // nrt[i*32 + k] = -R[i0+k][i0+i] for k < i: what drawing x_i subtracts from center k
+    double inv_r[kPB];      // 1 / R_ii
+    double r2[kPB];         // R_ii^2                      (||Bx - c||^2 = sum r_ii^2 (x_i - m_i)^2)
+    double inv2s2[kPB];     // 1 / (2 sigma_i^2)
+    double q[kPB];          // exp(-1/sigma_i^2)
+    double sq[kPB];         // exp(-1/(2 sigma_i^2))
+    double znorm[kPB];      // sigma_i sqrt(2 pi)
+    double eps1[kPB];       // 2 exp(-2 pi^2 sigma_i^2)
+    int kind[kPB];
+    int dmax[kPB];
+    int uidx[kPB];          // draw index of the coordinate in the reference's consumption order
+    unsigned char mode[kPB];  // 1 = round-to-mean coordinate (sigma_i < 1e-10, klein.py:201-204) or padding
+};
+
+// one batch worth of device workspace for the blocked path
+struct BlockedWork {
+    double* X = nullptr;    // [npad][cap] coordinate-major centers / coefficients
+    double* lp = nullptr;   // [cap] sum (x_i - m_i)^2 / (2 sigma_i^2)
+    double* d2 = nullptr;   // [cap] sum r_ii^2 (x_i - m_i)^2
+    double* lz = nullptr;   // [cap] sum log rho_{sigma_i,m_i}(Z)
+    int64_t cap = 0;        // samples per batch, multiple of 128
+};
+
+struct BlockedCtx {
+    bool ready = false;
+    int n = 0, npad = 0, mpad = 0;     // npad: coordinates padded to 32; mpad: rows of B padded to 64
+    double* Rp = nullptr;              // [npad][npad] R, identity on the padding
+    double* Bp = nullptr;              // [mpad][npad] basis, zero padding
+    double* tp = nullptr;              // [npad] Q^T c, zero padding
+    double sum_lognorm = 0.0;          // sum_i 0.5 log(2 pi) + log sigma_i   (klein.py:262)
+    double two_sigma2 = 0.0;
+    std::vector<PanelParams> panels;   // npad / 32 blocks, index = i0 / 32
+    BlockedWork work[2];
+};
+
+// per-coordinate constants computed once on the host by lgs_create()
+struct HostConsts {
+    std::vector<double> rdiag, sig, lognorm, inv2s2, q, sq, znorm, eps1;
+    std::vector<uint8_t> mode;
+    std::vector<int> uidx, kind, dmax;
+};
+
 struct Scratch {
     double* Xw = nullptr;  // [n][S_cap] coefficient workspace of the ordered Klein kernel
     int64_t cap = 0;
@@ -47,6 +97,7 @@ struct lgs_handle {
     void* arena = nullptr;      // one allocation holding every per-sampler constant
     lgs::Scratch scratch;
     lgs::ChainSet chains;
+    lgs::BlockedCtx blocked;
     // staging for the *_host entry points
     void* stage_dev = nullptr;
     size_t stage_cap = 0;
@@ -67,5 +118,11 @@ cudaError_t launch_imhk_get_state(const DeviceCtx& ctx, ChainSet& cs, int64_t* c
 cudaError_t launch_histogram(const DeviceCtx& ctx, const double* V, int64_t S, const int32_t* dims_dev, int n_dims,
                              double lo, double width, int nbins, int64_t* hist, cudaStream_t st);
 cudaError_t launch_reduce_counts(const ChainSet& cs, int64_t* out2, cudaStream_t st);
+
+// lgs_blocked.cu  (DMMA contractions + panel kernel)
+cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc);
+void blocked_free(BlockedCtx& bc);
+cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
+                                 double* logq, cudaStream_t st);
 
 }  // namespace lgs

@@ -1,0 +1,129 @@
+"""The blocked DMMA path (lgs_blocked.cu) against the ordered one-thread-per-sample path (lgs_ordered.cu, itself
+pinned bit-exact against the oracle in replay mode) and against the oracle.
+
+Both paths use the same Philox key per (sample, draw) and the same fast SampleZ, so they must produce the same
+integer coefficient vectors except where a conditional mean, which the blocked path accumulates in a different order
+(error ~1e-13 relative), moves a uniform across a CDF boundary: probability ~1e-12 per draw.  The test therefore
+requires *zero* differing samples at these sizes and reports the count otherwise.
+Floating-point outputs: lattice points are exact integers for integer bases (bit-exact required); log-densities agree
+to 1e-10 relative (different summation order, fma vs two roundings).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lgs():
+    import __graft_entry__ as g
+    g.build()
+    import lattice_gaussian_mcmc_b200 as m
+    return m
+
+
+def _pair(lgs, lat, sigma, center, seed):
+    a = lgs.KleinSampler(lat, sigma, center, seed=seed, path="ordered", samplez="fast")
+    b = lgs.KleinSampler(lat, sigma, center, seed=seed, path="blocked", samplez="fast")
+    return a, b
+
+
+@pytest.mark.parametrize("n,S", [(1, 300), (10, 1000), (32, 129), (33, 640), (48, 2000), (64, 128), (96, 1111),
+                                 (200, 700), (256, 512), (520, 300)])
+def test_blocked_equals_ordered(lgs, n, S):
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(n, seed=100 + n)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    center = np.random.RandomState(n).uniform(-40, 40, n)
+    a, b = _pair(lgs, lat, sigma, center, seed=7)
+    Va, Xa, la = a.sample_with_coefficients(S)
+    Vb, Xb, lb = b.sample_with_coefficients(S)
+    mism = int(np.sum(np.any(Xa != Xb, axis=1)))
+    assert mism == 0, f"{mism} of {S} samples differ between the blocked and the ordered path"
+    assert np.array_equal(Vb, Xb.astype(np.float64) @ lat.basis.T)
+    assert np.array_equal(Va, Vb)
+    assert np.max(np.abs(la - lb) / np.abs(la)) < 1e-10
+    # and the Klein log-density recomputed from the coefficients by the ordered kernel (klein.py:222-271)
+    lc = b.compute_log_density_batch(Xb)
+    assert np.max(np.abs(lc - lb) / np.abs(lc)) < 1e-10
+
+
+def test_blocked_real_basis(lgs):
+    rng = np.random.RandomState(8)
+    n = 80
+    B = rng.normal(size=(n, n)) * 2 + 12 * np.eye(n)
+    lat = lgs.SimpleLattice(B)
+    a, b = _pair(lgs, lat, 25.0, np.linspace(-3, 3, n), seed=3)
+    Va, Xa, la = a.sample_with_coefficients(900)
+    Vb, Xb, lb = b.sample_with_coefficients(900)
+    assert int(np.sum(np.any(Xa != Xb, axis=1))) == 0
+    ref = Xb.astype(np.float64) @ B.T
+    assert np.max(np.abs(Vb - ref)) <= 1e-12 * np.max(np.abs(ref))
+    assert np.max(np.abs(Va - Vb)) <= 1e-12 * np.max(np.abs(ref))
+
+
+def test_blocked_multi_batch_and_split_invariance(lgs):
+    """more samples than one device batch (2^17) and the same range drawn in pieces: identical output"""
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(16, seed=3)
+    S = (1 << 17) + 1000
+    # an off-lattice center: with center 0 on an integer basis the conditional means are rationals with small
+    # denominators and hit exact half-integers (about one sample in a thousand), where round-to-nearest of a mean
+    # that carries 1e-16 of summation noise may legitimately go either way and the two paths pick different -- equally
+    # valid -- draws
+    center = np.random.RandomState(1).uniform(-9, 9, 16)
+    a = lgs.KleinSampler(lat, 50.0, center, seed=11, path="blocked")
+    whole = a.sample_coefficients(S)
+    b = lgs.KleinSampler(lat, 50.0, center, seed=11, path="blocked")
+    parts = np.concatenate([b.sample_coefficients(70000), b.sample_coefficients(S - 70000)])
+    assert np.array_equal(whole, parts)
+    c = lgs.KleinSampler(lat, 50.0, center, seed=11, path="ordered", samplez="fast")
+    assert np.array_equal(whole[:5000], c.sample_coefficients(5000))
+    # center 0: ties happen; the paths then differ on a small fraction of samples only, and agree in law
+    a0 = lgs.KleinSampler(lat, 50.0, seed=11, path="blocked").sample_coefficients(20000)
+    c0 = lgs.KleinSampler(lat, 50.0, seed=11, path="ordered", samplez="fast").sample_coefficients(20000)
+    assert np.mean(np.any(a0 != c0, axis=1)) < 0.01
+
+
+def test_blocked_qary_and_round_mode_coordinates(lgs):
+    """q-ary shape (sigma_i in {sigma/q, sigma}) and a basis with a rounding coordinate (sigma_i < 1e-10)"""
+    from lattice_gaussian_mcmc_b200.lattices import qary_basis
+    A = np.random.RandomState(0).randint(0, 97, size=(20, 20))
+    Bq = qary_basis(A, 97)
+    lat = lgs.SimpleLattice(Bq)
+    a, b = _pair(lgs, lat, 30.0, None, seed=5)
+    Xa, Xb = a.sample_coefficients(1500), b.sample_coefficients(1500)
+    assert np.array_equal(Xa, Xb)
+    D = np.diag([1e12, 40.0, 1.0, 3.0])
+    lat = lgs.SimpleLattice(D)
+    a, b = _pair(lgs, lat, 2.0, np.array([3.3e11, 17.2, 0.4, 1.0]), seed=5)
+    Xa, Xb = a.sample_coefficients(500), b.sample_coefficients(500)
+    assert np.array_equal(Xa, Xb)
+    assert np.all(Xb[:, 0] == 0)   # round(3.3e11 / 1e12)
+
+
+def test_blocked_distribution_n1024_last_coordinates(lgs):
+    """n = 1024 on the dimension-sweep family: the last coordinate is exactly D_{Z, sigma/R_nn, t_n/R_nn};
+    chi-square against the reference table, plus V = B x exactly."""
+    from scipy import stats
+    from oracle import oracle
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    n, S = 1024, 40000
+    lat = dd_lattice(n, seed=1)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    smp = lgs.KleinSampler(lat, sigma, seed=2, path="blocked")
+    V, X, lq = smp.sample_with_coefficients(S)
+    assert np.array_equal(V, X.astype(np.float64) @ lat.basis.T)
+    rnn = smp.R[-1, -1]
+    sup, lp = oracle.table(smp.center_transformed[-1] / rnn, sigma / abs(rnn))
+    e = np.exp(lp) * S
+    keep = e >= 10
+    o = np.array([(X[:, -1] == s).sum() for s in sup[keep]], dtype=np.float64)
+    ee = e[keep]
+    o, ee = np.append(o, S - o.sum()), np.append(ee, S - ee.sum())
+    chi2 = np.sum((o - ee) ** 2 / ee)
+    assert stats.chi2.sf(chi2, len(ee) - 1) > 1e-3
+    # E||v||^2 within 10 % of n sigma^2 (tests/test_samplers.py:336-360)
+    assert abs(np.mean(np.sum(V * V, axis=1)) / (n * sigma ** 2) - 1) < 0.1
+    lc = smp.compute_log_density_batch(X[:2000])
+    assert np.max(np.abs(lc - lq[:2000]) / np.abs(lc)) < 1e-10
