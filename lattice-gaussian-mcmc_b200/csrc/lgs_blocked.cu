@@ -437,4 +437,170 @@ cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint6
     return cudaSuccess;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// IMHK on the blocked path (imhk.py:126-177): all chains of the handle step together.
+// One step = one blocked Klein batch (the proposals) + the accept kernel + a predicated copy of accepted
+// proposals into the current-state matrix; kept states go through the lattice-point contraction straight into
+// the caller's [chain][keep][n] array.  Burn-in and thinning never leave the device.
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+
+// imhk.py:102-124 + 156-174 for one chain per thread.  init != 0: _initialize_chain (no accept test, no count).
+__global__ void __launch_bounds__(256)
+imhk_accept_kernel(int64_t C, const double* __restrict__ lp, const double* __restrict__ d2,
+                   const double* __restrict__ lz, double sum_lognorm, double two_sigma2, int exact, int init,
+                   uint64_t seed, uint64_t first_id, uint32_t tag, double* __restrict__ lw_cur,
+                   int64_t* __restrict__ counts, uint8_t* __restrict__ flags) {
+    const int64_t ch = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (ch >= C) return;
+    // log pi(x) - log q(x): base.py:133-144 minus klein.py:246-269, with ||Bx - c||^2 = sum r_ii^2 (x_i - m_i)^2
+    const double logq = -lp[ch] - sum_lognorm;
+    const double lw_prop = exact ? lz[ch] : (-d2[ch] / two_sigma2) - logq;
+    if (init) {
+        lw_cur[ch] = lw_prop;
+        flags[ch] = 1;
+        return;
+    }
+    const double lw = lw_cur[ch];
+    const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
+    const Philox gen(seed);
+    const double u = philox_uniform(gen, first_id + (uint64_t)ch, kAcceptDraw, tag);
+    const bool acc = u < ratio;
+    counts[ch * 2 + 1] += 1;
+    if (acc) {
+        counts[ch * 2] += 1;
+        lw_cur[ch] = lw_prop;
+    }
+    flags[ch] = acc ? 1 : 0;
+}
+
+// current_state <- proposal where accepted (imhk.py:169-171); coalesced along chains
+__global__ void __launch_bounds__(256)
+imhk_commit_kernel(int64_t C, int npad, int64_t ld, const uint8_t* __restrict__ flags,
+                   const double* __restrict__ Xprop, double* __restrict__ Xcur) {
+    const int64_t ch = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (ch >= C) return;
+    const bool a0 = flags[ch], a1 = (ch + 1 < C) && flags[ch + 1];
+    if (!a0 && !a1) return;
+    for (int i = blockIdx.y; i < npad; i += gridDim.y) {
+        const size_t o = (size_t)i * ld + ch;
+        if (a0 && a1) {
+            *reinterpret_cast<double2*>(Xcur + o) = *reinterpret_cast<const double2*>(Xprop + o);
+        } else if (a0) {
+            Xcur[o] = Xprop[o];
+        } else {
+            Xcur[o + 1] = Xprop[o + 1];
+        }
+    }
+}
+
+// X (coordinate-major doubles) -> int64 out[s * ldo + i]
+__global__ void __launch_bounds__(256)
+export_coeffs_strided_kernel(const double* __restrict__ X, int64_t ld, int n, int64_t S, int64_t* __restrict__ out,
+                             int64_t ldo) {
+    __shared__ double tile[32][33];
+    const int64_t s0 = (int64_t)blockIdx.x * 32;
+    const int i0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) {
+        int i = i0 + r;
+        int64_t s = s0 + tx;
+        tile[r][tx] = (i < n && s < S) ? X[(size_t)i * ld + s] : 0.0;
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        int64_t s = s0 + r;
+        int i = i0 + tx;
+        if (s < S && i < n) out[(size_t)s * ldo + i] = (int64_t)tile[tx][r];
+    }
+}
+
+}  // namespace
+
+static cudaError_t ensure_blocked_chains(BlockedCtx& bc, ChainSet& cs) {
+    const int64_t cap = (cs.chains + 127) / 128 * 128;
+    if (cs.bl_cap >= cap && cs.Xcur) return cudaSuccess;
+    cudaFree(cs.Xcur);
+    cudaFree(cs.flags);
+    cs.Xcur = nullptr;
+    cs.flags = nullptr;
+    cs.bl_cap = 0;
+    cudaError_t e;
+    if ((e = cudaMalloc(&cs.Xcur, sizeof(double) * (size_t)bc.npad * cap)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&cs.flags, cap)) != cudaSuccess) return e;
+    if ((e = cudaMemset(cs.Xcur, 0, sizeof(double) * (size_t)bc.npad * cap)) != cudaSuccess) return e;
+    cs.bl_cap = cap;
+    return cudaSuccess;
+}
+
+cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin,
+                                int weight_mode, double* V, int64_t* X, cudaStream_t st) {
+    const int64_t C = cs.chains;
+    cudaError_t e;
+    if ((e = ensure_blocked_chains(bc, cs)) != cudaSuccess) return e;
+    BlockedWork& w = bc.work[1];
+    if ((e = ensure_work(bc, w, cs.bl_cap)) != cudaSuccess) return e;
+    if (w.cap != cs.bl_cap) {  // the proposal and the state matrices share one leading dimension
+        BlockedWork fresh;
+        cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
+        w = fresh;
+        if ((e = ensure_work(bc, w, cs.bl_cap)) != cudaSuccess) return e;
+    }
+    const int64_t ld = cs.bl_cap;
+    const bool exact = weight_mode == LGS_WEIGHT_EXACT;
+    const unsigned ablocks = (unsigned)((C + 255) / 256);
+    dim3 cgrid((unsigned)((C / 2 + 255) / 256 + 1), (unsigned)(bc.npad < 64 ? bc.npad : 64));
+    auto one_step = [&](bool init) -> cudaError_t {
+        const uint32_t tag = init ? 0u : (uint32_t)(++cs.bl_steps);
+        cudaError_t er = klein_batch(bc, w, C, cs.seed, cs.first_id, tag, nullptr, exact, st);
+        if (er != cudaSuccess) return er;
+        imhk_accept_kernel<<<ablocks, 256, 0, st>>>(C, w.lp, w.d2, w.lz, bc.sum_lognorm, bc.two_sigma2, exact ? 1 : 0,
+                                                    init ? 1 : 0, cs.seed, cs.first_id, tag, cs.logw, cs.counts,
+                                                    cs.flags);
+        imhk_commit_kernel<<<cgrid, 256, 0, st>>>(C, bc.npad, ld, cs.flags, w.X, cs.Xcur);
+        return cudaGetLastError();
+    };
+    if (!cs.bl_init) {
+        if ((e = one_step(true)) != cudaSuccess) return e;
+        cs.bl_init = true;
+    }
+    const int64_t steps = burn_in + keep * thin;
+    for (int64_t stp = 0; stp < steps; stp++) {
+        if ((e = one_step(false)) != cudaSuccess) return e;
+        if (stp >= burn_in && (stp - burn_in + 1) % thin == 0) {
+            const int64_t kidx = (stp - burn_in + 1) / thin - 1;
+            if (V) {
+                if ((e = launch_contract<64, MODE_POINT>(bc.Bp, bc.npad, cs.Xcur, ld, 0, bc.mpad, 0, bc.npad, nullptr,
+                                                         C, V + (size_t)kidx * bc.n, keep * (int64_t)bc.n, bc.n,
+                                                         st)) != cudaSuccess) return e;
+            }
+            if (X) {
+                dim3 grid((unsigned)((C + 31) / 32), (unsigned)((bc.n + 31) / 32));
+                export_coeffs_strided_kernel<<<grid, 256, 0, st>>>(cs.Xcur, ld, bc.n, C, X + (size_t)kidx * bc.n,
+                                                                   keep * (int64_t)bc.n);
+                if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            }
+        }
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_imhk_blocked_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
+                                          double* logw, cudaStream_t st) {
+    const int64_t C = cs.chains;
+    cudaError_t e;
+    if (counts && (e = cudaMemcpyAsync(counts, cs.counts, sizeof(int64_t) * 2 * C, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
+    if (logw && (e = cudaMemcpyAsync(logw, cs.logw, sizeof(double) * C, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
+    if (X) {
+        dim3 grid((unsigned)((C + 31) / 32), (unsigned)((bc.n + 31) / 32));
+        export_coeffs_strided_kernel<<<grid, 256, 0, st>>>(cs.Xcur, cs.bl_cap, bc.n, C, X, bc.n);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    if (V) {
+        if ((e = launch_contract<64, MODE_POINT>(bc.Bp, bc.npad, cs.Xcur, cs.bl_cap, 0, bc.mpad, 0, bc.npad, nullptr, C,
+                                                 V, bc.n, bc.n, st)) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
 }  // namespace lgs

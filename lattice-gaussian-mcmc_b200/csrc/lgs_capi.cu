@@ -51,7 +51,7 @@ int ensure_stage(lgs_handle* h, size_t nbytes) {
 
 void free_chains(ChainSet& cs) {
     cudaFree(cs.Xbuf); cudaFree(cs.Vbuf); cudaFree(cs.logw); cudaFree(cs.cur); cudaFree(cs.init);
-    cudaFree(cs.counts); cudaFree(cs.step_no);
+    cudaFree(cs.counts); cudaFree(cs.step_no); cudaFree(cs.Xcur); cudaFree(cs.flags);
     cs = ChainSet{};
 }
 
@@ -314,9 +314,6 @@ int lgs_imhk_reset(lgs_handle* h, int64_t chains, uint64_t seed, uint64_t first_
     ChainSet& cs = h->chains;
     if (cs.chains != chains) {
         free_chains(cs);
-        size_t buf = sizeof(double) * 2 * (size_t)h->n * chains;
-        LGS_CUDA(h, cudaMalloc(&cs.Xbuf, buf));
-        LGS_CUDA(h, cudaMalloc(&cs.Vbuf, buf));
         LGS_CUDA(h, cudaMalloc(&cs.logw, sizeof(double) * chains));
         LGS_CUDA(h, cudaMalloc(&cs.cur, sizeof(int32_t) * chains));
         LGS_CUDA(h, cudaMalloc(&cs.init, sizeof(int32_t) * chains));
@@ -326,13 +323,29 @@ int lgs_imhk_reset(lgs_handle* h, int64_t chains, uint64_t seed, uint64_t first_
     }
     cs.seed = seed;
     cs.first_id = first_chain_id;
-    LGS_CUDA(h, cudaMemset(cs.Xbuf, 0, sizeof(double) * 2 * (size_t)h->n * chains));
-    LGS_CUDA(h, cudaMemset(cs.Vbuf, 0, sizeof(double) * 2 * (size_t)h->n * chains));
+    cs.state_path = 0;
+    cs.bl_init = false;
+    cs.bl_steps = 0;
     LGS_CUDA(h, cudaMemset(cs.logw, 0, sizeof(double) * chains));
     LGS_CUDA(h, cudaMemset(cs.cur, 0, sizeof(int32_t) * chains));
     LGS_CUDA(h, cudaMemset(cs.init, 0, sizeof(int32_t) * chains));
     LGS_CUDA(h, cudaMemset(cs.counts, 0, sizeof(int64_t) * 2 * chains));
     LGS_CUDA(h, cudaMemset(cs.step_no, 0, sizeof(int64_t) * chains));
+    return LGS_OK;
+}
+
+// the ordered kernels keep two state buffers per chain (current / proposal), allocated on first use
+static int ensure_ordered_chains(lgs_handle* h) {
+    ChainSet& cs = h->chains;
+    if (cs.state_path == 2) return fail(h, LGS_E_STATE, "imhk: this chain set is owned by the blocked path; call lgs_imhk_reset()");
+    if (!cs.Xbuf) {
+        size_t buf = sizeof(double) * 2 * (size_t)h->n * cs.chains;
+        LGS_CUDA(h, cudaMalloc(&cs.Xbuf, buf));
+        LGS_CUDA(h, cudaMalloc(&cs.Vbuf, buf));
+        LGS_CUDA(h, cudaMemset(cs.Xbuf, 0, buf));
+        LGS_CUDA(h, cudaMemset(cs.Vbuf, 0, buf));
+    }
+    cs.state_path = 1;
     return LGS_OK;
 }
 
@@ -348,6 +361,19 @@ int lgs_imhk_run(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int
     int rc = imhk_check(h, burn_in, keep, thin);
     if (rc) return rc;
     LGS_CUDA(h, cudaSetDevice(h->device));
+    if (samplez != LGS_SAMPLEZ_TABLE && samplez != LGS_SAMPLEZ_FAST) return fail(h, LGS_E_INVALID, "imhk: unknown samplez");
+    if (weight_mode != LGS_WEIGHT_REFERENCE && weight_mode != LGS_WEIGHT_EXACT) return fail(h, LGS_E_INVALID, "imhk: unknown weight mode");
+    ChainSet& cs = h->chains;
+    const bool want_blocked = samplez == LGS_SAMPLEZ_FAST && h->path != LGS_PATH_ORDERED && h->blocked.ready;
+    if (cs.state_path == 2 || (cs.state_path == 0 && want_blocked)) {
+        if (!want_blocked) return fail(h, LGS_E_STATE, "imhk: this chain set is owned by the blocked path (fast SampleZ); call lgs_imhk_reset()");
+        cs.state_path = 2;
+        LGS_CUDA(h, launch_imhk_blocked(h->blocked, cs, burn_in, keep, thin, weight_mode, V_dev, X_dev,
+                                        (cudaStream_t)stream));
+        return LGS_OK;
+    }
+    rc = ensure_ordered_chains(h);
+    if (rc) return rc;
     RngSpec rng{nullptr, 0, h->chains.seed, h->chains.first_id};
     LGS_CUDA(h, launch_imhk_ordered(h->ctx, h->chains, burn_in, keep, thin, rng, samplez, weight_mode, V_dev, X_dev,
                                     nullptr, nullptr, nullptr, (cudaStream_t)stream));
@@ -361,6 +387,8 @@ int lgs_imhk_replay(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, 
     if (rc) return rc;
     if (!U_dev) return fail(h, LGS_E_INVALID, "lgs_imhk_replay: NULL uniform stream");
     LGS_CUDA(h, cudaSetDevice(h->device));
+    rc = ensure_ordered_chains(h);
+    if (rc) return rc;
     if (fallback_count_dev) LGS_CUDA(h, cudaMemsetAsync(fallback_count_dev, 0, sizeof(int32_t), (cudaStream_t)stream));
     RngSpec rng{U_dev, stride, 0, 0};
     LGS_CUDA(h, launch_imhk_ordered(h->ctx, h->chains, burn_in, keep, thin, rng, LGS_SAMPLEZ_TABLE, weight_mode, V_dev,
@@ -373,6 +401,12 @@ int lgs_imhk_get_state(lgs_handle* h, int64_t* counts_dev, int64_t* X_dev, doubl
     if (!h) return LGS_E_INVALID;
     if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
     LGS_CUDA(h, cudaSetDevice(h->device));
+    if (h->chains.state_path == 0) return fail(h, LGS_E_STATE, "imhk: the chains have no state yet");
+    if (h->chains.state_path == 2) {
+        LGS_CUDA(h, launch_imhk_blocked_get_state(h->blocked, h->chains, counts_dev, X_dev, V_dev, logw_dev,
+                                                  (cudaStream_t)stream));
+        return LGS_OK;
+    }
     LGS_CUDA(h, launch_imhk_get_state(h->ctx, h->chains, counts_dev, X_dev, V_dev, logw_dev, (cudaStream_t)stream));
     return LGS_OK;
 }

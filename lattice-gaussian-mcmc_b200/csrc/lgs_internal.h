@@ -32,6 +32,14 @@ struct ChainSet {
     int64_t* counts = nullptr;    // [chains*2] accepted, total
     int64_t* step_no = nullptr;   // [chains] steps performed so far (Philox stream index)
     int64_t* upos = nullptr;      // [chains] unused (replay positions are per call)
+    // which implementation owns the state: 0 = none yet, 1 = ordered kernels, 2 = blocked path
+    int state_path = 0;
+    // blocked path: all chains step together; current coefficient vectors coordinate-major [npad][cap]
+    double* Xcur = nullptr;
+    uint8_t* flags = nullptr;     // [cap] accept bit of the step in flight
+    int64_t bl_cap = 0;
+    int64_t bl_steps = 0;         // steps performed so far by every chain (Philox stream index)
+    bool bl_init = false;
 };
 
 // ---- blocked (DMMA) path -------------------------------------------------------------------------------
@@ -124,5 +132,9 @@ cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc
 void blocked_free(BlockedCtx& bc);
 cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
                                  double* logq, cudaStream_t st);
+cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin,
+                                int weight_mode, double* V, int64_t* X, cudaStream_t st);
+cudaError_t launch_imhk_blocked_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
+                                          double* logw, cudaStream_t st);
 
 }  // namespace lgs

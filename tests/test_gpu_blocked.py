@@ -127,3 +127,55 @@ def test_blocked_distribution_n1024_last_coordinates(lgs):
     assert abs(np.mean(np.sum(V * V, axis=1)) / (n * sigma ** 2) - 1) < 0.1
     lc = smp.compute_log_density_batch(X[:2000])
     assert np.max(np.abs(lc - lq[:2000]) / np.abs(lc)) < 1e-10
+
+
+@pytest.mark.parametrize("weight_mode", ["reference", "exact"])
+@pytest.mark.parametrize("n,chains", [(2, 500), (24, 300), (70, 130)])
+def test_imhk_blocked_equals_ordered(lgs, n, chains, weight_mode):
+    """same Philox keys, same fast SampleZ: the lock-step blocked chains reproduce the per-thread ordered chains
+    state for state, accept count for accept count"""
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    if n == 2:
+        lat = lgs.SimpleLattice(np.array([[4.0, 1.7], [0.0, 0.6]]))
+        sigma, center = 1.0, np.array([0.4, 0.25])   # (0.4, 0.3) would put the first mean on an exact tie, 0.3/0.6
+    else:
+        lat = dd_lattice(n, seed=n)
+        sigma = 0.6 * lat.max_gram_schmidt_norm if weight_mode == "exact" else 1.5 * lat.max_gram_schmidt_norm
+        center = np.random.RandomState(n).uniform(-20, 20, n)
+    kw = dict(burn_in=0, n_chains=chains, seed=17, weight_mode=weight_mode, samplez="fast")
+    a = lgs.IMHKSampler(lat, sigma, center, path="ordered", **kw)
+    b = lgs.IMHKSampler(lat, sigma, center, path="blocked", **kw)
+    Va = a.sample(n_samples=4, burn_in=7, thin=3)
+    Vb = b.sample(n_samples=4, burn_in=7, thin=3)
+    assert Vb.shape == (chains, 4, n)
+    if n == 2:   # non-integer basis: the DMMA contraction fuses multiply-add, the ordered kernel rounds twice
+        assert np.max(np.abs(Va - Vb)) <= 1e-14 * np.max(np.abs(Va))
+    else:
+        assert np.array_equal(Va, Vb)
+    assert a.total_proposals == b.total_proposals == chains * 19
+    assert a.accepted_proposals == b.accepted_proposals
+    if weight_mode == "exact" and n == 2:
+        assert 0.6 < b.acceptance_rate < 0.9
+    if weight_mode == "reference":
+        assert b.acceptance_rate > 0.999
+    # continue the same chains: state carried on the device
+    Xa = a.sample_coefficients(2, thin=2)
+    Xb = b.sample_coefficients(2, thin=2)
+    assert np.array_equal(Xa, Xb)
+    assert np.array_equal(a.current_coeffs, b.current_coeffs)
+    assert np.array_equal(b.current_state, b.current_coeffs.astype(np.float64) @ lat.basis.T)
+    assert np.allclose(a.current_log_weight, b.current_log_weight, rtol=1e-9, atol=1e-9)
+    assert np.array_equal(a.per_chain_acceptance, b.per_chain_acceptance)
+
+
+def test_imhk_blocked_n1024_runs_and_accepts(lgs):
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(1024, seed=1)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    im = lgs.IMHKSampler(lat, sigma, burn_in=0, n_chains=256, seed=3, path="blocked")
+    V = im.sample(n_samples=2, burn_in=3, thin=2)
+    assert V.shape == (256, 2, 1024)
+    X = im.current_coeffs
+    assert np.array_equal(V[:, -1], X.astype(np.float64) @ lat.basis.T)
+    assert im.total_proposals == 256 * 7 and im.acceptance_rate > 0.999
+    assert np.max(np.abs(im.current_log_weight - im.klein_log_partition)) < 1e-8 * abs(im.klein_log_partition)
