@@ -185,6 +185,23 @@ LGS_API int lgs_imhk_get_state_host(lgs_handle *h, int64_t *counts_host, int64_t
 LGS_API int lgs_histogram(lgs_handle *h, const double *V_dev, int64_t S, const int32_t *dims_host, int32_t n_dims,
                   double lo, double width, int32_t nbins, int64_t *hist_dev, void *stream);
 
+/*
+ * Measurement hooks (no reference counterpart; used by bench.py for the roofline figures).
+ * While enabled, every kernel launch of the blocked path is bracketed by CUDA events on its own stream;
+ * lgs_profile_read() synchronises the device, returns the summed device time [ms] and the launch count per kernel
+ * class, and clears the records.  The launch count doubles as the "how many of our kernels ran" figure.
+ */
+enum {
+    LGS_PROF_PANEL = 0,   /* klein_panel_kernel: 32 coordinates of every sample, SampleZ + in-block triangle */
+    LGS_PROF_CENTERS = 1, /* contract_kernel, centers of a block pair from all finished coordinates (DMMA) */
+    LGS_PROF_ACCUM = 2,   /* contract_kernel, 32x32 in-pair update (DMMA) */
+    LGS_PROF_POINT = 3,   /* contract_kernel, lattice points V = X B^T (DMMA) */
+    LGS_PROF_OTHER = 4,   /* accept / commit / export / log-density finish */
+    LGS_PROF_CLASSES = 5
+};
+LGS_API int lgs_profile_enable(lgs_handle *h, int on);
+LGS_API int lgs_profile_read(lgs_handle *h, double *ms_by_class, int64_t *launches_by_class);
+
 #ifdef __cplusplus
 }
 #endif

@@ -132,6 +132,18 @@ class Engine:
         check(self._h, self._lib.lgs_imhk_counts_host(self._h, ctypes.byref(a), ctypes.byref(t)))
         return int(a.value), int(t.value)
 
+    # ------------------------------------------------------------------ measurement hooks
+    PROF_CLASSES = ("panel", "centers", "accum", "point", "other")
+
+    def profile_enable(self, on=True):
+        check(self._h, self._lib.lgs_profile_enable(self._h, int(bool(on))))
+
+    def profile_read(self):
+        ms = (ctypes.c_double * 5)()
+        cnt = (ctypes.c_int64 * 5)()
+        check(self._h, self._lib.lgs_profile_read(self._h, ms, cnt))
+        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(self.PROF_CLASSES)}
+
     # ------------------------------------------------------------------ device-pointer forms
     def klein_sample_dev(self, S, seed, first_id, samplez="fast", V=0, X=0, logq=0, stream=0):
         check(self._h, self._lib.lgs_klein_sample(self._h, int(S), int(seed) & (2**64 - 1), int(first_id),

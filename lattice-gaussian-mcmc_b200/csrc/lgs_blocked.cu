@@ -22,6 +22,25 @@ namespace lgs {
 
 namespace {
 
+// brackets one launch with events when profiling is on (class ids: LGS_PROF_* in include/lgs_b200.h)
+struct ProfScope {
+    Prof& p;
+    cudaStream_t st;
+    cudaEvent_t e1 = nullptr;
+    ProfScope(Prof& prof, int cls, cudaStream_t s) : p(prof), st(s) {
+        if (!p.on) return;
+        cudaEvent_t ev[2];
+        for (auto& e : ev) {
+            if (!p.pool.empty()) { e = p.pool.back(); p.pool.pop_back(); }
+            else cudaEventCreate(&e);
+        }
+        cudaEventRecord(ev[0], st);
+        e1 = ev[1];
+        p.recs.push_back(ProfRec{cls, ev[0], ev[1]});
+    }
+    ~ProfScope() { if (e1) cudaEventRecord(e1, st); }
+};
+
 // ---------------------------------------------------------------------------------------------------------
 // panel kernel
 // ---------------------------------------------------------------------------------------------------------
@@ -257,16 +276,11 @@ __global__ void finish_logq_kernel(const double* __restrict__ lp, double sum_log
 }
 
 template <int BM, int MODE>
-cudaError_t launch_contract(const double* A, int64_t lda, double* X, int64_t ldx, int r0, int rows, int k0, int k1,
-                            const double* tvec, int64_t S, double* V, int64_t ldv, int n_valid, cudaStream_t st) {
-    static bool configured = false;
+cudaError_t launch_contract(Prof& prof, const double* A, int64_t lda, double* X, int64_t ldx, int r0, int rows, int k0,
+                            int k1, const double* tvec, int64_t S, double* V, int64_t ldv, int n_valid,
+                            cudaStream_t st) {
     const size_t smem = sizeof(GemmSmem<BM>);
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(contract_kernel<BM, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    ProfScope ps(prof, MODE == MODE_POINT ? LGS_PROF_POINT : (MODE == MODE_ACCUM ? LGS_PROF_ACCUM : LGS_PROF_CENTERS), st);
     dim3 grid((unsigned)(rows / BM), (unsigned)((S + kBN - 1) / kBN));
     contract_kernel<BM, MODE><<<grid, BM * 4, smem, st>>>(A, lda, X, ldx, r0, k0, k1, tvec, S, V, ldv, n_valid);
     return cudaGetLastError();
@@ -277,7 +291,26 @@ cudaError_t launch_contract(const double* A, int64_t lda, double* X, int64_t ldx
 // ---------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------
+cudaError_t blocked_profile_read(BlockedCtx& bc, double* ms, int64_t* launches, int nclass) {
+    for (int i = 0; i < nclass; i++) { ms[i] = 0.0; launches[i] = 0; }
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return e;
+    for (auto& r : bc.prof.recs) {
+        float t = 0.f;
+        if ((e = cudaEventElapsedTime(&t, r.e0, r.e1)) != cudaSuccess) return e;
+        if (r.cls >= 0 && r.cls < nclass) { ms[r.cls] += t; launches[r.cls] += 1; }
+        bc.prof.pool.push_back(r.e0);
+        bc.prof.pool.push_back(r.e1);
+    }
+    bc.prof.recs.clear();
+    return cudaSuccess;
+}
+
 void blocked_free(BlockedCtx& bc) {
+    for (auto& r : bc.prof.recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+    for (auto& e : bc.prof.pool) cudaEventDestroy(e);
+    bc.prof.recs.clear();
+    bc.prof.pool.clear();
     cudaFree(bc.Rp);
     cudaFree(bc.Bp);
     cudaFree(bc.tp);
@@ -378,6 +411,7 @@ static cudaError_t klein_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64
     const int pblocks = (int)((S + kPanelThreads - 1) / kPanelThreads);
     cudaError_t e;
     auto panel = [&](int b, bool first) {
+        ProfScope ps(bc.prof, LGS_PROF_PANEL, st);
         if (want_lz)
             klein_panel_kernel<true><<<pblocks, kPanelThreads, 0, st>>>(bc.panels[b], w.X, ld, b * kPB, S, seed, first_id,
                                                                         tag, tag_dev, first ? 1 : 0, w.lp, w.d2, w.lz);
@@ -390,7 +424,7 @@ static cudaError_t klein_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64
     int b = nb - 1;
     bool first = true;
     if (nb & 1) {  // odd number of 32-blocks: the top one stands alone
-        if ((e = launch_contract<32, MODE_PANEL>(bc.Rp, bc.npad, w.X, ld, b * kPB, kPB, bc.npad, bc.npad, bc.tp, S,
+        if ((e = launch_contract<32, MODE_PANEL>(bc.prof, bc.Rp, bc.npad, w.X, ld, b * kPB, kPB, bc.npad, bc.npad, bc.tp, S,
                                                  nullptr, 0, 0, st)) != cudaSuccess) return e;
         if ((e = panel(b, first)) != cudaSuccess) return e;
         first = false;
@@ -399,12 +433,12 @@ static cudaError_t klein_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64
     for (; b >= 1; b -= 2) {
         const int lo = (b - 1) * kPB;  // first coordinate of the pair
         // centers of both blocks from everything already drawn (coordinates >= lo + 64)
-        if ((e = launch_contract<64, MODE_PANEL>(bc.Rp, bc.npad, w.X, ld, lo, 64, lo + 64, bc.npad, bc.tp, S, nullptr,
+        if ((e = launch_contract<64, MODE_PANEL>(bc.prof, bc.Rp, bc.npad, w.X, ld, lo, 64, lo + 64, bc.npad, bc.tp, S, nullptr,
                                                  0, 0, st)) != cudaSuccess) return e;
         if ((e = panel(b, first)) != cudaSuccess) return e;
         first = false;
         // the upper block's contribution to the lower block
-        if ((e = launch_contract<32, MODE_ACCUM>(bc.Rp, bc.npad, w.X, ld, lo, kPB, lo + kPB, lo + 64, bc.tp, S,
+        if ((e = launch_contract<32, MODE_ACCUM>(bc.prof, bc.Rp, bc.npad, w.X, ld, lo, kPB, lo + kPB, lo + 64, bc.tp, S,
                                                  nullptr, 0, 0, st)) != cudaSuccess) return e;
         if ((e = panel(b - 1, false)) != cudaSuccess) return e;
     }
@@ -424,13 +458,15 @@ cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint6
         if ((e = klein_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, 0u, nullptr, false, st)) != cudaSuccess)
             return e;
         if (V) {
-            if ((e = launch_contract<64, MODE_POINT>(bc.Bp, bc.npad, w.X, w.cap, 0, bc.mpad, 0, bc.npad, nullptr, cnt,
+            if ((e = launch_contract<64, MODE_POINT>(bc.prof, bc.Bp, bc.npad, w.X, w.cap, 0, bc.mpad, 0, bc.npad, nullptr, cnt,
                                                      V + (size_t)s0 * bc.n, bc.n, bc.n, st)) != cudaSuccess) return e;
         }
         if (X) {
+            ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
             dim3 grid((unsigned)((cnt + 31) / 32), (unsigned)((bc.n + 31) / 32));
             export_coeffs_kernel<<<grid, 256, 0, st>>>(w.X, w.cap, bc.n, cnt, X + (size_t)s0 * bc.n);
         }
+        ProfScope ps2(bc.prof, LGS_PROF_OTHER, st);
         if (logq) finish_logq_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(w.lp, bc.sum_lognorm, cnt, logq + s0);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
@@ -554,6 +590,7 @@ cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, i
         const uint32_t tag = init ? 0u : (uint32_t)(++cs.bl_steps);
         cudaError_t er = klein_batch(bc, w, C, cs.seed, cs.first_id, tag, nullptr, exact, st);
         if (er != cudaSuccess) return er;
+        ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
         imhk_accept_kernel<<<ablocks, 256, 0, st>>>(C, w.lp, w.d2, w.lz, bc.sum_lognorm, bc.two_sigma2, exact ? 1 : 0,
                                                     init ? 1 : 0, cs.seed, cs.first_id, tag, cs.logw, cs.counts,
                                                     cs.flags);
@@ -570,7 +607,7 @@ cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, i
         if (stp >= burn_in && (stp - burn_in + 1) % thin == 0) {
             const int64_t kidx = (stp - burn_in + 1) / thin - 1;
             if (V) {
-                if ((e = launch_contract<64, MODE_POINT>(bc.Bp, bc.npad, cs.Xcur, ld, 0, bc.mpad, 0, bc.npad, nullptr,
+                if ((e = launch_contract<64, MODE_POINT>(bc.prof, bc.Bp, bc.npad, cs.Xcur, ld, 0, bc.mpad, 0, bc.npad, nullptr,
                                                          C, V + (size_t)kidx * bc.n, keep * (int64_t)bc.n, bc.n,
                                                          st)) != cudaSuccess) return e;
             }
@@ -597,7 +634,7 @@ cudaError_t launch_imhk_blocked_get_state(BlockedCtx& bc, ChainSet& cs, int64_t*
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     if (V) {
-        if ((e = launch_contract<64, MODE_POINT>(bc.Bp, bc.npad, cs.Xcur, cs.bl_cap, 0, bc.mpad, 0, bc.npad, nullptr, C,
+        if ((e = launch_contract<64, MODE_POINT>(bc.prof, bc.Bp, bc.npad, cs.Xcur, cs.bl_cap, 0, bc.mpad, 0, bc.npad, nullptr, C,
                                                  V, bc.n, bc.n, st)) != cudaSuccess) return e;
     }
     return cudaSuccess;

@@ -502,6 +502,19 @@ int lgs_imhk_counts_host(lgs_handle* h, int64_t* accepted, int64_t* total) {
     return LGS_OK;
 }
 
+int lgs_profile_enable(lgs_handle* h, int on) {
+    if (!h) return LGS_E_INVALID;
+    h->blocked.prof.on = on != 0;
+    return LGS_OK;
+}
+
+int lgs_profile_read(lgs_handle* h, double* ms_by_class, int64_t* launches_by_class) {
+    if (!h || !ms_by_class || !launches_by_class) return LGS_E_INVALID;
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    LGS_CUDA(h, blocked_profile_read(h->blocked, ms_by_class, launches_by_class, LGS_PROF_CLASSES));
+    return LGS_OK;
+}
+
 int lgs_histogram(lgs_handle* h, const double* V_dev, int64_t S, const int32_t* dims_host, int32_t n_dims, double lo,
                   double width, int32_t nbins, int64_t* hist_dev, void* stream) {
     if (!h) return LGS_E_INVALID;

@@ -71,8 +71,20 @@ struct BlockedWork {
     int64_t cap = 0;        // samples per batch, multiple of 128
 };
 
+// optional per-launch timing of the blocked path (lgs_profile_enable / lgs_profile_read)
+struct ProfRec {
+    int cls;
+    cudaEvent_t e0, e1;
+};
+struct Prof {
+    bool on = false;
+    std::vector<ProfRec> recs;
+    std::vector<cudaEvent_t> pool;  // recycled events
+};
+
 struct BlockedCtx {
     bool ready = false;
+    Prof prof;
     int n = 0, npad = 0, mpad = 0;     // npad: coordinates padded to 32; mpad: rows of B padded to 64
     double* Rp = nullptr;              // [npad][npad] R, identity on the padding
     double* Bp = nullptr;              // [mpad][npad] basis, zero padding
@@ -130,6 +142,7 @@ cudaError_t launch_reduce_counts(const ChainSet& cs, int64_t* out2, cudaStream_t
 // lgs_blocked.cu  (DMMA contractions + panel kernel)
 cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc);
 void blocked_free(BlockedCtx& bc);
+cudaError_t blocked_profile_read(BlockedCtx& bc, double* ms, int64_t* launches, int nclass);
 cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
                                  double* logq, cudaStream_t st);
 cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin,
