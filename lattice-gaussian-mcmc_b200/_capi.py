@@ -6,7 +6,8 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liblgs_b200.so")
+# LGS_B200_LIB: development override used by tools/ to A/B kernel variants; the default is the in-tree build
+LIB_PATH = os.environ.get("LGS_B200_LIB") or os.path.join(HERE, "liblgs_b200.so")
 
 LGS_OK = 0
 LGS_E_INVALID, LGS_E_CUDA, LGS_E_NOMEM, LGS_E_STATE, LGS_E_FALLBACK = -1, -2, -3, -4, -5

@@ -16,6 +16,7 @@
 #include "lgs_internal.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 namespace lgs {
@@ -52,16 +53,32 @@ __device__ __noinline__ double samplez_fast_call(double mean, double inv2s2, dou
     return (double)samplez_fast(mean, fz, u, zsum);
 }
 
+// One thread per sample.  The 32 coordinates of the block are walked in sub-blocks of kSub (upper first).  Only the
+// kSub running centers of the sub-block live in registers, in a ROTATING window: slot kSub-1 always holds the
+// coordinate being drawn, and the triangle update writes every slot one place up (c[j+1] = fma(T[j], x, c[j])), so the
+// coordinate loop is a rolled loop with a compact body (the fully unrolled form was 10k instructions per kernel and
+// stalled on instruction fetch) and the register budget allows 4-6 CTAs per SM -- the serial SampleZ chain is
+// latency-bound, warps in flight are what hides it.  Constants come from the kernel-parameter constant bank through
+// uniform loads: P.nrt row gi = [kSub shifted triangle entries (zero where the slot is empty) | rectangle entries for
+// the rows below the sub-block].  After a sub-block is drawn its contribution to the rows below goes through the
+// thread's own column of X (coalesced, L1/L2-resident).
+#ifndef LGS_PANEL_SUB
+#define LGS_PANEL_SUB 8
+#endif
+#ifndef LGS_PANEL_MINB
+#define LGS_PANEL_MINB 8
+#endif
+constexpr int kSub = LGS_PANEL_SUB;
+static_assert(kPB % kSub == 0, "sub-block width must divide the panel width");
+
 template <bool WANT_LZ>
-__global__ void __launch_bounds__(kPanelThreads)
+__global__ void __launch_bounds__(kPanelThreads, LGS_PANEL_MINB)
 klein_panel_kernel(const __grid_constant__ PanelParams P, double* __restrict__ X, int64_t ld, int i0, int64_t S,
                    uint64_t seed, uint64_t first_id, uint32_t tag, const int64_t* __restrict__ tag_dev, int first,
                    double* __restrict__ lp, double* __restrict__ d2, double* __restrict__ lz) {
     const int64_t s = (int64_t)blockIdx.x * kPanelThreads + threadIdx.x;
     if (s >= S) return;
-    double c[kPB];
-#pragma unroll
-    for (int k = 0; k < kPB; k++) c[k] = X[(size_t)(i0 + k) * ld + s];
+    double* __restrict__ Xs = X + (size_t)i0 * ld + s;
     double lpa = 0.0, d2a = 0.0, lza = 0.0;
     if (!first) {
         lpa = lp[s];
@@ -73,31 +90,55 @@ klein_panel_kernel(const __grid_constant__ PanelParams P, double* __restrict__ X
     const uint64_t id = first_id + (uint64_t)s;
     uint4 w = make_uint4(0, 0, 0, 0);
     int wpair = -1;
+#pragma unroll 1
+    for (int base = kPB - kSub; base >= 0; base -= kSub) {
+        double c[kSub];
 #pragma unroll
-    for (int i = kPB - 1; i >= 0; i--) {
-        const double mean = c[i] * P.inv_r[i];
-        double x;
-        if (P.mode[i]) {
-            x = rint(mean);
-        } else {
-            const int k = P.uidx[i];
-            if ((k >> 1) != wpair) {
-                wpair = k >> 1;
-                w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, tag);
+        for (int k = 0; k < kSub; k++) c[k] = Xs[(size_t)(base + k) * ld];
+#pragma unroll 1
+        for (int gi = base + kSub - 1; gi >= base; gi--) {
+            const double mean = c[kSub - 1] * P.inv_r[gi];
+            double x;
+            if (P.mode[gi]) {
+                x = rint(mean);
+            } else {
+                const int k = P.uidx[gi];
+                if ((k >> 1) != wpair) {
+                    wpair = k >> 1;
+                    w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, tag);
+                }
+                const double u = (k & 1) ? u53(w.z, w.w) : u53(w.x, w.y);
+                double zs;
+                x = samplez_fast_call(mean, P.inv2s2[gi], P.q[gi], P.sq[gi], P.znorm[gi], P.eps1[gi], P.kind[gi],
+                                      P.dmax[gi], u, &zs);
+                if (WANT_LZ) lza += log(zs);
             }
-            const double u = (k & 1) ? u53(w.z, w.w) : u53(w.x, w.y);
-            double zs;
-            x = samplez_fast_call(mean, P.inv2s2[i], P.q[i], P.sq[i], P.znorm[i], P.eps1[i], P.kind[i], P.dmax[i], u,
-                                  &zs);
-            if (WANT_LZ) lza += log(zs);
-        }
-        X[(size_t)(i0 + i) * ld + s] = x;
-        const double dl = x - mean;
-        const double dl2 = dl * dl;
-        lpa = fma(dl2, P.inv2s2[i], lpa);
-        d2a = fma(dl2, P.r2[i], d2a);
+            Xs[(size_t)gi * ld] = x;
+            const double dl = x - mean;
+            const double dl2 = dl * dl;
+            lpa = fma(dl2, P.inv2s2[gi], lpa);
+            d2a = fma(dl2, P.r2[gi], d2a);
+            const double* __restrict__ T = &P.nrt[gi * kPB];
 #pragma unroll
-        for (int k = 0; k < i; k++) c[k] = fma(P.nrt[i * kPB + k], x, c[k]);
+            for (int j = kSub - 2; j >= 0; j--) c[j + 1] = fma(T[j], x, c[j]);
+            c[0] = 0.0;
+        }
+        // contribution of this sub-block to the rows below it: rows [0, base) of the block, kSub at a time
+#pragma unroll 1
+        for (int r0 = 0; r0 < base; r0 += kSub) {
+            double a[kSub];
+#pragma unroll
+            for (int r = 0; r < kSub; r++) a[r] = Xs[(size_t)(r0 + r) * ld];
+#pragma unroll 1
+            for (int gj = base + kSub - 1; gj >= base; gj--) {
+                const double xj = Xs[(size_t)gj * ld];
+                const double* __restrict__ N = &P.nrt[gj * kPB + kSub + r0];
+#pragma unroll
+                for (int r = 0; r < kSub; r++) a[r] = fma(N[r], xj, a[r]);
+            }
+#pragma unroll
+            for (int r = 0; r < kSub; r++) Xs[(size_t)(r0 + r) * ld] = a[r];
+        }
     }
     lp[s] = lpa;
     d2[s] = d2a;
@@ -314,13 +355,14 @@ void blocked_free(BlockedCtx& bc) {
     cudaFree(bc.Rp);
     cudaFree(bc.Bp);
     cudaFree(bc.tp);
-    for (auto& w : bc.work) {
+    auto free_work = [](BlockedWork& w) {
         cudaFree(w.X);
         cudaFree(w.lp);
         cudaFree(w.d2);
         cudaFree(w.lz);
         w = BlockedWork{};
-    }
+    };
+    for (auto& w : bc.work) free_work(w);
     bc.Rp = bc.Bp = bc.tp = nullptr;
     bc.ready = false;
 }
@@ -350,7 +392,14 @@ cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc
         for (int i = 0; i < kPB; i++) {
             const int gi = i0 + i;
             if (gi < n) {
-                for (int k = 0; k < i; k++) P.nrt[i * kPB + k] = -d.R[(size_t)(i0 + k) * n + gi];
+                // row i of the packed constants (see klein_panel_kernel): slot j of the rotating window holds
+                // coordinate i - (kSub - 1) + j of the block while coordinate i is drawn
+                const int base = i / kSub * kSub;
+                for (int j = 0; j + 1 < kSub; j++) {
+                    const int k = i - (kSub - 1) + j;
+                    if (k >= base) P.nrt[i * kPB + j] = -d.R[(size_t)(i0 + k) * n + gi];
+                }
+                for (int r = 0; r < base; r++) P.nrt[i * kPB + kSub + r] = -d.R[(size_t)(i0 + r) * n + gi];
                 P.inv_r[i] = 1.0 / hc.rdiag[gi];
                 P.r2[i] = hc.rdiag[gi] * hc.rdiag[gi];
                 P.inv2s2[i] = hc.inv2s2[gi];
@@ -384,6 +433,13 @@ cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc
     LGS_SMEM_ATTR(32, MODE_ACCUM)
     LGS_SMEM_ATTR(64, MODE_POINT)
 #undef LGS_SMEM_ATTR
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&bc.sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (bc.sm_count <= 0) bc.sm_count = 148;
+        bc.wave = (int64_t)bc.sm_count * 2 * kBN;  // 37 888 samples on a 148-SM B200
+    }
     bc.ready = true;
     return cudaSuccess;
 }
@@ -445,30 +501,42 @@ static cudaError_t klein_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64
     return cudaSuccess;
 }
 
+// outputs of one finished batch held in w: lattice points, int64 coefficients, log-densities
+static cudaError_t klein_outputs(BlockedCtx& bc, BlockedWork& w, int64_t cnt, double* V, int64_t* X, double* logq,
+                                 cudaStream_t st) {
+    cudaError_t e;
+    if (V) {
+        if ((e = launch_contract<64, MODE_POINT>(bc.prof, bc.Bp, bc.npad, w.X, w.cap, 0, bc.mpad, 0, bc.npad, nullptr, cnt,
+                                                 V, bc.n, bc.n, st)) != cudaSuccess) return e;
+    }
+    if (X) {
+        ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+        dim3 grid((unsigned)((cnt + 31) / 32), (unsigned)((bc.n + 31) / 32));
+        export_coeffs_kernel<<<grid, 256, 0, st>>>(w.X, w.cap, bc.n, cnt, X);
+    }
+    if (logq) {
+        ProfScope ps2(bc.prof, LGS_PROF_OTHER, st);
+        finish_logq_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(w.lp, bc.sum_lognorm, cnt, logq);
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
                                  double* logq, cudaStream_t st) {
     if (S <= 0) return cudaSuccess;
-    const int64_t kMaxBatch = 1 << 17;
+    cudaError_t e;
+    const int n = bc.n;
+    // batches of up to four full waves of contraction tiles; a last partial wave of <= sm_count tiles runs one CTA
+    // per SM at twice the speed, so any S costs what its flops cost to within half a wave
+    const int64_t kMaxBatch = bc.wave * 4;
     int64_t cap = S < kMaxBatch ? (S + 127) / 128 * 128 : kMaxBatch;
     BlockedWork& w = bc.work[0];
-    cudaError_t e = ensure_work(bc, w, cap);
-    if (e != cudaSuccess) return e;
+    if ((e = ensure_work(bc, w, cap)) != cudaSuccess) return e;
     for (int64_t s0 = 0; s0 < S; s0 += w.cap) {
         const int64_t cnt = (S - s0) < w.cap ? (S - s0) : w.cap;
-        if ((e = klein_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, 0u, nullptr, false, st)) != cudaSuccess)
-            return e;
-        if (V) {
-            if ((e = launch_contract<64, MODE_POINT>(bc.prof, bc.Bp, bc.npad, w.X, w.cap, 0, bc.mpad, 0, bc.npad, nullptr, cnt,
-                                                     V + (size_t)s0 * bc.n, bc.n, bc.n, st)) != cudaSuccess) return e;
-        }
-        if (X) {
-            ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
-            dim3 grid((unsigned)((cnt + 31) / 32), (unsigned)((bc.n + 31) / 32));
-            export_coeffs_kernel<<<grid, 256, 0, st>>>(w.X, w.cap, bc.n, cnt, X + (size_t)s0 * bc.n);
-        }
-        ProfScope ps2(bc.prof, LGS_PROF_OTHER, st);
-        if (logq) finish_logq_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(w.lp, bc.sum_lognorm, cnt, logq + s0);
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if ((e = klein_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, 0u, nullptr, false, st)) != cudaSuccess) return e;
+        if ((e = klein_outputs(bc, w, cnt, V ? V + (size_t)s0 * n : nullptr, X ? X + (size_t)s0 * n : nullptr,
+                               logq ? logq + s0 : nullptr, st)) != cudaSuccess) return e;
     }
     return cudaSuccess;
 }

@@ -48,7 +48,7 @@ constexpr int kPB = 32;  // coordinates per panel-kernel block
 // Constants of one 32-coordinate block, passed by value as kernel parameters so that the in-block triangle of R
 // and the SampleZ constants are read from the constant bank (no shared-memory or global traffic in the serial loop).
 struct PanelParams {
-    double nrt[kPB * kPB];  // nrt[i*32 + k] = -R[i0+k][i0+i] for k < i: what drawing x_i subtracts from center k
+    double nrt[kPB * kPB];  // row i: [kSub shifted triangle entries | rectangle entries for the rows below the sub-block], see klein_panel_kernel
     double inv_r[kPB];      // 1 / R_ii
     double r2[kPB];         // R_ii^2                      (||Bx - c||^2 = sum r_ii^2 (x_i - m_i)^2)
     double inv2s2[kPB];     // 1 / (2 sigma_i^2)
@@ -92,7 +92,9 @@ struct BlockedCtx {
     double sum_lognorm = 0.0;          // sum_i 0.5 log(2 pi) + log sigma_i   (klein.py:262)
     double two_sigma2 = 0.0;
     std::vector<PanelParams> panels;   // npad / 32 blocks, index = i0 / 32
-    BlockedWork work[2];
+    BlockedWork work[2];               // [0] single-stream Klein batches, [1] IMHK proposals
+    int sm_count = 0;
+    int64_t wave = 0;                  // samples in one full wave of 64 x 128 contraction tiles (2 CTAs per SM)
 };
 
 // per-coordinate constants computed once on the host by lgs_create()

@@ -10,11 +10,12 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import __graft_entry__ as g  # noqa: E402
 
-g.build()
+g.build() if not os.environ.get("LGS_B200_LIB") else None
 import lattice_gaussian_mcmc_b200 as lgs  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
-S = 1 << (int(sys.argv[2]) if len(sys.argv) > 2 else 17)
+_a = int(sys.argv[2]) if len(sys.argv) > 2 else 17
+S = (1 << _a) if _a <= 40 else _a
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
 
 rng = np.random.RandomState(0)
@@ -41,3 +42,11 @@ for want_v in (True, False):
     flop = (3 * n * n - n) if want_v else n * (n - 1)
     print(f"n={n} S={S} want_v={want_v}: {ms:.2f} ms/batch  {S / ms * 1e3:.3e} samples/s  "
           f"{flop * S / ms * 1e-9:.2f} TFLOP/s algorithmic")
+
+eng.profile_enable(True)
+for r in range(reps):
+    eng.klein_sample_dev(S, 1, r * S, "fast", V=V.data_ptr(), stream=st)
+prof = eng.profile_read()
+eng.profile_enable(False)
+print("  per-batch ms by class:", {k: round(v[0] / reps, 3) for k, v in prof.items()}, "lib:",
+      os.environ.get("LGS_B200_LIB", "default"))
