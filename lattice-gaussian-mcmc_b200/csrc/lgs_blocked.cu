@@ -93,31 +93,43 @@ klein_panel_kernel(const __grid_constant__ PanelParams P, double* __restrict__ X
 #pragma unroll 1
     for (int base = kPB - kSub; base >= 0; base -= kSub) {
         double c[kSub];
+        {
+            const double* __restrict__ xl = Xs + (size_t)base * ld;
 #pragma unroll
-        for (int k = 0; k < kSub; k++) c[k] = Xs[(size_t)(base + k) * ld];
+            for (int k = 0; k < kSub; k++, xl += ld) c[k] = *xl;
+        }
+        double* __restrict__ xp = Xs + (size_t)(base + kSub - 1) * ld;  // row of the coordinate being drawn
 #pragma unroll 1
-        for (int gi = base + kSub - 1; gi >= base; gi--) {
-            const double mean = c[kSub - 1] * P.inv_r[gi];
+        for (int gi = base + kSub - 1; gi >= base; gi--, xp -= ld) {
+            const CoordConst& cc = P.cc[gi];
+            const int4 ci = P.ci[gi];
+            const double mean = c[kSub - 1] * cc.inv_r;
             double x;
-            if (P.mode[gi]) {
+            if (ci.w) {
                 x = rint(mean);
             } else {
-                const int k = P.uidx[gi];
-                if ((k >> 1) != wpair) {
-                    wpair = k >> 1;
+                if ((ci.z >> 1) != wpair) {
+                    wpair = ci.z >> 1;
                     w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, tag);
                 }
-                const double u = (k & 1) ? u53(w.z, w.w) : u53(w.x, w.y);
-                double zs;
-                x = samplez_fast_call(mean, P.inv2s2[gi], P.q[gi], P.sq[gi], P.znorm[gi], P.eps1[gi], P.kind[gi],
-                                      P.dmax[gi], u, &zs);
-                if (WANT_LZ) lza += log(zs);
+                const bool odd = ci.z & 1;
+                const double u = u53(odd ? w.z : w.x, odd ? w.w : w.y);
+                if (ci.x <= 1) {
+                    double logz;
+                    x = samplez_smooth<WANT_LZ>(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, cc.lognz, ci.x, ci.y, u,
+                                                &logz);
+                    if (WANT_LZ) lza += logz;
+                } else {
+                    double zs;
+                    x = samplez_fast_call(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, ci.x, ci.y, u, &zs);
+                    if (WANT_LZ) lza += log(zs);
+                }
             }
-            Xs[(size_t)gi * ld] = x;
+            *xp = x;
             const double dl = x - mean;
             const double dl2 = dl * dl;
-            lpa = fma(dl2, P.inv2s2[gi], lpa);
-            d2a = fma(dl2, P.r2[gi], d2a);
+            lpa = fma(dl2, cc.a, lpa);
+            d2a = fma(dl2, cc.r2, d2a);
             const double* __restrict__ T = &P.nrt[gi * kPB];
 #pragma unroll
             for (int j = kSub - 2; j >= 0; j--) c[j + 1] = fma(T[j], x, c[j]);
@@ -127,17 +139,19 @@ klein_panel_kernel(const __grid_constant__ PanelParams P, double* __restrict__ X
 #pragma unroll 1
         for (int r0 = 0; r0 < base; r0 += kSub) {
             double a[kSub];
+            double* __restrict__ xr = Xs + (size_t)r0 * ld;
 #pragma unroll
-            for (int r = 0; r < kSub; r++) a[r] = Xs[(size_t)(r0 + r) * ld];
+            for (int r = 0; r < kSub; r++) a[r] = xr[(size_t)r * ld];
+            const double* __restrict__ xj = Xs + (size_t)(base + kSub - 1) * ld;
+            const double* __restrict__ N = &P.nrt[(base + kSub - 1) * kPB + kSub + r0];
 #pragma unroll 1
-            for (int gj = base + kSub - 1; gj >= base; gj--) {
-                const double xj = Xs[(size_t)gj * ld];
-                const double* __restrict__ N = &P.nrt[gj * kPB + kSub + r0];
+            for (int j = 0; j < kSub; j++, xj -= ld, N -= kPB) {
+                const double xv = *xj;
 #pragma unroll
-                for (int r = 0; r < kSub; r++) a[r] = fma(N[r], xj, a[r]);
+                for (int r = 0; r < kSub; r++) a[r] = fma(N[r], xv, a[r]);
             }
 #pragma unroll
-            for (int r = 0; r < kSub; r++) Xs[(size_t)(r0 + r) * ld] = a[r];
+            for (int r = 0; r < kSub; r++) xr[(size_t)r * ld] = a[r];
         }
     }
     lp[s] = lpa;
@@ -400,20 +414,19 @@ cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc
                     if (k >= base) P.nrt[i * kPB + j] = -d.R[(size_t)(i0 + k) * n + gi];
                 }
                 for (int r = 0; r < base; r++) P.nrt[i * kPB + kSub + r] = -d.R[(size_t)(i0 + r) * n + gi];
-                P.inv_r[i] = 1.0 / hc.rdiag[gi];
-                P.r2[i] = hc.rdiag[gi] * hc.rdiag[gi];
-                P.inv2s2[i] = hc.inv2s2[gi];
-                P.q[i] = hc.q[gi];
-                P.sq[i] = hc.sq[gi];
-                P.znorm[i] = hc.znorm[gi];
-                P.eps1[i] = hc.eps1[gi];
-                P.kind[i] = hc.kind[gi];
-                P.dmax[i] = hc.dmax[gi];
-                P.uidx[i] = hc.uidx[gi];
-                P.mode[i] = hc.mode[gi];
+                CoordConst& cc = P.cc[i];
+                cc.inv_r = 1.0 / hc.rdiag[gi];
+                cc.r2 = hc.rdiag[gi] * hc.rdiag[gi];
+                cc.a = hc.inv2s2[gi];
+                cc.q = hc.q[gi];
+                cc.sq = hc.sq[gi];
+                cc.znorm = hc.znorm[gi];
+                cc.eps1 = hc.eps1[gi];
+                cc.lognz = std::log(hc.znorm[gi]);
+                P.ci[i] = make_int4(hc.kind[gi], hc.dmax[gi], hc.uidx[gi], hc.mode[gi]);
             } else {  // padding coordinate: center 0, R_ii = 1, rounded => x = 0, contributes nothing
-                P.inv_r[i] = 1.0;
-                P.mode[i] = 1;
+                P.cc[i].inv_r = 1.0;
+                P.ci[i] = make_int4(0, 0, 0, 1);
             }
         }
     }

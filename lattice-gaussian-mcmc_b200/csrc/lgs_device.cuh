@@ -266,4 +266,87 @@ __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, d
     return x - c.dmax;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Fast SampleZ, smooth regime (kind 0 / 1: sigma_i >= 1, full window): the same inverse transform as samplez_fast
+// (same ordering c0, c0+1, c0-1, ..., same one uniform), arranged for few instructions and short dependency chains:
+//   * weights in units of rho(c0), so only ratios are needed: with a = 1/(2 sigma_i^2), delta = c0 - mean,
+//       rho(c0 +- (d+1)) / rho(c0 +- d) = e^{-a} q^d E^{+-1},   E = e^{-2 a delta},  q = e^{-2a};
+//   * |2 a delta| <= a <= 1/2 here, so E and 1/E come from the even and odd parts of one Taylor polynomial
+//     (E = C + S, 1/E = C - S; truncation < 1e-16), with no range reduction, no division and no second exp;
+//   * the target u Z / rho(c0) = u sigma sqrt(2 pi) (1 + eps cos 2 pi delta) e^{a delta^2}, the last factor a
+//     degree-10 polynomial on [0, 1/8];
+//   * one branch per step of the outward walk (both sides are added, the side is decided after the exit).
+// log Z (for LGS_WEIGHT_EXACT) is lognz + eps cos(2 pi delta) to < 1e-16: no log call.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float cos2pi_half(float dl) {  // cos(2 pi dl), |dl| <= 1/2, abs. error ~1e-7
+    const float s2 = dl * dl;
+    float p = -2.1915353e-05f;
+    p = fmaf(p, s2, 4.6630281e-04f);
+    p = fmaf(p, s2, -7.3704309e-03f);
+    p = fmaf(p, s2, 8.2145887e-02f);
+    p = fmaf(p, s2, -0.59926453f);
+    p = fmaf(p, s2, 2.5501640f);
+    p = fmaf(p, s2, -5.1677128f);
+    p = fmaf(p, s2, 3.14159265f);
+    const float sn = p * dl;  // sin(pi dl)
+    return fmaf(-2.0f * sn, sn, 1.0f);
+}
+
+// Taylor coefficients in the constant bank: FP64 instructions take them as operands directly (an FP64 immediate
+// would cost two moves per use)
+static __constant__ double kEvenC[8] = {1.0, 0.5, 0.041666666666666664, 0.001388888888888889, 2.48015873015873e-05,
+                                        2.755731922398589e-07, 2.08767569878681e-09, 1.1470745597729725e-11};
+static __constant__ double kOddC[7] = {1.0, 0.16666666666666666, 0.008333333333333333, 0.0001984126984126984,
+                                       2.7557319223985893e-06, 2.505210838544172e-08, 1.6059043836821613e-10};
+static __constant__ double kExpC[11] = {1.0, 1.0, 0.5, 0.16666666666666666, 0.041666666666666664,
+                                        0.008333333333333333, 0.001388888888888889, 0.0001984126984126984,
+                                        2.48015873015873e-05, 2.7557319223985893e-06, 2.755731922398589e-07};
+
+template <bool WANT_LOGZ>
+__device__ __forceinline__ double samplez_smooth(double mean, double a, double q, double sq, double znorm, double eps1,
+                                                 double lognz, int kind, int dmax, double u, double* logz) {
+    const double c0 = rint(mean);
+    const double delta = c0 - mean;  // in [-1/2, 1/2]
+    const double ad = a * delta;
+    const double x = -2.0 * ad;      // E = e^x, |x| <= 1/2
+    const double y = x * x;
+    double C = kEvenC[7];
+#pragma unroll
+    for (int k = 6; k >= 0; k--) C = fma(C, y, kEvenC[k]);
+    double Sx = kOddC[6];
+#pragma unroll
+    for (int k = 5; k >= 0; k--) Sx = fma(Sx, y, kOddC[k]);
+    Sx *= x;
+    const double g = ad * delta;     // a delta^2 in [0, 1/8]
+    double G = kExpC[10];
+#pragma unroll
+    for (int k = 9; k >= 0; k--) G = fma(G, g, kExpC[k]);
+    double t = u * znorm;
+    if (WANT_LOGZ) *logz = lognz;
+    if (kind == 1) {
+        const double corr = eps1 * (double)cos2pi_half((float)delta);
+        t = fma(t, corr, t);
+        if (WANT_LOGZ) *logz = lognz + corr;
+    }
+    t *= G;
+    double ru = sq * (C + Sx), rd = sq * (C - Sx);
+    double vu = 1.0, vd = 1.0, cum = 1.0, cu = 2.0;
+    int d = 0;
+    if (!(t < 1.0)) {
+        // outward walk; leaving at d == dmax without t < cum means u Z lies beyond the accumulated mass (rounding,
+        // ~1e-16) and takes the last point visited, c0 - dmax, like samplez_fast
+        do {
+            d++;
+            vu *= ru;
+            vd *= rd;
+            cu = cum + vu;
+            cum = cu + vd;
+            ru *= q;
+            rd *= q;
+        } while (!(t < cum) && d < dmax);
+    }
+    const double sd = (double)d;
+    return (t < cu) ? c0 + sd : c0 - sd;   // d == 0: both are c0
+}
+
 }  // namespace lgs

@@ -47,19 +47,21 @@ constexpr int kPB = 32;  // coordinates per panel-kernel block
 
 // Constants of one 32-coordinate block, passed by value as kernel parameters so that the in-block triangle of R
 // and the SampleZ constants are read from the constant bank (no shared-memory or global traffic in the serial loop).
+struct CoordConst {  // 64 bytes of per-coordinate SampleZ / log-density constants
+    double inv_r;    // 1 / R_ii
+    double r2;       // R_ii^2                      (||Bx - c||^2 = sum r_ii^2 (x_i - m_i)^2)
+    double a;        // 1 / (2 sigma_i^2)
+    double q;        // exp(-1/sigma_i^2)
+    double sq;       // exp(-1/(2 sigma_i^2))
+    double znorm;    // sigma_i sqrt(2 pi)
+    double eps1;     // 2 exp(-2 pi^2 sigma_i^2)
+    double lognz;    // log(sigma_i sqrt(2 pi))
+};
 struct PanelParams {
     double nrt[kPB * kPB];  // row i: [kSub shifted triangle entries | rectangle entries for the rows below the sub-block], see klein_panel_kernel
-    double inv_r[kPB];      // 1 / R_ii
-    double r2[kPB];         // R_ii^2                      (||Bx - c||^2 = sum r_ii^2 (x_i - m_i)^2)
-    double inv2s2[kPB];     // 1 / (2 sigma_i^2)
-    double q[kPB];          // exp(-1/sigma_i^2)
-    double sq[kPB];         // exp(-1/(2 sigma_i^2))
-    double znorm[kPB];      // sigma_i sqrt(2 pi)
-    double eps1[kPB];       // 2 exp(-2 pi^2 sigma_i^2)
-    int kind[kPB];
-    int dmax[kPB];
-    int uidx[kPB];          // draw index of the coordinate in the reference's consumption order
-    unsigned char mode[kPB];  // 1 = round-to-mean coordinate (sigma_i < 1e-10, klein.py:201-204) or padding
+    CoordConst cc[kPB];
+    int4 ci[kPB];           // x = kind, y = dmax, z = draw index in the reference's consumption order,
+                            // w = 1 for a round-to-mean coordinate (sigma_i < 1e-10, klein.py:201-204) or padding
 };
 
 // one batch worth of device workspace for the blocked path

@@ -1,9 +1,8 @@
 #!/bin/bash
 # sweep the sub-batch pipelining knobs on the GPU box
 python -m pytest tests/test_gpu_blocked.py -x -q 2>&1 | tail -1
-for S in 17 151552; do
-for ns in 1 2 3 4; do
-for sub in 18944 37888 75776; do
-  echo "=== S=$S nstreams=$ns sub=$sub"
-  LGS_NSTREAMS=$ns LGS_SUBBATCH=$sub python tools/quick_klein.py 1024 $S 5 2>&1 | grep "want_v"
-done; done; done
+for cfg in "1 37888" "2 37888" "3 37888" "4 37888" "4 18944" "6 18944" "8 18944" "3 56832" "2 75776"; do
+  set -- $cfg
+  echo "=== nstreams=$1 sub=$2"
+  LGS_NSTREAMS=$1 LGS_SUBBATCH=$2 python tools/quick_klein.py 1024 151552 5 2>&1 | grep "want_v"
+done
