@@ -153,7 +153,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--log2-samples", type=int, default=17, help="Klein samples per GPU per step")
-    ap.add_argument("--log2-chains", type=int, default=16, help="IMHK chains per GPU")
+    ap.add_argument("--log2-chains", type=int, default=17, help="IMHK chains per GPU")
     ap.add_argument("--thin", type=int, default=10)
     ap.add_argument("--skip-imhk", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")

@@ -563,11 +563,14 @@ cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint6
 namespace {
 
 // imhk.py:102-124 + 156-174 for one chain per thread.  init != 0: _initialize_chain (no accept test, no count).
+// The accepted proposal is NOT copied anywhere: loc[ch] records that the chain's current state now lives in
+// proposal buffer `buf` (1 or 2).  A location pointing at this buffer from two steps ago was saved into Xcur by
+// imhk_materialize_kernel before the buffer was overwritten, so it is reset here.
 __global__ void __launch_bounds__(256)
 imhk_accept_kernel(int64_t C, const double* __restrict__ lp, const double* __restrict__ d2,
                    const double* __restrict__ lz, double sum_lognorm, double two_sigma2, int exact, int init,
                    uint64_t seed, uint64_t first_id, uint32_t tag, double* __restrict__ lw_cur,
-                   int64_t* __restrict__ counts, uint8_t* __restrict__ flags) {
+                   int64_t* __restrict__ counts, uint8_t* __restrict__ loc, int buf) {
     const int64_t ch = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (ch >= C) return;
     // log pi(x) - log q(x): base.py:133-144 minus klein.py:246-269, with ||Bx - c||^2 = sum r_ii^2 (x_i - m_i)^2
@@ -575,7 +578,7 @@ imhk_accept_kernel(int64_t C, const double* __restrict__ lp, const double* __res
     const double lw_prop = exact ? lz[ch] : (-d2[ch] / two_sigma2) - logq;
     if (init) {
         lw_cur[ch] = lw_prop;
-        flags[ch] = 1;
+        loc[ch] = (uint8_t)buf;
         return;
     }
     const double lw = lw_cur[ch];
@@ -587,26 +590,32 @@ imhk_accept_kernel(int64_t C, const double* __restrict__ lp, const double* __res
     if (acc) {
         counts[ch * 2] += 1;
         lw_cur[ch] = lw_prop;
+        loc[ch] = (uint8_t)buf;
+    } else if (loc[ch] == (uint8_t)buf) {
+        loc[ch] = 0;
     }
-    flags[ch] = acc ? 1 : 0;
 }
 
-// current_state <- proposal where accepted (imhk.py:169-171); coalesced along chains
+// current_state <- the proposal buffer that holds it (imhk.py:169-171, deferred), for the chains whose location is
+// in `which` (bit 0: buffer 1, bit 1: buffer 2); coalesced along chains.  Locations are reset by the caller
+// (imhk_accept_kernel for the buffer about to be reused, a memset after a full flush).
 __global__ void __launch_bounds__(256)
-imhk_commit_kernel(int64_t C, int npad, int64_t ld, const uint8_t* __restrict__ flags,
-                   const double* __restrict__ Xprop, double* __restrict__ Xcur) {
+imhk_materialize_kernel(int64_t C, int npad, int64_t ld, const uint8_t* __restrict__ loc, int which,
+                        const double* __restrict__ P1, const double* __restrict__ P2, double* __restrict__ Xcur) {
     const int64_t ch = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (ch >= C) return;
-    const bool a0 = flags[ch], a1 = (ch + 1 < C) && flags[ch + 1];
+    const int l0 = loc[ch], l1 = (ch + 1 < C) ? loc[ch + 1] : 0;
+    const bool a0 = l0 && ((which >> (l0 - 1)) & 1), a1 = l1 && ((which >> (l1 - 1)) & 1);
     if (!a0 && !a1) return;
+    const double* __restrict__ s0 = (l0 == 1) ? P1 : P2;
+    const double* __restrict__ s1 = (l1 == 1) ? P1 : P2;
     for (int i = blockIdx.y; i < npad; i += gridDim.y) {
         const size_t o = (size_t)i * ld + ch;
-        if (a0 && a1) {
-            *reinterpret_cast<double2*>(Xcur + o) = *reinterpret_cast<const double2*>(Xprop + o);
-        } else if (a0) {
-            Xcur[o] = Xprop[o];
+        if (a0 && a1 && s0 == s1) {
+            *reinterpret_cast<double2*>(Xcur + o) = *reinterpret_cast<const double2*>(s0 + o);
         } else {
-            Xcur[o + 1] = Xprop[o + 1];
+            if (a0) Xcur[o] = s0[o];
+            if (a1) Xcur[o + 1] = s1[o + 1];
         }
     }
 }
@@ -650,18 +659,31 @@ static cudaError_t ensure_blocked_chains(BlockedCtx& bc, ChainSet& cs) {
     return cudaSuccess;
 }
 
+// make Xcur hold every chain's current state (needed before it is read as a matrix: kept states, get_state)
+static cudaError_t imhk_flush(BlockedCtx& bc, ChainSet& cs, cudaStream_t st) {
+    const int64_t C = cs.chains;
+    if (!bc.work[1].X || !bc.work[2].X) return cudaSuccess;
+    ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+    dim3 cgrid((unsigned)((C / 2 + 255) / 256 + 1), (unsigned)(bc.npad < 64 ? bc.npad : 64));
+    imhk_materialize_kernel<<<cgrid, 256, 0, st>>>(C, bc.npad, cs.bl_cap, cs.flags, 3, bc.work[1].X, bc.work[2].X,
+                                                   cs.Xcur);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    return cudaMemsetAsync(cs.flags, 0, (size_t)cs.bl_cap, st);
+}
+
 cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin,
                                 int weight_mode, double* V, int64_t* X, cudaStream_t st) {
     const int64_t C = cs.chains;
     cudaError_t e;
     if ((e = ensure_blocked_chains(bc, cs)) != cudaSuccess) return e;
-    BlockedWork& w = bc.work[1];
-    if ((e = ensure_work(bc, w, cs.bl_cap)) != cudaSuccess) return e;
-    if (w.cap != cs.bl_cap) {  // the proposal and the state matrices share one leading dimension
-        BlockedWork fresh;
-        cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
-        w = fresh;
-        if ((e = ensure_work(bc, w, cs.bl_cap)) != cudaSuccess) return e;
+    for (int b = 1; b <= 2; b++) {  // the two proposal buffers share the state matrix's leading dimension
+        BlockedWork& w = bc.work[b];
+        if (w.cap != cs.bl_cap) {
+            cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
+            w = BlockedWork{};
+            if ((e = ensure_work(bc, w, cs.bl_cap)) != cudaSuccess) return e;
+        }
     }
     const int64_t ld = cs.bl_cap;
     const bool exact = weight_mode == LGS_WEIGHT_EXACT;
@@ -669,24 +691,32 @@ cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, i
     dim3 cgrid((unsigned)((C / 2 + 255) / 256 + 1), (unsigned)(bc.npad < 64 ? bc.npad : 64));
     auto one_step = [&](bool init) -> cudaError_t {
         const uint32_t tag = init ? 0u : (uint32_t)(++cs.bl_steps);
+        const int buf = 1 + (int)(cs.bl_steps & 1);  // proposal buffer of this step
+        BlockedWork& w = bc.work[buf];
+        {   // states still living in this buffer (accepted two steps ago, rejected since) move to Xcur first
+            ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+            imhk_materialize_kernel<<<cgrid, 256, 0, st>>>(C, bc.npad, ld, cs.flags, 1 << (buf - 1), bc.work[1].X,
+                                                           bc.work[2].X, cs.Xcur);
+        }
         cudaError_t er = klein_batch(bc, w, C, cs.seed, cs.first_id, tag, nullptr, exact, st);
         if (er != cudaSuccess) return er;
         ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
         imhk_accept_kernel<<<ablocks, 256, 0, st>>>(C, w.lp, w.d2, w.lz, bc.sum_lognorm, bc.two_sigma2, exact ? 1 : 0,
                                                     init ? 1 : 0, cs.seed, cs.first_id, tag, cs.logw, cs.counts,
-                                                    cs.flags);
-        imhk_commit_kernel<<<cgrid, 256, 0, st>>>(C, bc.npad, ld, cs.flags, w.X, cs.Xcur);
+                                                    cs.flags, buf);
         return cudaGetLastError();
     };
     if (!cs.bl_init) {
+        if ((e = cudaMemsetAsync(cs.flags, 0, (size_t)cs.bl_cap, st)) != cudaSuccess) return e;
         if ((e = one_step(true)) != cudaSuccess) return e;
         cs.bl_init = true;
     }
     const int64_t steps = burn_in + keep * thin;
     for (int64_t stp = 0; stp < steps; stp++) {
         if ((e = one_step(false)) != cudaSuccess) return e;
-        if (stp >= burn_in && (stp - burn_in + 1) % thin == 0) {
+        if (stp >= burn_in && (stp - burn_in + 1) % thin == 0 && (V || X)) {
             const int64_t kidx = (stp - burn_in + 1) / thin - 1;
+            if ((e = imhk_flush(bc, cs, st)) != cudaSuccess) return e;
             if (V) {
                 if ((e = launch_contract<64, MODE_POINT>(bc.prof, bc.Bp, bc.npad, cs.Xcur, ld, 0, bc.mpad, 0, bc.npad, nullptr,
                                                          C, V + (size_t)kidx * bc.n, keep * (int64_t)bc.n, bc.n,
@@ -709,6 +739,7 @@ cudaError_t launch_imhk_blocked_get_state(BlockedCtx& bc, ChainSet& cs, int64_t*
     cudaError_t e;
     if (counts && (e = cudaMemcpyAsync(counts, cs.counts, sizeof(int64_t) * 2 * C, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
     if (logw && (e = cudaMemcpyAsync(logw, cs.logw, sizeof(double) * C, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
+    if ((X || V) && (e = imhk_flush(bc, cs, st)) != cudaSuccess) return e;
     if (X) {
         dim3 grid((unsigned)((C + 31) / 32), (unsigned)((bc.n + 31) / 32));
         export_coeffs_strided_kernel<<<grid, 256, 0, st>>>(cs.Xcur, cs.bl_cap, bc.n, C, X, bc.n);

@@ -36,7 +36,7 @@ struct ChainSet {
     int state_path = 0;
     // blocked path: all chains step together; current coefficient vectors coordinate-major [npad][cap]
     double* Xcur = nullptr;
-    uint8_t* flags = nullptr;     // [cap] accept bit of the step in flight
+    uint8_t* flags = nullptr;     // [cap] where the current state of the chain lives: 0 = Xcur, 1 / 2 = proposal buffer 0 / 1
     int64_t bl_cap = 0;
     int64_t bl_steps = 0;         // steps performed so far by every chain (Philox stream index)
     bool bl_init = false;
@@ -94,7 +94,7 @@ struct BlockedCtx {
     double sum_lognorm = 0.0;          // sum_i 0.5 log(2 pi) + log sigma_i   (klein.py:262)
     double two_sigma2 = 0.0;
     std::vector<PanelParams> panels;   // npad / 32 blocks, index = i0 / 32
-    BlockedWork work[2];               // [0] single-stream Klein batches, [1] IMHK proposals
+    BlockedWork work[3];               // [0] Klein batches, [1] and [2] IMHK proposals of even / odd steps
     int sm_count = 0;
     int64_t wave = 0;                  // samples in one full wave of 64 x 128 contraction tiles (2 CTAs per SM)
 };
