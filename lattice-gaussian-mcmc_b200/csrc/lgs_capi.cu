@@ -199,6 +199,12 @@ void lgs_destroy(lgs_handle* h) {
     cudaFree(h->scratch.Xw);
     cudaFree(h->stage_dev);
     cudaFree(h->arena);
+    if (h->host_compute) cudaStreamDestroy(h->host_compute);
+    if (h->host_copy) cudaStreamDestroy(h->host_copy);
+    for (int i = 0; i < 2; i++) {
+        if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+        if (h->ev_free[i]) cudaEventDestroy(h->ev_free[i]);
+    }
     delete h;
 }
 
@@ -236,6 +242,10 @@ int lgs_klein_replay(lgs_handle* h, int64_t S, const double* U_dev, double* V_de
     return LGS_OK;
 }
 
+// Host-buffer Klein call.  The batch is cut into chunks; chunk k is computed on the compute stream into one of two
+// staging slots while chunk k-1 travels to the host on the copy stream, so the PCIe transfer (the larger cost:
+// 8n bytes per sample) hides the sampling.  Works with pageable host memory too (the copy then blocks the host, not
+// the device).
 static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uint64_t seed, uint64_t first_id,
                              int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host) {
     if (!h) return LGS_E_INVALID;
@@ -243,31 +253,61 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
     if (S == 0) return LGS_OK;
     LGS_CUDA(h, cudaSetDevice(h->device));
     const size_t n = h->n;
-    size_t bV = V_host ? align256(sizeof(double) * S * n) : 0;
-    size_t bX = X_host ? align256(sizeof(int64_t) * S * n) : 0;
-    size_t bq = logq_host ? align256(sizeof(double) * S) : 0;
-    size_t bU = U_host ? align256(sizeof(double) * S * h->ctx.ups) : 0;
-    size_t bf = 256;
-    int rc = ensure_stage(h, bV + bX + bq + bU + bf);
-    if (rc) return rc;
-    uint8_t* p = (uint8_t*)h->stage_dev;
-    double* dV = V_host ? (double*)p : nullptr; p += bV;
-    int64_t* dX = X_host ? (int64_t*)p : nullptr; p += bX;
-    double* dq = logq_host ? (double*)p : nullptr; p += bq;
-    double* dU = U_host ? (double*)p : nullptr; p += bU;
-    int32_t* dfb = (int32_t*)p;
-    if (U_host) {
-        LGS_CUDA(h, cudaMemcpy(dU, U_host, sizeof(double) * S * h->ctx.ups, cudaMemcpyHostToDevice));
-        rc = lgs_klein_replay(h, S, dU, dV, dX, dq, dfb, nullptr);
-    } else {
-        rc = lgs_klein_sample(h, S, seed, first_id, samplez, dV, dX, dq, nullptr);
+    const int ups = h->ctx.ups;
+    if (!h->host_compute) {
+        LGS_CUDA(h, cudaStreamCreateWithFlags(&h->host_compute, cudaStreamNonBlocking));
+        LGS_CUDA(h, cudaStreamCreateWithFlags(&h->host_copy, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) {
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
+        }
     }
+    // chunk = two full waves of contraction tiles on the blocked path (75 776 samples on a B200), else 64 Ki
+    int64_t chunk = h->blocked.ready && h->blocked.wave > 0 ? 2 * h->blocked.wave : (int64_t)65536;
+    if (chunk > S) chunk = S;
+    const size_t bV = V_host ? align256(sizeof(double) * chunk * n) : 0;
+    const size_t bX = X_host ? align256(sizeof(int64_t) * chunk * n) : 0;
+    const size_t bq = logq_host ? align256(sizeof(double) * chunk) : 0;
+    const size_t bU = U_host ? align256(sizeof(double) * chunk * ups) : 0;
+    const size_t slot = bV + bX + bq + bU;
+    int rc = ensure_stage(h, 2 * slot + 256);
     if (rc) return rc;
-    if (V_host) LGS_CUDA(h, cudaMemcpy(V_host, dV, sizeof(double) * S * n, cudaMemcpyDeviceToHost));
-    if (X_host) LGS_CUDA(h, cudaMemcpy(X_host, dX, sizeof(int64_t) * S * n, cudaMemcpyDeviceToHost));
-    if (logq_host) LGS_CUDA(h, cudaMemcpy(logq_host, dq, sizeof(double) * S, cudaMemcpyDeviceToHost));
-    if (fb_host && U_host) LGS_CUDA(h, cudaMemcpy(fb_host, dfb, sizeof(int32_t), cudaMemcpyDeviceToHost));
-    LGS_CUDA(h, cudaDeviceSynchronize());
+    int32_t* dfb = (int32_t*)((uint8_t*)h->stage_dev + 2 * slot);
+    cudaStream_t cs = h->host_compute, ps = h->host_copy;
+    if (U_host && fb_host) LGS_CUDA(h, cudaMemsetAsync(dfb, 0, sizeof(int32_t), cs));
+    int k = 0;
+    for (int64_t s0 = 0; s0 < S; s0 += chunk, k++) {
+        const int64_t cnt = (S - s0) < chunk ? (S - s0) : chunk;
+        const int b = k & 1;
+        uint8_t* p = (uint8_t*)h->stage_dev + b * slot;
+        double* dV = V_host ? (double*)p : nullptr; p += bV;
+        int64_t* dX = X_host ? (int64_t*)p : nullptr; p += bX;
+        double* dq = logq_host ? (double*)p : nullptr; p += bq;
+        double* dU = U_host ? (double*)p : nullptr;
+        if (k >= 2) LGS_CUDA(h, cudaStreamWaitEvent(cs, h->ev_free[b], 0));  // slot b has left for the host
+        if (U_host) {
+            LGS_CUDA(h, cudaMemcpyAsync(dU, U_host + (size_t)s0 * ups, sizeof(double) * cnt * ups,
+                                        cudaMemcpyHostToDevice, cs));
+            RngSpec rng{dU, ups, 0, 0};
+            // the fallback counter accumulates over chunks (no per-chunk reset)
+            LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, cnt, rng, LGS_SAMPLEZ_TABLE, dV, dX, dq,
+                                             fb_host ? dfb : nullptr, cs));
+        } else {
+            rc = lgs_klein_sample(h, cnt, seed, first_id + (uint64_t)s0, samplez, dV, dX, dq, cs);
+            if (rc) return rc;
+        }
+        LGS_CUDA(h, cudaEventRecord(h->ev_done[b], cs));
+        LGS_CUDA(h, cudaStreamWaitEvent(ps, h->ev_done[b], 0));
+        if (V_host) LGS_CUDA(h, cudaMemcpyAsync(V_host + (size_t)s0 * n, dV, sizeof(double) * cnt * n, cudaMemcpyDeviceToHost, ps));
+        if (X_host) LGS_CUDA(h, cudaMemcpyAsync(X_host + (size_t)s0 * n, dX, sizeof(int64_t) * cnt * n, cudaMemcpyDeviceToHost, ps));
+        if (logq_host) LGS_CUDA(h, cudaMemcpyAsync(logq_host + s0, dq, sizeof(double) * cnt, cudaMemcpyDeviceToHost, ps));
+        LGS_CUDA(h, cudaEventRecord(h->ev_free[b], ps));
+    }
+    LGS_CUDA(h, cudaStreamSynchronize(ps));
+    if (fb_host && U_host) {
+        LGS_CUDA(h, cudaMemcpyAsync(fb_host, dfb, sizeof(int32_t), cudaMemcpyDeviceToHost, cs));
+    }
+    LGS_CUDA(h, cudaStreamSynchronize(cs));
     return LGS_OK;
 }
 

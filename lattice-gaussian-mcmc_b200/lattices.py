@@ -113,3 +113,57 @@ def lattice_from_rows(rows: np.ndarray, name: str = "SimpleLattice") -> SimpleLa
     """Wrap a row-basis the way the reference's scripts do: the matrix is handed to the sampler unchanged
     (klein_scaling_analysis.py:175), i.e. the sampler then treats its columns as the basis."""
     return SimpleLattice(rows, name=name)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# LLL stand-in.  The reference reduces through Sage's Matrix.LLL() (fplll; src/lattices/reduction.py:103,
+# klein_scaling_analysis.py:95-108), which is not vendored and not installable here; no reference test stores a
+# reduced basis, so parity for the reduction itself is unpinned (SURVEY.md 8c).  This is a textbook floating-point
+# LLL on an exact integer row basis -- host setup for the n <= 64 configurations, not part of the sampling path.
+# ---------------------------------------------------------------------------------------------------------
+def lll_reduce(rows: np.ndarray, delta: float = 0.99, eta: float = 0.501) -> np.ndarray:
+    """LLL-reduce the ROWS of an integer matrix (Lenstra-Lenstra-Lovasz with parameters (delta, eta)).
+    The basis is kept in exact Python integers; Gram-Schmidt data in float64 (adequate for the n <= 64,
+    |entries| <= 50 inputs of the reference's scaling runs).  Returns the reduced row basis as float64."""
+    B = np.array(np.rint(np.asarray(rows, dtype=np.float64)), dtype=object)
+    n = B.shape[0]
+    Bf = np.array(B, dtype=np.float64)
+    Bs = np.zeros((n, B.shape[1]))
+    mu = np.zeros((n, n))
+    nrm = np.zeros(n)
+
+    def gso_row(k):
+        v = Bf[k].copy()
+        if k:
+            mu[k, :k] = (Bs[:k] @ Bf[k]) / nrm[:k]
+            v -= mu[k, :k] @ Bs[:k]
+        Bs[k] = v
+        nrm[k] = v @ v
+
+    gso_row(0)
+    k = 1
+    while k < n:
+        gso_row(k)
+        for j in range(k - 1, -1, -1):          # size reduction
+            if abs(mu[k, j]) > eta:
+                q = int(np.rint(mu[k, j]))
+                B[k] = B[k] - q * B[j]
+                Bf[k] = np.array(B[k], dtype=np.float64)
+                mu[k, :j] -= q * mu[j, :j]
+                mu[k, j] -= q
+        gso_row(k)
+        if nrm[k] >= (delta - mu[k, k - 1] ** 2) * nrm[k - 1]:   # Lovasz condition
+            k += 1
+        else:
+            B[[k, k - 1]] = B[[k - 1, k]]
+            Bf[[k, k - 1]] = Bf[[k - 1, k]]
+            k = max(k - 1, 1)
+            if k == 1:
+                gso_row(0)
+    return np.array(B, dtype=np.float64)
+
+
+def lll_lattice(n: int, seed: int | None = None, delta: float = 0.99) -> SimpleLattice:
+    """BASELINE config C2 / the n <= 64 points of C5: randint(0, 51) matrix with seed 0 + n
+    (klein_scaling_analysis.py:83-86), LLL-reduced by rows, handed to the sampler unchanged (ibid. :175)."""
+    return lattice_from_rows(lll_reduce(random_int_basis(n, seed), delta), name=f"LLL-reduced random lattice (n={n})")

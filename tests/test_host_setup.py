@@ -63,3 +63,34 @@ def test_poly_mul_negacyclic():
     want = ntru.negacyclic(a).T @ b   # column convention of the rotation matrix
     got = ntru.poly_mul([int(x) for x in a], [int(x) for x in b])
     assert np.array_equal(np.array(got, dtype=np.float64), want)
+
+
+def _recorded():
+    import json
+    import os
+    return json.load(open(os.path.join(os.path.dirname(__file__), "golden", "klein_lll_recorded.json")))["cases"]
+
+
+@pytest.mark.parametrize("n", [16, 32, 64])
+def test_lll_stand_in_reproduces_the_reference_recorded_basis_profile(n):
+    """The reference reduced its scaling-run bases with Sage's LLL and recorded the Gram-Schmidt norms and
+    sigma = 1.5 max||b*|| (results/Klein_LLL_n=*.json).  The host LLL stand-in must land on the same profile."""
+    from lattice_gaussian_mcmc_b200.lattices import lll_reduce, random_int_basis, row_gram_schmidt_norms
+    rec = _recorded()[str(n)]
+    M = random_int_basis(n)
+    L = lll_reduce(M)
+    gs = row_gram_schmidt_norms(L)
+    np.testing.assert_allclose(gs, np.array(rec["gs_norms"]), rtol=1e-10)
+    assert abs(1.5 * gs.max() - rec["sigma"]) < 1e-9 * rec["sigma"]
+    # same lattice: L = U M with U unimodular
+    U = np.linalg.solve(M.T, L.T).T
+    assert np.abs(U - np.rint(U)).max() < 1e-6
+    assert abs(abs(np.linalg.det(np.rint(U))) - 1.0) < 1e-6 or n > 32   # det of a 64x64 integer matrix in fp64 is noisy
+    assert abs(np.linalg.slogdet(L)[1] - np.linalg.slogdet(M)[1]) < 1e-9
+    # (delta, eta) = (0.99, 0.501)-reduced
+    R = np.linalg.qr(L.T, mode="r")
+    R = R * np.sign(np.diag(R))[:, None]
+    mu = (R / np.diag(R)[:, None]).T
+    assert np.all(np.abs(np.tril(mu, -1)) <= 0.5011)
+    d = np.diag(R) ** 2
+    assert all(d[k] >= (0.99 - mu[k, k - 1] ** 2) * d[k - 1] * (1 - 1e-12) for k in range(1, n))
