@@ -5,7 +5,7 @@
     python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithm (oracle port), rank 0 only
 
 One "step" of the Klein leg = one batch of 2^17 samples per GPU through the hot path (lgs_klein_sample: blocked fp64
-back-substitution + SampleZ + lattice points), output resident in HBM.  One step of the IMHK leg = 10 MH steps of 2^16
+back-substitution + SampleZ + lattice points), output resident in HBM.  One step of the IMHK leg = 10 MH steps of 2^17
 chains per GPU (lgs_imhk_run, thin = 10, the kept state written as a lattice point), followed by the NCCL all-reduce of
 the accept counters and marginal histograms.  Independent samples / chains are sharded over ranks by global id
 (Philox key = seed, counter = global id): no data-path collective, weak scaling.
@@ -120,7 +120,7 @@ def run_reference(args, rank, world):
     lat = build_lattice()
     cores = os.cpu_count() or 1
     prob = oracle.Problem(lat.basis, SIGMA)
-    S = 16 * cores                                                     # bounded sample per step
+    S = 256 * cores                                                    # bounded sample per step (~0.3 s)
     for w in range(args.warmup):
         oracle.klein_seeded(prob, cores, seed=100 + w, chains=cores, threads=cores)
     t0 = time.perf_counter()
@@ -286,24 +286,31 @@ def main():
             imhk_step(w)
         hist.zero_()
 
+        from lattice_gaussian_mcmc_b200 import distributed as D
+
         def imhk_all(k):
             imhk_step(k)
             if k == K - 1:                                # ... and all-reduce once at the end of the run (NCCL)
                 eng.imhk_state_dev(counts=counts.data_ptr(), stream=stream)
-                tot = counts.sum(dim=0)
-                if world > 1:
-                    dist.all_reduce(tot)
-                    dist.all_reduce(hist)
-                imhk_all.tot = tot
+                imhk_all.tot, imhk_all.hist = D.allreduce_stats(counts, hist)
         ms_imhk = timed(imhk_all, K)
         tot = imhk_all.tot.cpu().numpy()
         rate = world * C * thin * K / (ms_imhk * 1e-3)
+        # per-class device time of the same work (separate pass, events around every launch)
+        eng.profile_enable(True)
+        for k in range(2):
+            imhk_step(k)
+        iprof = eng.profile_read()
+        eng.profile_enable(False)
+        itot = max(sum(v[0] for v in iprof.values()), 1e-9)
         imhk = {"value": rate, "unit": "chain-steps/s", "chains_per_gpu": C, "thin": thin, "ms_per_step": ms_imhk / K,
-                "acceptance_rate": float(tot[0]) / max(float(tot[1]), 1.0),
+                "acceptance_rate": D.acceptance_rate(imhk_all.tot.cpu()),
                 "flop_per_chain_step": imhk_flop(thin),
                 "fp64_tflops_per_gpu": rate / world * imhk_flop(thin) * 1e-12,
                 "fp64_frac_of_peak": rate / world * imhk_flop(thin) * 1e-12 / peak,
-                "hist_total": int(hist.sum().item())}
+                "share_of_step": {k: round(v[0] / itot, 4) for k, v in iprof.items()},
+                "gpu_launches_per_step": sum(v[1] for v in iprof.values()) // 2,
+                "hist_total": int(imhk_all.hist.sum().item())}
 
     clk = clocks.stop(windows) if rank == 0 else None
     cpu = None
@@ -326,7 +333,11 @@ def main():
             "fp64_frac_of_peak": klein_rate / world * KLEIN_FLOP * 1e-12 / peak,
             "roofline": {"bound": "tensor", "kernel": "contract_kernel<64, MODE_POINT> (V = X B^T, fp64 DMMA)",
                          "achieved": pt_tf, "peak": peak, "unit": "TFLOP/s", "frac": pt_tf / peak,
-                         "peak_source": peak_src, "traffic": None,
+                         "peak_source": peak_src,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel per launch from the ncu
+                         # --set full capture of this command at S = 2^17 (profiles/r01b_ncu_full_summary.json):
+                         # 1.084 GB + 1.041 GB, against 2 * 8 n S = 2.147 GB of algorithmic X-read + V-write
+                         "traffic": 2.125e9 if (S == 1 << 17 and n == 1024) else None,
                          "algorithmic_flop_per_launch": pt_flop, "avg_launch_ms": pt_ms / pt_cnt,
                          "share_of_step": share},
             "gpu_launches": int(launches_per_step * K),

@@ -167,7 +167,10 @@ klein_panel_kernel(const __grid_constant__ PanelParams P, double* __restrict__ X
 // CTA tile BM x 128 samples, warps 32 x 32, k-tile 16, kStages-deep cp.async pipeline.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int MODE_PANEL = 0, MODE_ACCUM = 1, MODE_POINT = 2;
-constexpr int kBN = 128, kBK = 16, kStages = 4;
+#ifndef LGS_GEMM_STAGES
+#define LGS_GEMM_STAGES 4
+#endif
+constexpr int kBN = 128, kBK = 16, kStages = LGS_GEMM_STAGES;
 constexpr int kLdA = kBK + 4;   // 20 doubles: conflict-free LDS.64 for the A fragments (row stride = 4 mod 16)
 constexpr int kLdB = kBN + 4;   // 132 doubles: same for the B fragments
 

@@ -198,6 +198,7 @@ void lgs_destroy(lgs_handle* h) {
     blocked_free(h->blocked);
     cudaFree(h->scratch.Xw);
     cudaFree(h->stage_dev);
+    cudaFree(h->hist_dims);
     cudaFree(h->arena);
     if (h->host_compute) cudaStreamDestroy(h->host_compute);
     if (h->host_copy) cudaStreamDestroy(h->host_copy);
@@ -562,16 +563,14 @@ int lgs_histogram(lgs_handle* h, const double* V_dev, int64_t S, const int32_t* 
         return fail(h, LGS_E_INVALID, "lgs_histogram: bad arguments");
     for (int i = 0; i < n_dims; i++)
         if (dims_host[i] < 0 || dims_host[i] >= h->n) return fail(h, LGS_E_INVALID, "lgs_histogram: dim out of range");
+    if (n_dims > 256) return fail(h, LGS_E_INVALID, "lgs_histogram: at most 256 tracked coordinates");
     LGS_CUDA(h, cudaSetDevice(h->device));
-    int32_t* dims_dev = nullptr;
-    LGS_CUDA(h, cudaMalloc(&dims_dev, sizeof(int32_t) * n_dims));
-    cudaError_t e = cudaMemcpyAsync(dims_dev, dims_host, sizeof(int32_t) * n_dims, cudaMemcpyHostToDevice,
-                                    (cudaStream_t)stream);
-    if (e == cudaSuccess)
-        e = launch_histogram(h->ctx, V_dev, S, dims_dev, n_dims, lo, width, nbins, hist_dev, (cudaStream_t)stream);
-    cudaStreamSynchronize((cudaStream_t)stream);
-    cudaFree(dims_dev);
-    if (e != cudaSuccess) return cuda_fail(h, e, "lgs_histogram");
+    if (!h->hist_dims) LGS_CUDA(h, cudaMalloc(&h->hist_dims, sizeof(int32_t) * 256));
+    // stream-ordered, no host synchronisation: the tiny pageable copy is staged by the driver before it returns
+    LGS_CUDA(h, cudaMemcpyAsync(h->hist_dims, dims_host, sizeof(int32_t) * n_dims, cudaMemcpyHostToDevice,
+                                (cudaStream_t)stream));
+    LGS_CUDA(h, launch_histogram(h->ctx, V_dev, S, h->hist_dims, n_dims, lo, width, nbins, hist_dev,
+                                 (cudaStream_t)stream));
     return LGS_OK;
 }
 

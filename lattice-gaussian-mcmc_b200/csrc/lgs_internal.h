@@ -125,6 +125,7 @@ struct lgs_handle {
     // staging for the *_host entry points
     void* stage_dev = nullptr;
     size_t stage_cap = 0;
+    int32_t* hist_dims = nullptr;  // device copy of the tracked coordinates of the last lgs_histogram call
     cudaStream_t host_compute = nullptr, host_copy = nullptr;  // compute / transfer overlap of the *_host calls
     cudaEvent_t ev_done[2] = {}, ev_free[2] = {};
     std::string err;
