@@ -197,7 +197,8 @@ enum {
     LGS_PROF_ACCUM = 2,   /* contract_kernel, 32x32 in-pair update (DMMA) */
     LGS_PROF_POINT = 3,   /* contract_kernel, lattice points V = X B^T (DMMA) */
     LGS_PROF_OTHER = 4,   /* accept / commit / export / log-density finish */
-    LGS_PROF_CLASSES = 5
+    LGS_PROF_CHAIN = 5,   /* klein_chain_kernel: the persistent warp-specialised kernel (centers + panels + lattice points) */
+    LGS_PROF_CLASSES = 6
 };
 LGS_API int lgs_profile_enable(lgs_handle *h, int on);
 LGS_API int lgs_profile_read(lgs_handle *h, double *ms_by_class, int64_t *launches_by_class);

@@ -133,14 +133,14 @@ class Engine:
         return int(a.value), int(t.value)
 
     # ------------------------------------------------------------------ measurement hooks
-    PROF_CLASSES = ("panel", "centers", "accum", "point", "other")
+    PROF_CLASSES = ("panel", "centers", "accum", "point", "other", "chain")
 
     def profile_enable(self, on=True):
         check(self._h, self._lib.lgs_profile_enable(self._h, int(bool(on))))
 
     def profile_read(self):
-        ms = (ctypes.c_double * 5)()
-        cnt = (ctypes.c_int64 * 5)()
+        ms = (ctypes.c_double * len(self.PROF_CLASSES))()
+        cnt = (ctypes.c_int64 * len(self.PROF_CLASSES))()
         check(self._h, self._lib.lgs_profile_read(self._h, ms, cnt))
         return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(self.PROF_CLASSES)}
 

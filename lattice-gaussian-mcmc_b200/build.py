@@ -23,6 +23,7 @@ COMMON = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler",
 UNITS = [
     ("lgs_ordered.cu", ["-fmad=false"]),
     ("lgs_blocked.cu", []),
+    ("lgs_chain.cu", []),
     ("lgs_capi.cu", []),
 ]
 

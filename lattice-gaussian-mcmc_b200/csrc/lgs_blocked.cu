@@ -23,25 +23,6 @@ namespace lgs {
 
 namespace {
 
-// brackets one launch with events when profiling is on (class ids: LGS_PROF_* in include/lgs_b200.h)
-struct ProfScope {
-    Prof& p;
-    cudaStream_t st;
-    cudaEvent_t e1 = nullptr;
-    ProfScope(Prof& prof, int cls, cudaStream_t s) : p(prof), st(s) {
-        if (!p.on) return;
-        cudaEvent_t ev[2];
-        for (auto& e : ev) {
-            if (!p.pool.empty()) { e = p.pool.back(); p.pool.pop_back(); }
-            else cudaEventCreate(&e);
-        }
-        cudaEventRecord(ev[0], st);
-        e1 = ev[1];
-        p.recs.push_back(ProfRec{cls, ev[0], ev[1]});
-    }
-    ~ProfScope() { if (e1) cudaEventRecord(e1, st); }
-};
-
 // ---------------------------------------------------------------------------------------------------------
 // panel kernel
 // ---------------------------------------------------------------------------------------------------------
@@ -365,6 +346,7 @@ cudaError_t blocked_profile_read(BlockedCtx& bc, double* ms, int64_t* launches, 
 }
 
 void blocked_free(BlockedCtx& bc) {
+    chain_free(bc);
     for (auto& r : bc.prof.recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
     for (auto& e : bc.prof.pool) cudaEventDestroy(e);
     bc.prof.recs.clear();
@@ -456,6 +438,11 @@ cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc
         if (bc.sm_count <= 0) bc.sm_count = 148;
         bc.wave = (int64_t)bc.sm_count * 2 * kBN;  // 37 888 samples on a 148-SM B200
     }
+    {
+        const char* env = getenv("LGS_CHAIN");
+        bc.use_chain = env ? atoi(env) : 1;
+        if ((e = chain_init(bc, d, hc)) != cudaSuccess) return e;
+    }
     bc.ready = true;
     return cudaSuccess;
 }
@@ -540,6 +527,7 @@ static cudaError_t klein_outputs(BlockedCtx& bc, BlockedWork& w, int64_t cnt, do
 cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
                                  double* logq, cudaStream_t st) {
     if (S <= 0) return cudaSuccess;
+    if (bc.use_chain && bc.chain.ready) return launch_klein_chain(bc, S, seed, first_id, V, X, logq, st);
     cudaError_t e;
     const int n = bc.n;
     // batches of up to four full waves of contraction tiles; a last partial wave of <= sm_count tiles runs one CTA

@@ -1,0 +1,782 @@
+// Chain kernel: the whole Klein sampler (klein.py:181-220) for a batch of samples in ONE persistent,
+// warp-specialised kernel, one CTA per SM.
+//
+// A CTA owns sample tiles of 128 samples from their first coordinate to their lattice point.  Roles:
+//   * 8 DMMA warps (two warpgroups): consume a ring of shared-memory stages, each a 64 x 16 sliver of R (or of the
+//     basis) and the matching 16 x 128 sliver of the tile's coefficient matrix, with mma.sync m16n8k8 f64; the
+//     epilogue writes the centers of a 64-coordinate block pair (t - R[rows, done] X[done, tile]) or 64 rows of
+//     the tile's lattice points;
+//   * 1 producer warp: fills the ring with bulk asynchronous copies (cp.async.bulk = the TMA engine, completion on
+//     an mbarrier) and is the scheduler: it hands the DMMA warps the next ready work item -- centers of a tile whose
+//     panel warps have finished the pair above (priority), else 64 rows of lattice points of a finished tile;
+//   * 3 panel warpgroups, one tile each: one thread per sample walks the 64 coordinates of a pair serially
+//     (conditional mean -> Philox -> SampleZ -> log-density terms -> in-pair triangle update), then hands the tile
+//     back to the scheduler.
+// While a tile is in its serial panel phase the DMMA warps work for the other tiles, so the FP64 tensor pipe stays
+// busy; registers are moved from the producer / panel warpgroups to the DMMA warpgroups with setmaxnreg.
+//
+// HBM layout of the coefficient workspace ("tiled"): Xt[tile][coordinate][132], 128 samples + 4 doubles of padding
+// per row, so that a 16-coordinate sliver of a tile is one contiguous 16 896-byte bulk copy whose shared-memory
+// image already has the conflict-free row stride of the B fragments.  R and the basis are pre-packed once per
+// sampler into the shared-memory image of their 64 x 16 slivers (row stride 20 doubles).
+#include "lgs_internal.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+namespace lgs {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(smem_u32(b)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(smem_u32(b)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+    while (!mbar_try_wait(b, parity)) {
+    }
+}
+// bulk asynchronous copy global -> shared (TMA engine), completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* b) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(b))
+                 : "memory");
+}
+// orders this thread's generic-proxy writes before later async-proxy (bulk copy) reads of the same memory
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void dmma_16x8x8(double (&d)[4], const double (&a)[4], const double (&b)[2]) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+        : "+d"(d[0]), "+d"(d[1]), "+d"(d[2]), "+d"(d[3])
+        : "d"(a[0]), "d"(a[1]), "d"(a[2]), "d"(a[3]), "d"(b[0]), "d"(b[1]));
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// geometry
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kTile = 128;            // samples per tile
+constexpr int kRowLd = kChainRowLd;   // 132: doubles per coordinate row of a tile in HBM and in shared memory
+constexpr int kPair = 64;             // coordinates per work item (a pair of 32-blocks of the v1 path)
+constexpr int kBK = 16;               // contraction depth of one stage
+constexpr int kLdA = kBK + 4;         // 20: row stride of an A sliver (conflict-free LDS.64 fragment loads)
+constexpr int kSubW = 8;              // coordinates per sub-block of the panel (width of the register window)
+#ifndef LGS_CHAIN_STAGES
+#define LGS_CHAIN_STAGES 6
+#endif
+constexpr int kStages = LGS_CHAIN_STAGES;
+constexpr int kSlots = 3;             // tiles in flight per CTA = panel warpgroups
+constexpr int kDmmaThreads = 256, kProdThreads = 128, kPanelThreads = kSlots * 128;
+constexpr int kThreads = kDmmaThreads + kProdThreads + kPanelThreads;  // 768
+constexpr int kRegsDmma = 120, kRegsProd = 24, kRegsPanel = 72;        // 768 x 80 at launch, rebalanced
+constexpr uint32_t kABytes = kPair * kLdA * 8;   // 10 240
+constexpr uint32_t kBBytes = kBK * kRowLd * 8;   // 16 896
+
+// F_NODATA: a stage without operand bytes (the top pair has nothing above it: its centers are t itself);
+// F_NOSTORE: no epilogue stores, only the cready signal (wakes a panel warpgroup that has no tile left)
+enum : int { F_FIRST = 1, F_LAST = 2, F_POINT = 4, F_NOSTORE = 8, F_EXIT = 16, F_NODATA = 32 };
+
+struct StageHdr {
+    int flags;
+    int slot;      // centers items: whose tile this is (cready[slot] is signalled by the epilogue)
+    int r0;        // first row of the 64-row block
+    int tile;
+};
+
+struct ChainSmem {
+    double A[kStages][kPair][kLdA];
+    double B[kStages][kBK][kRowLd];
+    SubPack sub[kSlots][2];            // double-buffered constants of the sub-block being drawn
+    double xs[kSlots][kSubW][kTile];   // the sub-block's draws, for the update of the rows below
+    StageHdr hdr[kStages];
+    uint64_t full[kStages], empty[kStages];
+    uint64_t cready[kSlots], pdone[kSlots], cfull[kSlots][2];
+    int slot_tile[kSlots];
+};
+
+struct ChainArgs {
+    const double* Rpk;      // packed slivers of R: [npad/64][npad/16][64][20]
+    const double* Bpk;      // packed slivers of the basis, same shape
+    const double* tvec;     // [npad]
+    const SubPack* subs;    // [npad/8] sub-block constants, index = first coordinate / 8
+    double* Xt;             // tiled coefficient workspace
+    double* lp;             // [cap] per-sample accumulators (outputs)
+    double* d2;
+    double* lz;
+    double* V;              // lattice points [S][ldv] or nullptr
+    int64_t ldv;
+    int64_t S;
+    int npad;               // multiple of 64
+    int n_valid;            // n
+    int ntiles;
+    int want_lz;
+    uint64_t seed, first_id;
+    uint32_t tag;
+    unsigned long long* stats;  // development counters (LGS_CHAIN_STATS=1), 8 per CTA, or nullptr
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// DMMA warps: consume stages until the producer sends F_EXIT
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int wm = warp >> 2, wn = warp & 3;
+    const int g = lane >> 2, t = lane & 3;
+    double acc[2][4][4];
+    uint32_t it = 0;
+    const bool rec = P.stats && tid == 0;
+    long long t_wait = 0;
+    const long long t_begin = rec ? clock64() : 0;
+    for (;; it++) {
+        const int stage = it % kStages;
+        if (rec) {
+            const long long t0 = clock64();
+            mbar_wait(&sm.full[stage], (it / kStages) & 1);
+            t_wait += clock64() - t0;
+        } else {
+            mbar_wait(&sm.full[stage], (it / kStages) & 1);
+        }
+        const StageHdr h = sm.hdr[stage];
+        if (h.flags & F_EXIT) break;
+        if (h.flags & F_FIRST) {
+#pragma unroll
+            for (int a = 0; a < 2; a++)
+#pragma unroll
+                for (int b = 0; b < 4; b++)
+#pragma unroll
+                    for (int c = 0; c < 4; c++) acc[a][b][c] = 0.0;
+        }
+        {
+            if (!(h.flags & F_NODATA)) {
+#pragma unroll
+                for (int kk = 0; kk < kBK; kk += 8) {
+                    double af[2][4], bf[4][2];
+#pragma unroll
+                    for (int mt = 0; mt < 2; mt++) {
+                        const double* ap = &sm.A[stage][wm * 32 + mt * 16 + g][kk + t];
+                        af[mt][0] = ap[0];
+                        af[mt][1] = ap[8 * kLdA];
+                        af[mt][2] = ap[4];
+                        af[mt][3] = ap[8 * kLdA + 4];
+                    }
+#pragma unroll
+                    for (int nt = 0; nt < 4; nt++) {
+                        const double* bp = &sm.B[stage][kk + t][wn * 32 + nt * 8 + g];
+                        bf[nt][0] = bp[0];
+                        bf[nt][1] = bp[4 * kRowLd];
+                    }
+#pragma unroll
+                    for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                        for (int nt = 0; nt < 4; nt++) dmma_16x8x8(acc[mt][nt], af[mt], bf[nt]);
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[stage]);
+        if (!(h.flags & F_LAST)) continue;
+        if (!(h.flags & F_NOSTORE)) {
+            // fragment (mt, nt): rows g / g+8 of the 16-row tile, columns 2t, 2t+1 of the 8-column tile
+            if (h.flags & F_POINT) {
+                const int64_t s0 = (int64_t)h.tile * kTile;
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++) {
+                        const int row = h.r0 + wm * 32 + mt * 16 + g + hh * 8;
+                        if (row >= P.n_valid) continue;
+#pragma unroll
+                        for (int nt = 0; nt < 4; nt++) {
+                            const int64_t col = s0 + wn * 32 + nt * 8 + t * 2;
+                            if (col < P.S) P.V[(size_t)col * P.ldv + row] = acc[mt][nt][hh * 2];
+                            if (col + 1 < P.S) P.V[(size_t)(col + 1) * P.ldv + row] = acc[mt][nt][hh * 2 + 1];
+                        }
+                    }
+            } else {
+                double* xt = P.Xt + (size_t)h.tile * P.npad * kRowLd;
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++) {
+                        const int row = h.r0 + wm * 32 + mt * 16 + g + hh * 8;
+                        const double tv = P.tvec[row];
+#pragma unroll
+                        for (int nt = 0; nt < 4; nt++) {
+                            const int col = wn * 32 + nt * 8 + t * 2;
+                            double2 o;
+                            o.x = tv - acc[mt][nt][hh * 2];
+                            o.y = tv - acc[mt][nt][hh * 2 + 1];
+                            *reinterpret_cast<double2*>(xt + (size_t)row * kRowLd + col) = o;
+                        }
+                    }
+            }
+        }
+        if (!(h.flags & F_POINT)) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.cready[h.slot]);
+        }
+    }
+    if (rec) {
+        P.stats[blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - t_begin);
+        P.stats[blockIdx.x * 8 + 1] = (unsigned long long)t_wait;
+        P.stats[blockIdx.x * 8 + 2] = it;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// producer / scheduler: one thread
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P) {
+    const int G = gridDim.x;
+    const int npairs = P.npad / kPair;
+    const int nkt = P.npad / kBK;
+    uint32_t it = 0;
+    long long t_empty = 0, t_idle = 0;
+    const bool rec = P.stats != nullptr;
+    auto push = [&](int flags, int slot, int r0, int tile, const double* asrc, const double* bsrc) {
+        const int stage = it % kStages;
+        if (rec) {
+            const long long t0 = clock64();
+            mbar_wait(&sm.empty[stage], ((it / kStages) & 1) ^ 1);
+            t_empty += clock64() - t0;
+        } else {
+            mbar_wait(&sm.empty[stage], ((it / kStages) & 1) ^ 1);
+        }
+        sm.hdr[stage] = StageHdr{flags, slot, r0, tile};
+        if (flags & (F_NODATA | F_EXIT)) {
+            mbar_arrive(&sm.full[stage]);
+        } else {
+            mbar_arrive_expect_tx(&sm.full[stage], kABytes + kBBytes);
+            bulk_g2s(&sm.A[stage][0][0], asrc, kABytes, &sm.full[stage]);
+            bulk_g2s(&sm.B[stage][0][0], bsrc, kBBytes, &sm.full[stage]);
+        }
+        it++;
+    };
+    // centers of pair p (0 = top) of a tile: rows [lo, lo + 64) against every coordinate above them
+    auto issue_centers = [&](int slot, int p, int tile) {
+        const int lo = P.npad - kPair * (p + 1);
+        if (p == 0) {
+            push(F_FIRST | F_LAST | F_NODATA, slot, lo, tile, nullptr, nullptr);
+            return;
+        }
+        const int rt = lo / kPair;
+        const int kt0 = (lo + kPair) / kBK;
+        const double* a = P.Rpk + ((size_t)rt * nkt + kt0) * (kPair * kLdA);
+        const double* b = P.Xt + (size_t)tile * P.npad * kRowLd + (size_t)kt0 * kBK * kRowLd;
+        for (int kt = kt0; kt < nkt; kt++, a += kPair * kLdA, b += kBK * kRowLd)
+            push((kt == kt0 ? F_FIRST : 0) | (kt == nkt - 1 ? F_LAST : 0), slot, lo, tile, a, b);
+    };
+    // 64 rows of the lattice points of a finished tile
+    auto issue_point = [&](int tile, int rt) {
+        const double* a = P.Bpk + (size_t)rt * nkt * (kPair * kLdA);
+        const double* b = P.Xt + (size_t)tile * P.npad * kRowLd;
+        for (int kt = 0; kt < nkt; kt++, a += kPair * kLdA, b += kBK * kRowLd)
+            push(F_POINT | (kt == 0 ? F_FIRST : 0) | (kt == nkt - 1 ? F_LAST : 0), 0, rt * kPair, tile, a, b);
+    };
+
+    int next_tile = blockIdx.x;
+    int s_pair[kSlots], s_tile[kSlots];
+    uint32_t pd_par[kSlots];
+    bool s_active[kSlots];
+    int n_active = 0;
+    auto assign = [&](int s) {
+        if (next_tile < P.ntiles) {
+            s_tile[s] = next_tile;
+            next_tile += G;
+            s_pair[s] = 1;
+            sm.slot_tile[s] = s_tile[s];
+            issue_centers(s, 0, s_tile[s]);
+        } else {
+            s_active[s] = false;
+            n_active--;
+            sm.slot_tile[s] = -1;
+            push(F_FIRST | F_LAST | F_NODATA | F_NOSTORE, s, 0, -1, nullptr, nullptr);
+        }
+    };
+    for (int s = 0; s < kSlots; s++) {
+        pd_par[s] = 0;
+        s_active[s] = true;
+        n_active++;
+        assign(s);
+    }
+    // finished tiles whose lattice points are still to be contracted (filler work for the DMMA warps)
+    constexpr int kQ = 32;
+    int pq[kQ];
+    int pq_head = 0, pq_cnt = 0, pq_rt = 0;
+    int rr = 0;
+    for (;;) {
+        bool progressed = false;
+        if (pq_cnt < kQ) {
+            for (int i = 0; i < kSlots; i++) {
+                const int s = (rr + i) % kSlots;
+                if (!s_active[s] || !mbar_test_wait(&sm.pdone[s], pd_par[s])) continue;
+                pd_par[s] ^= 1;
+                if (s_pair[s] == npairs) {
+                    if (P.V) { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
+                    assign(s);
+                } else {
+                    issue_centers(s, s_pair[s], s_tile[s]);
+                    s_pair[s]++;
+                }
+                rr = s + 1;
+                progressed = true;
+                break;
+            }
+        }
+        if (progressed) continue;
+        if (pq_cnt > 0) {
+            issue_point(pq[pq_head], pq_rt);
+            if (++pq_rt == npairs) {
+                pq_rt = 0;
+                pq_head = (pq_head + 1) % kQ;
+                pq_cnt--;
+            }
+            continue;
+        }
+        if (n_active == 0) break;
+        if (rec) {
+            const long long t0 = clock64();
+            __nanosleep(200);
+            t_idle += clock64() - t0;
+        } else {
+            __nanosleep(200);
+        }
+    }
+    push(F_EXIT, 0, 0, -1, nullptr, nullptr);
+    if (rec) {
+        P.stats[blockIdx.x * 8 + 3] = (unsigned long long)t_empty;
+        P.stats[blockIdx.x * 8 + 4] = (unsigned long long)t_idle;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// panel warpgroup: one thread per sample of the slot's tile
+// ---------------------------------------------------------------------------------------------------------
+__device__ __noinline__ double chain_samplez_fast_call(double mean, double inv2s2, double q, double sq, double znorm,
+                                                       double eps1, int kind, int dmax, double u, double* zsum) {
+    FastZ fz{inv2s2, q, sq, znorm, eps1, kind, dmax};
+    return (double)samplez_fast(mean, fz, u, zsum);
+}
+
+template <bool WANT_LZ>
+__device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, const int slot) {
+    const int sl = (threadIdx.x - (kDmmaThreads + kProdThreads)) & 127;
+    const int lane = threadIdx.x & 31;
+    const int npairs = P.npad / kPair;
+    const int nsub = P.npad / kSubW;
+    const Philox gen(P.seed);
+    double* __restrict__ xs = &sm.xs[slot][0][sl];
+    uint32_t cr_par = 0, q = 0;
+    const bool rec = P.stats && slot == 0 && sl == 0;
+    long long t_cwait = 0;
+    const long long t_begin = rec ? clock64() : 0;
+    for (;;) {
+        mbar_wait(&sm.cready[slot], cr_par);
+        cr_par ^= 1;
+        const int tile = sm.slot_tile[slot];
+        if (tile < 0) break;
+        if (sl == 0) {
+            mbar_arrive_expect_tx(&sm.cfull[slot][q & 1], (uint32_t)sizeof(SubPack));
+            bulk_g2s(&sm.sub[slot][q & 1], &P.subs[nsub - 1], (uint32_t)sizeof(SubPack), &sm.cfull[slot][q & 1]);
+        }
+        const int64_t s = (int64_t)tile * kTile + sl;
+        const uint64_t id = P.first_id + (uint64_t)s;
+        double* __restrict__ xt = P.Xt + (size_t)tile * P.npad * kRowLd + sl;
+        double lpa = 0.0, d2a = 0.0, lza = 0.0;
+        uint4 w = make_uint4(0, 0, 0, 0);
+        int wpair = -1;
+#pragma unroll 1
+        for (int p = 0; p < npairs; p++) {
+            if (p > 0) {
+                const long long t0 = rec ? clock64() : 0;
+                mbar_wait(&sm.cready[slot], cr_par);
+                if (rec) t_cwait += clock64() - t0;
+                cr_par ^= 1;
+            }
+            const int lo = P.npad - kPair * (p + 1);
+            double c[kSubW];
+            {
+                const double* xl = xt + (size_t)(lo + kPair - kSubW) * kRowLd;
+#pragma unroll
+                for (int k = 0; k < kSubW; k++) c[k] = __ldcg(xl + (size_t)k * kRowLd);
+            }
+#pragma unroll 1
+            for (int base = kPair - kSubW; base >= 0; base -= kSubW) {
+                const int gsub = (lo + base) / kSubW;
+                const int buf = q & 1;
+                mbar_wait(&sm.cfull[slot][buf], (q >> 1) & 1);
+                named_bar_sync(1 + slot, 128);  // the whole warpgroup has left the other buffer
+                if (sl == 0 && gsub > 0) {
+                    mbar_arrive_expect_tx(&sm.cfull[slot][buf ^ 1], (uint32_t)sizeof(SubPack));
+                    bulk_g2s(&sm.sub[slot][buf ^ 1], &P.subs[gsub - 1], (uint32_t)sizeof(SubPack),
+                             &sm.cfull[slot][buf ^ 1]);
+                }
+                q++;
+                const SubPack& sp = sm.sub[slot][buf];
+                double* __restrict__ xp = xt + (size_t)(lo + base + kSubW - 1) * kRowLd;
+#pragma unroll 1
+                for (int j = kSubW - 1; j >= 0; j--, xp -= kRowLd) {
+                    const CoordConst cc = sp.cc[j];
+                    const int4 ci = sp.ci[j];
+                    const double mean = c[kSubW - 1] * cc.inv_r;
+                    double x;
+                    if (ci.w) {
+                        x = rint(mean);
+                    } else {
+                        if ((ci.z >> 1) != wpair) {
+                            wpair = ci.z >> 1;
+                            w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, P.tag);
+                        }
+                        const bool odd = ci.z & 1;
+                        const double u = u53(odd ? w.z : w.x, odd ? w.w : w.y);
+                        if (ci.x <= 1) {
+                            double logz;
+                            x = samplez_smooth<WANT_LZ>(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, cc.lognz, ci.x, ci.y,
+                                                        u, &logz);
+                            if (WANT_LZ) lza += logz;
+                        } else {
+                            double zs;
+                            x = chain_samplez_fast_call(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, ci.x, ci.y, u, &zs);
+                            if (WANT_LZ) lza += log(zs);
+                        }
+                    }
+                    *xp = x;
+                    xs[j * kTile] = x;
+                    const double dl = x - mean;
+                    const double dl2 = dl * dl;
+                    lpa = fma(dl2, cc.a, lpa);
+                    d2a = fma(dl2, cc.r2, d2a);
+                    const double* __restrict__ T = sp.nrt[j];
+#pragma unroll
+                    for (int jj = kSubW - 2; jj >= 0; jj--) c[jj + 1] = fma(T[jj], x, c[jj]);
+                    c[0] = 0.0;
+                }
+                // contribution of this sub-block to the rows below it (rows [0, base) of the pair), 8 at a time; the
+                // last group is the next sub-block: it stays in registers as the next window
+#pragma unroll 1
+                for (int r0 = 0; r0 < base - kSubW; r0 += kSubW) {
+                    double a[kSubW];
+                    double* __restrict__ xr = xt + (size_t)(lo + r0) * kRowLd;
+#pragma unroll
+                    for (int r = 0; r < kSubW; r++) a[r] = __ldcg(xr + (size_t)r * kRowLd);
+#pragma unroll 1
+                    for (int j = 0; j < kSubW; j++) {
+                        const double xv = xs[j * kTile];
+                        const double* __restrict__ N = &sp.nrt[j][kSubW + r0];
+#pragma unroll
+                        for (int r = 0; r < kSubW; r++) a[r] = fma(N[r], xv, a[r]);
+                    }
+#pragma unroll
+                    for (int r = 0; r < kSubW; r++) xr[(size_t)r * kRowLd] = a[r];
+                }
+                if (base > 0) {
+                    const int r0 = base - kSubW;
+                    const double* __restrict__ xr = xt + (size_t)(lo + r0) * kRowLd;
+#pragma unroll
+                    for (int r = 0; r < kSubW; r++) c[r] = __ldcg(xr + (size_t)r * kRowLd);
+#pragma unroll 1
+                    for (int j = 0; j < kSubW; j++) {
+                        const double xv = xs[j * kTile];
+                        const double* __restrict__ N = &sp.nrt[j][kSubW + r0];
+#pragma unroll
+                        for (int r = 0; r < kSubW; r++) c[r] = fma(N[r], xv, c[r]);
+                    }
+                }
+            }
+            // the pair's coefficients are read next by bulk copies (async proxy)
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.pdone[slot]);
+        }
+        P.lp[s] = lpa;
+        P.d2[s] = d2a;
+        if (WANT_LZ) P.lz[s] = lza;
+    }
+    if (rec) {
+        P.stats[blockIdx.x * 8 + 5] = (unsigned long long)(clock64() - t_begin);
+        P.stats[blockIdx.x * 8 + 6] = (unsigned long long)t_cwait;
+    }
+}
+
+template <bool WANT_LZ>
+__global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_constant__ ChainArgs P) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    ChainSmem& sm = *reinterpret_cast<ChainSmem*>(smem_raw);
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kStages; i++) {
+            mbar_init(&sm.full[i], 1);
+            mbar_init(&sm.empty[i], kDmmaThreads / 32);
+        }
+        for (int s = 0; s < kSlots; s++) {
+            mbar_init(&sm.cready[s], kDmmaThreads / 32);
+            mbar_init(&sm.pdone[s], 4);
+            mbar_init(&sm.cfull[s][0], 1);
+            mbar_init(&sm.cfull[s][1], 1);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+    const int wg = threadIdx.x >> 7;
+    if (wg < 2) {
+        reg_inc<kRegsDmma>();
+        dmma_role(sm, P);
+    } else if (wg == 2) {
+        reg_dec<kRegsProd>();
+        if (threadIdx.x == kDmmaThreads) producer_role(sm, P);
+    } else {
+        reg_dec<kRegsPanel>();
+        panel_role<WANT_LZ>(sm, P, wg - 3);
+    }
+}
+
+// tiled workspace -> int64 [S][n] row-major, through a 32x32 shared-memory transpose
+__global__ void __launch_bounds__(256)
+export_coeffs_tiled_kernel(const double* __restrict__ Xt, int npad, int n, int64_t S, int64_t* __restrict__ out,
+                           int64_t ldo) {
+    __shared__ double tile[32][33];
+    const int64_t s0 = (int64_t)blockIdx.x * 32;
+    const int i0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) {
+        const int i = i0 + r;
+        const int64_t s = s0 + tx;
+        tile[r][tx] = (i < n && s < S) ? Xt[((size_t)(s >> 7) * npad + i) * kRowLd + (s & 127)] : 0.0;
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int64_t s = s0 + r;
+        const int i = i0 + tx;
+        if (s < S && i < n) out[(size_t)s * ldo + i] = (int64_t)tile[tx][r];
+    }
+}
+
+__global__ void chain_finish_logq_kernel(const double* __restrict__ lp, double sum_lognorm, int64_t S,
+                                         double* __restrict__ logq) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < S) logq[s] = -lp[s] - sum_lognorm;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------
+void chain_free(BlockedCtx& bc) {
+    ChainCtx& cc = bc.chain;
+    cudaFree(cc.Rpk);
+    cudaFree(cc.Bpk);
+    cudaFree(cc.tp);
+    cudaFree(cc.subs);
+    for (auto& w : cc.work) {
+        cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
+        w = BlockedWork{};
+    }
+    cc = ChainCtx{};
+}
+
+// shared-memory images of the 64 x 16 slivers of an [rows][cols] row-major matrix M (ldm = its row length):
+// out[rt][kt][r][20], zero outside the matrix
+static void pack_slivers(const double* M, int rows, int cols, int ldm, int npad, std::vector<double>& out,
+                         bool identity_pad) {
+    const int nrt = npad / kPair, nkt = npad / kBK;
+    out.assign((size_t)nrt * nkt * kPair * kLdA, 0.0);
+    for (int rt = 0; rt < nrt; rt++)
+        for (int kt = 0; kt < nkt; kt++) {
+            double* t = &out[((size_t)rt * nkt + kt) * kPair * kLdA];
+            for (int r = 0; r < kPair; r++)
+                for (int k = 0; k < kBK; k++) {
+                    const int i = rt * kPair + r, j = kt * kBK + k;
+                    double v = 0.0;
+                    if (i < rows && j < cols) v = M[(size_t)i * ldm + j];
+                    else if (identity_pad && i == j) v = 1.0;
+                    t[r * kLdA + k] = v;
+                }
+        }
+}
+
+cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) {
+    ChainCtx& cc = bc.chain;
+    const int n = d.n;
+    const int npad = (n + kPair - 1) / kPair * kPair;
+    cc.npad = npad;
+    std::vector<double> Rup((size_t)n * n, 0.0);
+    for (int i = 0; i < n; i++)
+        for (int j = i; j < n; j++) Rup[(size_t)i * n + j] = d.R[(size_t)i * n + j];
+    std::vector<double> Rpk, Bpk, tp(npad, 0.0);
+    pack_slivers(Rup.data(), n, n, n, npad, Rpk, true);
+    pack_slivers(d.B, n, n, n, npad, Bpk, false);
+    for (int i = 0; i < n; i++) tp[i] = d.t[i];
+    std::vector<SubPack> subs(npad / kSubW);
+    for (int gs = 0; gs < npad / kSubW; gs++) {
+        SubPack& sp = subs[gs];
+        memset(&sp, 0, sizeof(sp));
+        const int g0 = gs * kSubW;
+        const int lo = g0 / kPair * kPair;
+        const int base = g0 - lo;
+        for (int j = 0; j < kSubW; j++) {
+            const int gi = g0 + j;
+            if (gi < n) {
+                for (int jj = 0; jj + 1 < kSubW; jj++) {
+                    const int k = j - (kSubW - 1) + jj;  // sub-block-relative coordinate held by window slot jj
+                    if (k >= 0) sp.nrt[j][jj] = -d.R[(size_t)(g0 + k) * n + gi];
+                }
+                for (int r = 0; r < base; r++) sp.nrt[j][kSubW + r] = -d.R[(size_t)(lo + r) * n + gi];
+                CoordConst& c = sp.cc[j];
+                c.inv_r = 1.0 / hc.rdiag[gi];
+                c.r2 = hc.rdiag[gi] * hc.rdiag[gi];
+                c.a = hc.inv2s2[gi];
+                c.q = hc.q[gi];
+                c.sq = hc.sq[gi];
+                c.znorm = hc.znorm[gi];
+                c.eps1 = hc.eps1[gi];
+                c.lognz = std::log(hc.znorm[gi]);
+                sp.ci[j] = make_int4(hc.kind[gi], hc.dmax[gi], hc.uidx[gi], hc.mode[gi]);
+            } else {  // padding coordinate: center 0, R_ii = 1, rounded => x = 0
+                sp.cc[j].inv_r = 1.0;
+                sp.ci[j] = make_int4(0, 0, 0, 1);
+            }
+        }
+    }
+    cudaError_t e;
+    auto up = [&](void** dst, const void* src, size_t bytes) -> cudaError_t {
+        cudaError_t er = cudaMalloc(dst, bytes);
+        if (er != cudaSuccess) return er;
+        return cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice);
+    };
+    if ((e = up((void**)&cc.Rpk, Rpk.data(), sizeof(double) * Rpk.size())) != cudaSuccess) return e;
+    if ((e = up((void**)&cc.Bpk, Bpk.data(), sizeof(double) * Bpk.size())) != cudaSuccess) return e;
+    if ((e = up((void**)&cc.tp, tp.data(), sizeof(double) * tp.size())) != cudaSuccess) return e;
+    if ((e = up((void**)&cc.subs, subs.data(), sizeof(SubPack) * subs.size())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(klein_chain_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(ChainSmem))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(klein_chain_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(ChainSmem))) != cudaSuccess) return e;
+    cc.batch = (int64_t)(bc.sm_count > 0 ? bc.sm_count : 148) * kTile * 3 * kSlots;
+    cc.ready = true;
+    return cudaSuccess;
+}
+
+static cudaError_t chain_ensure_work(ChainCtx& cc, BlockedWork& w, int64_t cap) {
+    if (w.cap >= cap) return cudaSuccess;
+    cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
+    w = BlockedWork{};
+    cudaError_t e;
+    const size_t xbytes = sizeof(double) * (size_t)(cap / kTile) * cc.npad * kRowLd;
+    if ((e = cudaMalloc(&w.X, xbytes)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w.lp, sizeof(double) * cap)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w.d2, sizeof(double) * cap)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w.lz, sizeof(double) * cap)) != cudaSuccess) return e;
+    // the padding columns of every row are read by the bulk copies: keep them finite
+    if ((e = cudaMemset(w.X, 0, xbytes)) != cudaSuccess) return e;
+    w.cap = cap;
+    return cudaSuccess;
+}
+
+// one batch of S <= w.cap samples: coefficients into w.X (tiled), accumulators into w.lp / d2 / lz, lattice points
+// into V (may be nullptr)
+static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64_t seed, uint64_t first_id, uint32_t tag,
+                               bool want_lz, double* V, int64_t ldv, cudaStream_t st) {
+    ChainCtx& cc = bc.chain;
+    ChainArgs a{};
+    a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.subs = cc.subs;
+    a.Xt = w.X; a.lp = w.lp; a.d2 = w.d2; a.lz = w.lz;
+    a.V = V; a.ldv = ldv; a.S = S;
+    a.npad = cc.npad; a.n_valid = bc.n;
+    a.ntiles = (int)((S + kTile - 1) / kTile);
+    a.want_lz = want_lz ? 1 : 0;
+    a.seed = seed; a.first_id = first_id; a.tag = tag;
+    const int sms = bc.sm_count > 0 ? bc.sm_count : 148;
+    const int grid = a.ntiles < sms ? a.ntiles : sms;
+    static const bool want_stats = getenv("LGS_CHAIN_STATS") != nullptr;
+    static unsigned long long* stats_dev = nullptr;
+    if (want_stats && !stats_dev) cudaMalloc(&stats_dev, sizeof(unsigned long long) * 8 * 1024);
+    a.stats = want_stats ? stats_dev : nullptr;
+    {
+        ProfScope ps(bc.prof, LGS_PROF_CHAIN, st);
+        if (want_lz) klein_chain_kernel<true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        else klein_chain_kernel<false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+    }
+    if (want_stats) {  // development only: synchronous read-back, mean over CTAs
+        std::vector<unsigned long long> hs((size_t)grid * 8);
+        cudaStreamSynchronize(st);
+        cudaMemcpy(hs.data(), stats_dev, sizeof(unsigned long long) * hs.size(), cudaMemcpyDeviceToHost);
+        double m[8] = {};
+        for (int b = 0; b < grid; b++)
+            for (int k = 0; k < 8; k++) m[k] += (double)hs[(size_t)b * 8 + k] / grid;
+        fprintf(stderr,
+                "[chain stats] grid %d tiles %d V=%d | dmma total %.0f kcyc, wait-full %.0f (%.1f%%), stages %.0f | producer "
+                "wait-empty %.0f idle %.0f | panel0 total %.0f wait-centers %.0f (%.1f%%)\n",
+                grid, a.ntiles, V ? 1 : 0, m[0] / 1e3, m[1] / 1e3, 100.0 * m[1] / (m[0] + 1), m[2], m[3] / 1e3, m[4] / 1e3,
+                m[5] / 1e3, m[6] / 1e3, 100.0 * m[6] / (m[5] + 1));
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
+                               double* logq, cudaStream_t st) {
+    if (S <= 0) return cudaSuccess;
+    ChainCtx& cc = bc.chain;
+    cudaError_t e;
+    const int n = bc.n;
+    const int64_t cap = S < cc.batch ? (S + kTile - 1) / kTile * kTile : cc.batch;
+    BlockedWork& w = cc.work[0];
+    if ((e = chain_ensure_work(cc, w, cap)) != cudaSuccess) return e;
+    for (int64_t s0 = 0; s0 < S; s0 += w.cap) {
+        const int64_t cnt = (S - s0) < w.cap ? (S - s0) : w.cap;
+        if ((e = chain_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, 0u, false, V ? V + (size_t)s0 * n : nullptr, n,
+                             st)) != cudaSuccess) return e;
+        if (X) {
+            ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+            dim3 grid((unsigned)((cnt + 31) / 32), (unsigned)((n + 31) / 32));
+            export_coeffs_tiled_kernel<<<grid, 256, 0, st>>>(w.X, cc.npad, n, cnt, X + (size_t)s0 * n, n);
+        }
+        if (logq) {
+            ProfScope ps2(bc.prof, LGS_PROF_OTHER, st);
+            chain_finish_logq_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(w.lp, bc.sum_lognorm, cnt, logq + s0);
+        }
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace lgs

@@ -64,6 +64,16 @@ struct PanelParams {
                             // w = 1 for a round-to-mean coordinate (sigma_i < 1e-10, klein.py:201-204) or padding
 };
 
+// ---- chain kernel (lgs_chain.cu): constants of one 8-coordinate sub-block, staged into shared memory by a bulk copy
+constexpr int kChainRowLd = 132;  // doubles per coordinate row of a 128-sample tile (128 + 4 padding)
+struct SubPack {
+    CoordConst cc[8];
+    int4 ci[8];          // as PanelParams::ci
+    double nrt[8][64];   // row j (coordinate base + j of its 64-block): [0..6] rotating-window triangle entries,
+                         // [8 + r] = -R[block row r][coordinate] for the rows r < base below the sub-block
+};
+static_assert(sizeof(SubPack) == 4736, "SubPack is copied as raw bytes");
+
 // one batch worth of device workspace for the blocked path
 struct BlockedWork {
     double* X = nullptr;    // [npad][cap] coordinate-major centers / coefficients
@@ -84,9 +94,42 @@ struct Prof {
     std::vector<cudaEvent_t> pool;  // recycled events
 };
 
+// brackets one launch with events when profiling is on (class ids: LGS_PROF_* in include/lgs_b200.h)
+struct ProfScope {
+    Prof& p;
+    cudaStream_t st;
+    cudaEvent_t e1 = nullptr;
+    ProfScope(Prof& prof, int cls, cudaStream_t s) : p(prof), st(s) {
+        if (!p.on) return;
+        cudaEvent_t ev[2];
+        for (auto& e : ev) {
+            if (!p.pool.empty()) { e = p.pool.back(); p.pool.pop_back(); }
+            else cudaEventCreate(&e);
+        }
+        cudaEventRecord(ev[0], st);
+        e1 = ev[1];
+        p.recs.push_back(ProfRec{cls, ev[0], ev[1]});
+    }
+    ~ProfScope() { if (e1) cudaEventRecord(e1, st); }
+};
+
+// chain kernel (lgs_chain.cu): packed operands and tiled workspaces
+struct ChainCtx {
+    bool ready = false;
+    int npad = 0;                 // n padded to a multiple of 64
+    double* Rpk = nullptr;        // [npad/64][npad/16][64][20] shared-memory images of the 64 x 16 slivers of R
+    double* Bpk = nullptr;        // same for the basis
+    double* tp = nullptr;         // [npad]
+    SubPack* subs = nullptr;      // [npad/8]
+    BlockedWork work[3];          // tiled: X = [cap/128][npad][132]; [0] Klein, [1]/[2] IMHK proposals
+    int64_t batch = 0;            // samples per full batch: sm_count x 128 x 9
+};
+
 struct BlockedCtx {
     bool ready = false;
     Prof prof;
+    ChainCtx chain;
+    int use_chain = 1;                 // LGS_CHAIN=0 selects the multi-kernel v1 path (development A/B)
     int n = 0, npad = 0, mpad = 0;     // npad: coordinates padded to 32; mpad: rows of B padded to 64
     double* Rp = nullptr;              // [npad][npad] R, identity on the padding
     double* Bp = nullptr;              // [mpad][npad] basis, zero padding
@@ -156,5 +199,11 @@ cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, i
                                 int weight_mode, double* V, int64_t* X, cudaStream_t st);
 cudaError_t launch_imhk_blocked_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
                                           double* logw, cudaStream_t st);
+
+// lgs_chain.cu  (persistent warp-specialised kernel)
+cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc);
+void chain_free(BlockedCtx& bc);
+cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
+                               double* logq, cudaStream_t st);
 
 }  // namespace lgs
