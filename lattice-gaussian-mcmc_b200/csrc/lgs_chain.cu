@@ -22,6 +22,7 @@
 #include "lgs_internal.h"
 
 #include <cmath>
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -91,29 +92,65 @@ __device__ __forceinline__ void dmma_16x8x8(double (&d)[4], const double (&a)[4]
         : "d"(a[0]), "d"(a[1]), "d"(a[2]), "d"(a[3]), "d"(b[0]), "d"(b[1]));
 }
 
+// DMMA.8x8x4, the SASS unit an m16n8k8 is split into.  volatile: the issue order of these is chosen by hand, see
+// LGS_CHAIN_DEPDIST.  Fragments: a = A[g][t], b = B[t][g], d = C[g][2t], C[g][2t+1]  (g = lane / 4, t = lane % 4)
+__device__ __forceinline__ void dmma_8x8x4(double (&d)[2], const double a, const double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(d[0]), "+d"(d[1])
+                 : "d"(a), "d"(b));
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // geometry
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kTile = 128;            // samples per tile
 constexpr int kRowLd = kChainRowLd;   // 132: doubles per coordinate row of a tile in HBM and in shared memory
 constexpr int kPair = 64;             // coordinates per work item (a pair of 32-blocks of the v1 path)
-constexpr int kBK = 16;               // contraction depth of one stage
+#ifndef LGS_CHAIN_BK
+#define LGS_CHAIN_BK 16
+#endif
+constexpr int kBK = LGS_CHAIN_BK;     // contraction depth of one stage
 constexpr int kLdA = kBK + 4;         // 20: row stride of an A sliver (conflict-free LDS.64 fragment loads)
 constexpr int kSubW = 8;              // coordinates per sub-block of the panel (width of the register window)
+#ifndef LGS_CHAIN_SLOTS
+#define LGS_CHAIN_SLOTS 3
+#endif
+#ifndef LGS_CHAIN_DEPDIST
+#define LGS_CHAIN_DEPDIST 0   // 0: m16n8k8 in compiler order; D > 0: m8n8k4, dependent instructions D places apart
+#endif
+#ifndef LGS_CHAIN_INTDELTA
+#define LGS_CHAIN_INTDELTA 0
+#endif
+#ifndef LGS_CHAIN_NOBAR
+#define LGS_CHAIN_NOBAR 0
+#endif
 #ifndef LGS_CHAIN_STAGES
-#define LGS_CHAIN_STAGES 6
+#define LGS_CHAIN_STAGES 5
 #endif
 constexpr int kStages = LGS_CHAIN_STAGES;
-constexpr int kSlots = 3;             // tiles in flight per CTA = panel warpgroups
+constexpr int kSlots = LGS_CHAIN_SLOTS;  // tiles in flight per CTA = panel warpgroups
 constexpr int kDmmaThreads = 256, kProdThreads = 128, kPanelThreads = kSlots * 128;
 constexpr int kThreads = kDmmaThreads + kProdThreads + kPanelThreads;  // 768
-constexpr int kRegsDmma = 120, kRegsProd = 24, kRegsPanel = 72;        // 768 x 80 at launch, rebalanced
+// thread layout: panel warpgroups first (lowest warp ids), then the producer warpgroup, then the DMMA warpgroups
+#ifndef LGS_CHAIN_PANEL_FIRST
+#define LGS_CHAIN_PANEL_FIRST 1
+#endif
+constexpr int kPanelBase = LGS_CHAIN_PANEL_FIRST ? 0 : kDmmaThreads + kProdThreads;
+constexpr int kProdBase = LGS_CHAIN_PANEL_FIRST ? kPanelThreads : kDmmaThreads;
+constexpr int kDmmaBase = LGS_CHAIN_PANEL_FIRST ? kPanelThreads + kProdThreads : 0;
+// registers: 768 x 80 at launch (3 slots) or 896 x 72 (4 slots), rebalanced between the roles with setmaxnreg
+constexpr int kRegsDmma = kSlots == 3 ? 120 : 112, kRegsProd = 24, kRegsPanel = kSlots == 3 ? 72 : 64;
 constexpr uint32_t kABytes = kPair * kLdA * 8;   // 10 240
 constexpr uint32_t kBBytes = kBK * kRowLd * 8;   // 16 896
 
 // F_NODATA: a stage without operand bytes (the top pair has nothing above it: its centers are t itself);
 // F_NOSTORE: no epilogue stores, only the cready signal (wakes a panel warpgroup that has no tile left)
-enum : int { F_FIRST = 1, F_LAST = 2, F_POINT = 4, F_NOSTORE = 8, F_EXIT = 16, F_NODATA = 32 };
+// F_PART_OUT / F_PART_IN: look-ahead.  The centers of pair p are contracted in two items: the columns of the pairs
+// above p - 1 as soon as those are drawn (while the tile's panel warps are still busy with pair p - 1; the partial
+// result t - acc is parked in the pair's own rows), and the 64 columns of pair p - 1 when its panel is done -- so a
+// finished panel waits for a 4-stage item, not for a contraction over every finished coordinate.
+enum : int { F_FIRST = 1, F_LAST = 2, F_POINT = 4, F_NOSTORE = 8, F_EXIT = 16, F_NODATA = 32, F_PART_OUT = 64,
+             F_PART_IN = 128 };
 
 struct StageHdr {
     int flags;
@@ -126,17 +163,20 @@ struct ChainSmem {
     double A[kStages][kPair][kLdA];
     double B[kStages][kBK][kRowLd];
     SubPack sub[kSlots][2];            // double-buffered constants of the sub-block being drawn
-    double xs[kSlots][kSubW][kTile];   // the sub-block's draws, for the update of the rows below
+    alignas(16) double xs[kSlots][kSubW][kRowLd];  // the sub-block's draws (B operand of the rows-below update), then
+                                                   // the next window on its way back to one-thread-per-sample
     StageHdr hdr[kStages];
     uint64_t full[kStages], empty[kStages];
     uint64_t cready[kSlots], pdone[kSlots], cfull[kSlots][2];
     int slot_tile[kSlots];
+    int cdone[kSlots][2];              // warps of the slot that have finished with a constants buffer
 };
 
 struct ChainArgs {
     const double* Rpk;      // packed slivers of R: [npad/64][npad/16][64][20]
     const double* Bpk;      // packed slivers of the basis, same shape
     const double* tvec;     // [npad]
+    const double* invr;     // [npad] 1 / R_ii (1 on the padding): centers are kept divided by their R_ii
     const SubPack* subs;    // [npad/8] sub-block constants, index = first coordinate / 8
     double* Xt;             // tiled coefficient workspace
     double* lp;             // [cap] per-sample accumulators (outputs)
@@ -151,6 +191,7 @@ struct ChainArgs {
     int want_lz;
     uint64_t seed, first_id;
     uint32_t tag;
+    double inv_two_sigma2;  // 1 / (2 sigma^2)
     unsigned long long* stats;  // development counters (LGS_CHAIN_STATS=1), 8 per CTA, or nullptr
 };
 
@@ -158,11 +199,15 @@ struct ChainArgs {
 // DMMA warps: consume stages until the producer sends F_EXIT
 // ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x - kDmmaBase;
     const int warp = tid >> 5, lane = tid & 31;
     const int wm = warp >> 2, wn = warp & 3;
     const int g = lane >> 2, t = lane & 3;
+#if LGS_CHAIN_DEPDIST
+    double acc[4][4][2];   // [m8 tile][n8 tile]: rows 8 mt + g, columns 8 nt + 2t, 2t + 1
+#else
     double acc[2][4][4];
+#endif
     uint32_t it = 0;
     const bool rec = P.stats && tid == 0;
     long long t_wait = 0;
@@ -180,14 +225,44 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
         if (h.flags & F_EXIT) break;
         if (h.flags & F_FIRST) {
 #pragma unroll
-            for (int a = 0; a < 2; a++)
+            for (int a = 0; a < (int)(sizeof(acc) / sizeof(acc[0])); a++)
 #pragma unroll
                 for (int b = 0; b < 4; b++)
 #pragma unroll
-                    for (int c = 0; c < 4; c++) acc[a][b][c] = 0.0;
+                    for (int c = 0; c < (int)(sizeof(acc[0][0]) / sizeof(double)); c++) acc[a][b][c] = 0.0;
         }
         {
             if (!(h.flags & F_NODATA)) {
+#if LGS_CHAIN_DEPDIST
+                // One DMMA.8x8x4 per instruction, issued so that an instruction depends on the one LGS_CHAIN_DEPDIST
+                // places before it.  A warp that issues back-to-back independent DMMAs keeps the scheduler's greedy
+                // slot for its whole burst (1024 cycles per stage) and the panel warps' FP64 instructions wait that
+                // long; short dependency chains make the DMMA warps hand the pipe over after every few instructions.
+                constexpr int D = LGS_CHAIN_DEPDIST;
+#pragma unroll
+                for (int kh = 0; kh < kBK; kh += 8) {
+                    double af[4][2], bf[4][2];   // [tile][k4 step]
+#pragma unroll
+                    for (int mt = 0; mt < 4; mt++) {
+                        af[mt][0] = sm.A[stage][wm * 32 + mt * 8 + g][kh + t];
+                        af[mt][1] = sm.A[stage][wm * 32 + mt * 8 + g][kh + 4 + t];
+                    }
+#pragma unroll
+                    for (int nt = 0; nt < 4; nt++) {
+                        bf[nt][0] = sm.B[stage][kh + t][wn * 32 + nt * 8 + g];
+                        bf[nt][1] = sm.B[stage][kh + 4 + t][wn * 32 + nt * 8 + g];
+                    }
+#pragma unroll
+                    for (int grp = 0; grp < 16; grp += D)
+#pragma unroll
+                        for (int ks = 0; ks < 2; ks++)
+#pragma unroll
+                            for (int i = 0; i < D; i++) {
+                                const int blk = grp + i, mt = blk >> 2, nt = blk & 3;
+                                dmma_8x8x4(acc[mt][nt], af[mt][ks], bf[nt][ks]);
+                            }
+                }
+#else
 #pragma unroll
                 for (int kk = 0; kk < kBK; kk += 8) {
                     double af[2][4], bf[4][2];
@@ -210,6 +285,7 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
 #pragma unroll
                         for (int nt = 0; nt < 4; nt++) dmma_16x8x8(acc[mt][nt], af[mt], bf[nt]);
                 }
+#endif
             }
         }
         __syncwarp();
@@ -217,6 +293,11 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
         if (!(h.flags & F_LAST)) continue;
         if (!(h.flags & F_NOSTORE)) {
             // fragment (mt, nt): rows g / g+8 of the 16-row tile, columns 2t, 2t+1 of the 8-column tile
+#if LGS_CHAIN_DEPDIST
+#define LGS_ACC(mt, hh, nt, c) acc[(mt) * 2 + (hh)][nt][c]
+#else
+#define LGS_ACC(mt, hh, nt, c) acc[mt][nt][(hh) * 2 + (c)]
+#endif
             if (h.flags & F_POINT) {
                 const int64_t s0 = (int64_t)h.tile * kTile;
 #pragma unroll
@@ -228,8 +309,8 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
 #pragma unroll
                         for (int nt = 0; nt < 4; nt++) {
                             const int64_t col = s0 + wn * 32 + nt * 8 + t * 2;
-                            if (col < P.S) P.V[(size_t)col * P.ldv + row] = acc[mt][nt][hh * 2];
-                            if (col + 1 < P.S) P.V[(size_t)(col + 1) * P.ldv + row] = acc[mt][nt][hh * 2 + 1];
+                            if (col < P.S) P.V[(size_t)col * P.ldv + row] = LGS_ACC(mt, hh, nt, 0);
+                            if (col + 1 < P.S) P.V[(size_t)(col + 1) * P.ldv + row] = LGS_ACC(mt, hh, nt, 1);
                         }
                     }
             } else {
@@ -240,18 +321,21 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
                     for (int hh = 0; hh < 2; hh++) {
                         const int row = h.r0 + wm * 32 + mt * 16 + g + hh * 8;
                         const double tv = P.tvec[row];
+                        const double ir = (h.flags & F_PART_OUT) ? 1.0 : P.invr[row];
 #pragma unroll
                         for (int nt = 0; nt < 4; nt++) {
                             const int col = wn * 32 + nt * 8 + t * 2;
-                            double2 o;
-                            o.x = tv - acc[mt][nt][hh * 2];
-                            o.y = tv - acc[mt][nt][hh * 2 + 1];
-                            *reinterpret_cast<double2*>(xt + (size_t)row * kRowLd + col) = o;
+                            double2* dst = reinterpret_cast<double2*>(xt + (size_t)row * kRowLd + col);
+                            double2 o = make_double2(tv, tv);
+                            if (h.flags & F_PART_IN) o = *dst;  // written by these same threads (F_PART_OUT item)
+                            o.x = (o.x - LGS_ACC(mt, hh, nt, 0)) * ir;
+                            o.y = (o.y - LGS_ACC(mt, hh, nt, 1)) * ir;
+                            *dst = o;
                         }
                     }
             }
         }
-        if (!(h.flags & F_POINT)) {
+        if (!(h.flags & (F_POINT | F_PART_OUT))) {
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.cready[h.slot]);
         }
@@ -292,19 +376,28 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
         }
         it++;
     };
-    // centers of pair p (0 = top) of a tile: rows [lo, lo + 64) against every coordinate above them
-    auto issue_centers = [&](int slot, int p, int tile) {
+    // centers of pair p (0 = top) of a tile, rows [lo, lo + 64):
+    //   part A (p >= 2): the columns of pairs 0 .. p - 2, issued ahead (look-ahead), parks t - acc in the rows;
+    //   part B (p >= 1): the 64 columns of pair p - 1, finishes the centers and wakes the panel warpgroup.
+    auto issue_range = [&](int flags, int slot, int lo, int tile, int c0, int c1) {
+        const int rt = lo / kPair;
+        const int kt0 = c0 / kBK, kt1 = c1 / kBK;
+        const double* a = P.Rpk + ((size_t)rt * nkt + kt0) * (kPair * kLdA);
+        const double* b = P.Xt + (size_t)tile * P.npad * kRowLd + (size_t)kt0 * kBK * kRowLd;
+        for (int kt = kt0; kt < kt1; kt++, a += kPair * kLdA, b += kBK * kRowLd)
+            push(flags | (kt == kt0 ? F_FIRST : 0) | (kt == kt1 - 1 ? F_LAST : 0), slot, lo, tile, a, b);
+    };
+    auto issue_A = [&](int slot, int p, int tile) {
+        const int lo = P.npad - kPair * (p + 1);
+        issue_range(F_PART_OUT, slot, lo, tile, lo + 2 * kPair, P.npad);
+    };
+    auto issue_B = [&](int slot, int p, int tile) {
         const int lo = P.npad - kPair * (p + 1);
         if (p == 0) {
             push(F_FIRST | F_LAST | F_NODATA, slot, lo, tile, nullptr, nullptr);
             return;
         }
-        const int rt = lo / kPair;
-        const int kt0 = (lo + kPair) / kBK;
-        const double* a = P.Rpk + ((size_t)rt * nkt + kt0) * (kPair * kLdA);
-        const double* b = P.Xt + (size_t)tile * P.npad * kRowLd + (size_t)kt0 * kBK * kRowLd;
-        for (int kt = kt0; kt < nkt; kt++, a += kPair * kLdA, b += kBK * kRowLd)
-            push((kt == kt0 ? F_FIRST : 0) | (kt == nkt - 1 ? F_LAST : 0), slot, lo, tile, a, b);
+        issue_range(p >= 2 ? F_PART_IN : 0, slot, lo, tile, lo + kPair, lo + 2 * kPair);
     };
     // 64 rows of the lattice points of a finished tile
     auto issue_point = [&](int tile, int rt) {
@@ -315,7 +408,8 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     };
 
     int next_tile = blockIdx.x;
-    int s_pair[kSlots], s_tile[kSlots];
+    int s_pair[kSlots], s_tile[kSlots];   // s_pair: pairs whose centers have been completed (part B issued)
+    int s_ahead[kSlots];                  // next pair whose part A has not been issued yet
     uint32_t pd_par[kSlots];
     bool s_active[kSlots];
     int n_active = 0;
@@ -324,8 +418,9 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
             s_tile[s] = next_tile;
             next_tile += G;
             s_pair[s] = 1;
+            s_ahead[s] = 2;
             sm.slot_tile[s] = s_tile[s];
-            issue_centers(s, 0, s_tile[s]);
+            issue_B(s, 0, s_tile[s]);
         } else {
             s_active[s] = false;
             n_active--;
@@ -343,7 +438,7 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     constexpr int kQ = 32;
     int pq[kQ];
     int pq_head = 0, pq_cnt = 0, pq_rt = 0;
-    int rr = 0;
+    int rr = 0, ra = 0;
     for (;;) {
         bool progressed = false;
         if (pq_cnt < kQ) {
@@ -355,13 +450,30 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
                     if (P.V) { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
                     assign(s);
                 } else {
-                    issue_centers(s, s_pair[s], s_tile[s]);
+                    const int pr = s_pair[s];  // its panel may start once part B is through
+                    if (pr >= 2 && s_ahead[s] <= pr) {
+                        issue_A(s, pr, s_tile[s]);
+                        s_ahead[s] = pr + 1;
+                    }
+                    issue_B(s, pr, s_tile[s]);
                     s_pair[s]++;
                 }
                 rr = s + 1;
                 progressed = true;
                 break;
             }
+        }
+        if (progressed) continue;
+        // look-ahead: part A of pair s_pair (its columns, the pairs up to s_pair - 2, are all drawn) while the
+        // slot's panel warps work on pair s_pair - 1
+        for (int i = 0; i < kSlots; i++) {
+            const int s = (ra + i) % kSlots;
+            if (!s_active[s] || s_ahead[s] > s_pair[s] || s_ahead[s] >= npairs) continue;
+            issue_A(s, s_ahead[s], s_tile[s]);
+            s_ahead[s]++;
+            ra = s + 1;
+            progressed = true;
+            break;
         }
         if (progressed) continue;
         if (pq_cnt > 0) {
@@ -398,31 +510,46 @@ __device__ __noinline__ double chain_samplez_fast_call(double mean, double inv2s
     return (double)samplez_fast(mean, fz, u, zsum);
 }
 
-template <bool WANT_LZ>
+template <bool WANT_LZ, bool WANT_D2>
 __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, const int slot) {
-    const int sl = (threadIdx.x - (kDmmaThreads + kProdThreads)) & 127;
+    const int sl = (threadIdx.x - kPanelBase) & 127;
     const int lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int wbase = sl & ~31;  // first sample of this warp inside the tile
     const int npairs = P.npad / kPair;
     const int nsub = P.npad / kSubW;
     const Philox gen(P.seed);
-    double* __restrict__ xs = &sm.xs[slot][0][sl];
+    double* __restrict__ xs = &sm.xs[slot][0][sl];        // this thread's column of the sub-block's draws
+    double* __restrict__ xsw = &sm.xs[slot][0][wbase];    // the warp's 32 columns (DMMA fragments)
     uint32_t cr_par = 0, q = 0;
     const bool rec = P.stats && slot == 0 && sl == 0;
     long long t_cwait = 0;
     const long long t_begin = rec ? clock64() : 0;
+    // bytes of the constants of the sub-block whose rows-below count is `base` (the rect rows come last)
+    auto sub_bytes = [](int base) -> uint32_t {
+        return (uint32_t)(offsetof(SubPack, rect) + ((base + 15) / 16 * 16) * kRectLd * sizeof(double));
+    };
     for (;;) {
         mbar_wait(&sm.cready[slot], cr_par);
         cr_par ^= 1;
         const int tile = sm.slot_tile[slot];
         if (tile < 0) break;
-        if (sl == 0) {
-            mbar_arrive_expect_tx(&sm.cfull[slot][q & 1], (uint32_t)sizeof(SubPack));
-            bulk_g2s(&sm.sub[slot][q & 1], &P.subs[nsub - 1], (uint32_t)sizeof(SubPack), &sm.cfull[slot][q & 1]);
+        // constants of sub-block i of a tile (i = 0 is the top one): SubPack nsub - 1 - i, rows below = 8 (7 - i % 8)
+        auto load_sub = [&](int i, uint32_t qq) {
+            const uint32_t nb = sub_bytes(kSubW * (7 - (i & 7)));
+            mbar_arrive_expect_tx(&sm.cfull[slot][qq & 1], nb);
+            bulk_g2s(&sm.sub[slot][qq & 1], &P.subs[nsub - 1 - i], nb, &sm.cfull[slot][qq & 1]);
+        };
+        if (sl == 0) {  // every warp of the slot has finished the previous tile (pdone -> scheduler -> cready)
+            load_sub(0, q);
+            load_sub(1, q + 1);
         }
+        int isub = 0;
         const int64_t s = (int64_t)tile * kTile + sl;
         const uint64_t id = P.first_id + (uint64_t)s;
-        double* __restrict__ xt = P.Xt + (size_t)tile * P.npad * kRowLd + sl;
-        double lpa = 0.0, d2a = 0.0, lza = 0.0;
+        double* __restrict__ xtile = P.Xt + (size_t)tile * P.npad * kRowLd;
+        double* __restrict__ xt = xtile + sl;
+        double d2a = 0.0, lza = 0.0;
         uint4 w = make_uint4(0, 0, 0, 0);
         int wpair = -1;
 #pragma unroll 1
@@ -442,23 +569,36 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
             }
 #pragma unroll 1
             for (int base = kPair - kSubW; base >= 0; base -= kSubW) {
-                const int gsub = (lo + base) / kSubW;
                 const int buf = q & 1;
+                // done with this buffer: the last of the slot's four warps to say so refills it with the constants of
+                // the sub-block after next (no warpgroup-wide barrier in the coordinate loop)
+                auto release_sub = [&](int b) {
+#if !LGS_CHAIN_NOBAR
+                    named_bar_sync(1 + slot, 128);
+                    if (sl == 0 && isub + 2 < nsub) load_sub(isub + 2, q + 1);
+                    isub++;
+                    return;
+#endif
+                    __syncwarp();
+                    if (lane == 0) {
+                        __threadfence_block();
+                        if (atomicAdd(&sm.cdone[slot][b], 1) == 3) {
+                            sm.cdone[slot][b] = 0;
+                            if (isub + 2 < nsub) load_sub(isub + 2, q + 1);  // q was already advanced: (q + 1) & 1 == b
+                        }
+                    }
+                    __syncwarp();
+                    isub++;
+                };
                 mbar_wait(&sm.cfull[slot][buf], (q >> 1) & 1);
-                named_bar_sync(1 + slot, 128);  // the whole warpgroup has left the other buffer
-                if (sl == 0 && gsub > 0) {
-                    mbar_arrive_expect_tx(&sm.cfull[slot][buf ^ 1], (uint32_t)sizeof(SubPack));
-                    bulk_g2s(&sm.sub[slot][buf ^ 1], &P.subs[gsub - 1], (uint32_t)sizeof(SubPack),
-                             &sm.cfull[slot][buf ^ 1]);
-                }
                 q++;
                 const SubPack& sp = sm.sub[slot][buf];
                 double* __restrict__ xp = xt + (size_t)(lo + base + kSubW - 1) * kRowLd;
 #pragma unroll 1
                 for (int j = kSubW - 1; j >= 0; j--, xp -= kRowLd) {
-                    const CoordConst cc = sp.cc[j];
+                    const CoordConst& cc = sp.cc[j];
                     const int4 ci = sp.ci[j];
-                    const double mean = c[kSubW - 1] * cc.inv_r;
+                    const double mean = c[kSubW - 1];  // 1/r_ii is folded into the centers and the triangle
                     double x;
                     if (ci.w) {
                         x = rint(mean);
@@ -468,68 +608,118 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                             w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, P.tag);
                         }
                         const bool odd = ci.z & 1;
-                        const double u = u53(odd ? w.z : w.x, odd ? w.w : w.y);
-                        if (ci.x <= 1) {
-                            double logz;
-                            x = samplez_smooth<WANT_LZ>(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, cc.lognz, ci.x, ci.y,
-                                                        u, &logz);
-                            if (WANT_LZ) lza += logz;
-                        } else {
-                            double zs;
-                            x = chain_samplez_fast_call(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, ci.x, ci.y, u, &zs);
-                            if (WANT_LZ) lza += log(zs);
+                        const uint32_t uhi = odd ? w.z : w.x, ulo = odd ? w.w : w.y;
+                        const int kind = ci.x & 3;
+                        bool done = false;
+                        float dlf;
+#if LGS_CHAIN_INTDELTA
+                        const bool dl_ok = rint_delta_f32(mean, &dlf);
+#else
+                        const bool dl_ok = true;
+                        dlf = (float)(rint(mean) - mean);
+#endif
+                        if (ci.x <= 1 && dl_ok) {  // smooth regime, eligible for the FP32 screen
+                            // no FP64 instruction between the window update above and x below: a panel warp's first
+                            // FP64 instruction after a stretch of other work waits for a whole DMMA burst
+                            float off, corr;
+                            done = samplez_smooth_screen(dlf, sp.cf[j], kind, ci.y, uhi, &off, &corr);
+                            x = rint(mean) + (double)off;
+                            if (WANT_LZ && done) lza += cc.lognz + (double)corr;
+                        }
+                        if (!done) {
+                            const double u = u53(uhi, ulo);
+                            if (kind <= 1) {
+                                double logz;
+                                x = samplez_smooth<WANT_LZ>(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, cc.lognz, kind,
+                                                            ci.y, u, &logz);
+                                if (WANT_LZ) lza += logz;
+                            } else {
+                                double zs;
+                                x = chain_samplez_fast_call(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, kind, ci.y, u,
+                                                            &zs);
+                                if (WANT_LZ) lza += log(zs);
+                            }
                         }
                     }
                     *xp = x;
-                    xs[j * kTile] = x;
-                    const double dl = x - mean;
-                    const double dl2 = dl * dl;
-                    lpa = fma(dl2, cc.a, lpa);
-                    d2a = fma(dl2, cc.r2, d2a);
-                    const double* __restrict__ T = sp.nrt[j];
+                    xs[j * kRowLd] = x;
+                    if (WANT_D2) {
+                        const double dl = x - mean;
+                        d2a = fma(dl * dl, cc.r2, d2a);
+                    }
+                    const double* __restrict__ T = sp.win[j];
 #pragma unroll
                     for (int jj = kSubW - 2; jj >= 0; jj--) c[jj + 1] = fma(T[jj], x, c[jj]);
                     c[0] = 0.0;
                 }
-                // contribution of this sub-block to the rows below it (rows [0, base) of the pair), 8 at a time; the
-                // last group is the next sub-block: it stays in registers as the next window
-#pragma unroll 1
-                for (int r0 = 0; r0 < base - kSubW; r0 += kSubW) {
-                    double a[kSubW];
-                    double* __restrict__ xr = xt + (size_t)(lo + r0) * kRowLd;
+                if (base == 0) {
+                    release_sub(buf);
+                    continue;
+                }
+                // Contribution of the sub-block to the rows below it (rows [0, base) of the pair) as warp-level DMMA:
+                // C[16 rows, 8 samples] += rect[16 rows, 8 coordinates] * x[8 coordinates, 8 samples], one instruction
+                // instead of 128 scalar FMAs per lane group -- every FP64 instruction of a panel warp queues behind
+                // the DMMA warps' stream, so their count is what the panel's speed depends on.  The 8 rows right
+                // below the sub-block are the next window: they go to the (now free) xs rows instead of HBM.
+                __syncwarp();
+                double bf[4][2];
 #pragma unroll
-                    for (int r = 0; r < kSubW; r++) a[r] = __ldcg(xr + (size_t)r * kRowLd);
+                for (int nt = 0; nt < 4; nt++) {
+                    bf[nt][0] = xsw[t * kRowLd + nt * 8 + g];
+                    bf[nt][1] = xsw[(t + 4) * kRowLd + nt * 8 + g];
+                }
+                __syncwarp();
+                const int wrow = base - kSubW;  // first row of the next window
 #pragma unroll 1
-                    for (int j = 0; j < kSubW; j++) {
-                        const double xv = xs[j * kTile];
-                        const double* __restrict__ N = &sp.nrt[j][kSubW + r0];
+                for (int r0 = 0; r0 < base; r0 += 16) {
+                    double af[4];
+                    af[0] = sp.rect[r0 + g][t];
+                    af[1] = sp.rect[r0 + g + 8][t];
+                    af[2] = sp.rect[r0 + g][t + 4];
+                    af[3] = sp.rect[r0 + g + 8][t + 4];
+                    const bool hi_ok = r0 + 8 < base;
+                    double* __restrict__ r_lo = xtile + (size_t)(lo + r0 + g) * kRowLd + wbase + 2 * t;
+                    double* __restrict__ r_hi = r_lo + 8 * kRowLd;
+                    double d[4][4];
 #pragma unroll
-                        for (int r = 0; r < kSubW; r++) a[r] = fma(N[r], xv, a[r]);
+                    for (int nt = 0; nt < 4; nt++) {
+                        const double2 a = __ldcg(reinterpret_cast<const double2*>(r_lo + nt * 8));
+                        d[nt][0] = a.x;
+                        d[nt][1] = a.y;
+                        double2 b = make_double2(0.0, 0.0);
+                        if (hi_ok) b = __ldcg(reinterpret_cast<const double2*>(r_hi + nt * 8));
+                        d[nt][2] = b.x;
+                        d[nt][3] = b.y;
                     }
 #pragma unroll
-                    for (int r = 0; r < kSubW; r++) xr[(size_t)r * kRowLd] = a[r];
-                }
-                if (base > 0) {
-                    const int r0 = base - kSubW;
-                    const double* __restrict__ xr = xt + (size_t)(lo + r0) * kRowLd;
+                    for (int nt = 0; nt < 4; nt++) dmma_16x8x8(d[nt], af, bf[nt]);
+                    const bool lo_win = r0 == wrow, hi_win = r0 + 8 == wrow;
 #pragma unroll
-                    for (int r = 0; r < kSubW; r++) c[r] = __ldcg(xr + (size_t)r * kRowLd);
-#pragma unroll 1
-                    for (int j = 0; j < kSubW; j++) {
-                        const double xv = xs[j * kTile];
-                        const double* __restrict__ N = &sp.nrt[j][kSubW + r0];
-#pragma unroll
-                        for (int r = 0; r < kSubW; r++) c[r] = fma(N[r], xv, c[r]);
+                    for (int nt = 0; nt < 4; nt++) {
+                        if (lo_win)
+                            *reinterpret_cast<double2*>(&xsw[g * kRowLd + nt * 8 + 2 * t]) = make_double2(d[nt][0], d[nt][1]);
+                        else
+                            *reinterpret_cast<double2*>(r_lo + nt * 8) = make_double2(d[nt][0], d[nt][1]);
+                        if (hi_win)
+                            *reinterpret_cast<double2*>(&xsw[g * kRowLd + nt * 8 + 2 * t]) = make_double2(d[nt][2], d[nt][3]);
+                        else if (hi_ok)
+                            *reinterpret_cast<double2*>(r_hi + nt * 8) = make_double2(d[nt][2], d[nt][3]);
                     }
                 }
+                release_sub(buf);
+#pragma unroll
+                for (int k = 0; k < kSubW; k++) c[k] = xs[k * kRowLd];
             }
             // the pair's coefficients are read next by bulk copies (async proxy)
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.pdone[slot]);
         }
-        P.lp[s] = lpa;
-        P.d2[s] = d2a;
+        // sum (x_i - m_i)^2 / (2 sigma_i^2) = sum r_ii^2 (x_i - m_i)^2 / (2 sigma^2)
+        if (WANT_D2) {
+            P.lp[s] = d2a * P.inv_two_sigma2;
+            P.d2[s] = d2a;
+        }
         if (WANT_LZ) P.lz[s] = lza;
     }
     if (rec) {
@@ -538,7 +728,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     }
 }
 
-template <bool WANT_LZ>
+template <bool WANT_LZ, bool WANT_D2>
 __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_constant__ ChainArgs P) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ChainSmem& sm = *reinterpret_cast<ChainSmem*>(smem_raw);
@@ -552,20 +742,21 @@ __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_c
             mbar_init(&sm.pdone[s], 4);
             mbar_init(&sm.cfull[s][0], 1);
             mbar_init(&sm.cfull[s][1], 1);
+            sm.cdone[s][0] = sm.cdone[s][1] = 0;
         }
         fence_mbar_init();
     }
     __syncthreads();
-    const int wg = threadIdx.x >> 7;
-    if (wg < 2) {
+    const int tid = threadIdx.x;
+    if (tid >= kDmmaBase && tid < kDmmaBase + kDmmaThreads) {
         reg_inc<kRegsDmma>();
         dmma_role(sm, P);
-    } else if (wg == 2) {
+    } else if (tid >= kProdBase && tid < kProdBase + kProdThreads) {
         reg_dec<kRegsProd>();
-        if (threadIdx.x == kDmmaThreads) producer_role(sm, P);
+        if (tid == kProdBase) producer_role(sm, P);
     } else {
         reg_dec<kRegsPanel>();
-        panel_role<WANT_LZ>(sm, P, wg - 3);
+        panel_role<WANT_LZ, WANT_D2>(sm, P, (tid - kPanelBase) >> 7);
     }
 }
 
@@ -606,6 +797,7 @@ void chain_free(BlockedCtx& bc) {
     cudaFree(cc.Rpk);
     cudaFree(cc.Bpk);
     cudaFree(cc.tp);
+    cudaFree(cc.invr);
     cudaFree(cc.subs);
     for (auto& w : cc.work) {
         cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
@@ -646,6 +838,12 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     pack_slivers(Rup.data(), n, n, n, npad, Rpk, true);
     pack_slivers(d.B, n, n, n, npad, Bpk, false);
     for (int i = 0; i < n; i++) tp[i] = d.t[i];
+    std::vector<double> invr(npad, 1.0);
+    for (int i = 0; i < n; i++) {
+        invr[i] = 1.0 / hc.rdiag[i];
+        // the chain kernel derives sum (x-m)^2/(2 sigma_i^2) from sum r_ii^2 (x-m)^2: needs sigma_i = sigma/|r_ii| unclamped
+        if (hc.sig[i] != d.sigma / std::fabs(hc.rdiag[i])) return cudaSuccess;  // not ready: the v1 path serves
+    }
     std::vector<SubPack> subs(npad / kSubW);
     for (int gs = 0; gs < npad / kSubW; gs++) {
         SubPack& sp = subs[gs];
@@ -658,11 +856,11 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
             if (gi < n) {
                 for (int jj = 0; jj + 1 < kSubW; jj++) {
                     const int k = j - (kSubW - 1) + jj;  // sub-block-relative coordinate held by window slot jj
-                    if (k >= 0) sp.nrt[j][jj] = -d.R[(size_t)(g0 + k) * n + gi];
+                    if (k >= 0) sp.win[j][jj] = -d.R[(size_t)(g0 + k) * n + gi] * invr[g0 + k];
                 }
-                for (int r = 0; r < base; r++) sp.nrt[j][kSubW + r] = -d.R[(size_t)(lo + r) * n + gi];
+                for (int r = 0; r < base; r++) sp.rect[r][j] = -d.R[(size_t)(lo + r) * n + gi] * invr[lo + r];
                 CoordConst& c = sp.cc[j];
-                c.inv_r = 1.0 / hc.rdiag[gi];
+                c.inv_r = invr[gi];
                 c.r2 = hc.rdiag[gi] * hc.rdiag[gi];
                 c.a = hc.inv2s2[gi];
                 c.q = hc.q[gi];
@@ -670,7 +868,14 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
                 c.znorm = hc.znorm[gi];
                 c.eps1 = hc.eps1[gi];
                 c.lognz = std::log(hc.znorm[gi]);
-                sp.ci[j] = make_int4(hc.kind[gi], hc.dmax[gi], hc.uidx[gi], hc.mode[gi]);
+                // FP32 screen (samplez_smooth_screen): eligible while its error bound keeps the FP64 fallback rare
+                const double sg = hc.sig[gi];
+                const bool f32ok = hc.kind[gi] <= 1 && sg <= 16.0;
+                SmoothF32& f = sp.cf[j];
+                f.a = (float)c.a; f.sq = (float)c.sq; f.q = (float)c.q; f.znorm = (float)c.znorm; f.eps1 = (float)c.eps1;
+                f.tol_r = (float)(4e-6 + 4e-7 * sg * sg);
+                f.tol_a = (float)(1.6e-7 * c.znorm);
+                sp.ci[j] = make_int4(hc.kind[gi] | (f32ok ? 0 : 4), hc.dmax[gi], hc.uidx[gi], hc.mode[gi]);
             } else {  // padding coordinate: center 0, R_ii = 1, rounded => x = 0
                 sp.cc[j].inv_r = 1.0;
                 sp.ci[j] = make_int4(0, 0, 0, 1);
@@ -686,11 +891,17 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     if ((e = up((void**)&cc.Rpk, Rpk.data(), sizeof(double) * Rpk.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.Bpk, Bpk.data(), sizeof(double) * Bpk.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.tp, tp.data(), sizeof(double) * tp.size())) != cudaSuccess) return e;
+    if ((e = up((void**)&cc.invr, invr.data(), sizeof(double) * invr.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.subs, subs.data(), sizeof(SubPack) * subs.size())) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(klein_chain_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)sizeof(ChainSmem))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(klein_chain_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)sizeof(ChainSmem))) != cudaSuccess) return e;
+#define LGS_CHAIN_ATTR(LZ, D2)                                                                                     \
+    if ((e = cudaFuncSetAttribute(klein_chain_kernel<LZ, D2>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+                                  (int)sizeof(ChainSmem))) != cudaSuccess)                                        \
+        return e;
+    LGS_CHAIN_ATTR(false, false)
+    LGS_CHAIN_ATTR(false, true)
+    LGS_CHAIN_ATTR(true, false)
+    LGS_CHAIN_ATTR(true, true)
+#undef LGS_CHAIN_ATTR
     cc.batch = (int64_t)(bc.sm_count > 0 ? bc.sm_count : 148) * kTile * 3 * kSlots;
     cc.ready = true;
     return cudaSuccess;
@@ -715,10 +926,11 @@ static cudaError_t chain_ensure_work(ChainCtx& cc, BlockedWork& w, int64_t cap) 
 // one batch of S <= w.cap samples: coefficients into w.X (tiled), accumulators into w.lp / d2 / lz, lattice points
 // into V (may be nullptr)
 static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64_t seed, uint64_t first_id, uint32_t tag,
-                               bool want_lz, double* V, int64_t ldv, cudaStream_t st) {
+                               bool want_lz, bool want_d2, double* V, int64_t ldv, cudaStream_t st) {
     ChainCtx& cc = bc.chain;
     ChainArgs a{};
-    a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.subs = cc.subs;
+    a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.invr = cc.invr; a.subs = cc.subs;
+    a.inv_two_sigma2 = 1.0 / bc.two_sigma2;
     a.Xt = w.X; a.lp = w.lp; a.d2 = w.d2; a.lz = w.lz;
     a.V = V; a.ldv = ldv; a.S = S;
     a.npad = cc.npad; a.n_valid = bc.n;
@@ -733,8 +945,10 @@ static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64
     a.stats = want_stats ? stats_dev : nullptr;
     {
         ProfScope ps(bc.prof, LGS_PROF_CHAIN, st);
-        if (want_lz) klein_chain_kernel<true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
-        else klein_chain_kernel<false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        if (want_lz && want_d2) klein_chain_kernel<true, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        else if (want_lz) klein_chain_kernel<true, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        else if (want_d2) klein_chain_kernel<false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        else klein_chain_kernel<false, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
     }
     if (want_stats) {  // development only: synchronous read-back, mean over CTAs
         std::vector<unsigned long long> hs((size_t)grid * 8);
@@ -763,7 +977,7 @@ cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_
     if ((e = chain_ensure_work(cc, w, cap)) != cudaSuccess) return e;
     for (int64_t s0 = 0; s0 < S; s0 += w.cap) {
         const int64_t cnt = (S - s0) < w.cap ? (S - s0) : w.cap;
-        if ((e = chain_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, 0u, false, V ? V + (size_t)s0 * n : nullptr, n,
+        if ((e = chain_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, 0u, false, logq != nullptr, V ? V + (size_t)s0 * n : nullptr, n,
                              st)) != cudaSuccess) return e;
         if (X) {
             ProfScope ps(bc.prof, LGS_PROF_OTHER, st);

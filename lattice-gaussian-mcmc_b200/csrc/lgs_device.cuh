@@ -349,4 +349,79 @@ __device__ __forceinline__ double samplez_smooth(double mean, double a, double q
     return (t < cu) ? c0 + sd : c0 - sd;   // d == 0: both are c0
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Single-precision screen of samplez_smooth (chain kernel).  The same inverse transform evaluated in FP32 (24 bits of
+// the uniform, ex2-based exponentials, FP32 walk); the draw is accepted only when the target is clear of the three
+// thresholds that decide it (the cumulative sums before / inside / after the step the walk stopped at) by more than a
+// bound on everything FP32 can have got wrong: tol = tol_r * cum + tol_a, tol_a covering the 29 dropped bits of the
+// uniform, tol_r the rounding of the exponentials and of the walk.  Otherwise the caller recomputes the coordinate
+// with samplez_smooth in FP64 (a few draws in 10^5), so the map u -> x is the FP64 one bit for bit.  Why: in the chain
+// kernel the panel warps share the FP64 pipe with back-to-back DMMA, every FP64 instruction of a panel warp waits for
+// a DMMA slot, and SampleZ was 3/4 of them.
+// ---------------------------------------------------------------------------------------------------------
+struct SmoothF32 {
+    float a, sq, q, znorm, eps1, tol_r, tol_a, pad;
+};
+
+// dl = (float)(c0 - mean); uhi = the high word of the coordinate's uniform.  Returns true when certain; *off is the
+// signed offset of the draw from c0 and *corr the theta-series correction eps cos(2 pi dl) (0 for kind 0).
+__device__ __forceinline__ bool samplez_smooth_screen(float dl, const SmoothF32& k, int kind, int dmax, uint32_t uhi,
+                                                      float* off, float* corr_out) {
+    const float ad = k.a * dl;
+    const float x = -2.0f * ad;
+    const float E = __expf(x), Ei = __expf(-x);
+    const float G = __expf(ad * dl);
+    float t = (float)(uhi >> 8) * 5.9604644775390625e-8f * k.znorm;
+    float corr = 0.0f;
+    if (kind == 1) {
+        corr = k.eps1 * cos2pi_half(dl);
+        t = fmaf(t, corr, t);
+    }
+    *corr_out = corr;
+    t *= G;
+    float ru = k.sq * E, rd = k.sq * Ei;
+    float vu = 1.0f, vd = 1.0f, cum = 1.0f, cu = 2.0f, cprev = 0.0f;
+    int d = 0;
+    if (!(t < 1.0f)) {
+        do {
+            d++;
+            cprev = cum;
+            vu *= ru;
+            vd *= rd;
+            cu = cum + vu;
+            cum = cu + vd;
+            ru *= k.q;
+            rd *= k.q;
+        } while (!(t < cum) && d < dmax);
+    }
+    const float tol = fmaf(k.tol_r, cum, k.tol_a);
+    const float sd = (float)d;
+    *off = (t < cu) ? sd : -sd;
+    return (t < cum) && fabsf(t - cprev) > tol && fabsf(t - cu) > tol && fabsf(t - cum) > tol;
+}
+
+// delta = rint(mean) - mean as a float WITHOUT FP64 arithmetic: the mantissa of `mean` is shifted to a fixed-point
+// number with 32 fractional bits with integer instructions and the fraction is taken from there (absolute error
+// < 2^-32 plus one FP32 rounding, inside the screen's tolerance).  Returns false for a fraction of exactly one half
+// at that resolution (round-half-even is decided by the FP64 path) and for |mean| >= 2^31.
+__device__ __forceinline__ bool rint_delta_f32(double mean, float* dl) {
+    const uint32_t hi = (uint32_t)__double2hiint(mean), lo = (uint32_t)__double2loint(mean);
+    const int e = (int)((hi >> 20) & 0x7ffu) - 1023;
+    if (e > 30) return false;
+    if (e < -30) {  // |mean| < 2^-30: rint(mean) = 0
+        *dl = -(float)mean;
+        return true;
+    }
+    const uint64_t M = ((uint64_t)((hi & 0xfffffu) | 0x100000u) << 32) | lo;  // 1.m * 2^52
+    const int sh = e - 20;                                                    // a * 2^32 = M * 2^(e - 20)
+    const uint64_t A = sh >= 0 ? (M << sh) : (M >> (-sh));
+    const uint32_t F = (uint32_t)A;
+    if (F == 0x80000000u) return false;
+    // fraction below one half: rint = floor, delta_a = -F / 2^32; above: rint = floor + 1, delta_a = (2^32 - F) / 2^32
+    const float d = (F < 0x80000000u) ? -(float)F : (float)(0u - F);
+    const float ds = d * 2.3283064365386963e-10f;
+    *dl = (hi >> 31) ? -ds : ds;
+    return true;
+}
+
 }  // namespace lgs

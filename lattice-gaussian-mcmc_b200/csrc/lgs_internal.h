@@ -66,13 +66,17 @@ struct PanelParams {
 
 // ---- chain kernel (lgs_chain.cu): constants of one 8-coordinate sub-block, staged into shared memory by a bulk copy
 constexpr int kChainRowLd = 132;  // doubles per coordinate row of a 128-sample tile (128 + 4 padding)
+constexpr int kRectLd = 12;       // row stride of SubPack::rect (conflict-free LDS.64 A-fragment loads)
 struct SubPack {
     CoordConst cc[8];
-    int4 ci[8];          // as PanelParams::ci
-    double nrt[8][64];   // row j (coordinate base + j of its 64-block): [0..6] rotating-window triangle entries,
-                         // [8 + r] = -R[block row r][coordinate] for the rows r < base below the sub-block
+    int4 ci[8];           // as PanelParams::ci; x carries bit 2 when the coordinate is not eligible for the FP32 screen
+    SmoothF32 cf[8];      // FP32 screen constants
+    double win[8][8];     // row j: [0..6] rotating-window triangle entries of coordinate base + j
+    double rect[64][kRectLd];  // rect[r][j] = -R[lo + r][base + j] / R[lo + r][lo + r] for the rows r < base below the
+                               // sub-block (A operand of the panel warps' DMMA update), zero elsewhere; copied up to
+                               // the 16-row tile that contains row base - 1
 };
-static_assert(sizeof(SubPack) == 4736, "SubPack is copied as raw bytes");
+static_assert(sizeof(SubPack) == 7552 && sizeof(SubPack) % 16 == 0, "SubPack is copied as raw bytes");
 
 // one batch worth of device workspace for the blocked path
 struct BlockedWork {
@@ -120,6 +124,7 @@ struct ChainCtx {
     double* Rpk = nullptr;        // [npad/64][npad/16][64][20] shared-memory images of the 64 x 16 slivers of R
     double* Bpk = nullptr;        // same for the basis
     double* tp = nullptr;         // [npad]
+    double* invr = nullptr;       // [npad] 1 / R_ii
     SubPack* subs = nullptr;      // [npad/8]
     BlockedWork work[3];          // tiled: X = [cap/128][npad][132]; [0] Klein, [1]/[2] IMHK proposals
     int64_t batch = 0;            // samples per full batch: sm_count x 128 x 9
