@@ -665,6 +665,7 @@ static cudaError_t imhk_flush(BlockedCtx& bc, ChainSet& cs, cudaStream_t st) {
 
 cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin,
                                 int weight_mode, double* V, int64_t* X, cudaStream_t st) {
+    if (bc.use_chain && bc.chain.ready) return launch_imhk_chain(bc, cs, burn_in, keep, thin, weight_mode, V, X, st);
     const int64_t C = cs.chains;
     cudaError_t e;
     if ((e = ensure_blocked_chains(bc, cs)) != cudaSuccess) return e;
@@ -726,6 +727,7 @@ cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, i
 
 cudaError_t launch_imhk_blocked_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
                                           double* logw, cudaStream_t st) {
+    if (bc.use_chain && bc.chain.ready) return launch_imhk_chain_get_state(bc, cs, counts, X, V, logw, st);
     const int64_t C = cs.chains;
     cudaError_t e;
     if (counts && (e = cudaMemcpyAsync(counts, cs.counts, sizeof(int64_t) * 2 * C, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;

@@ -155,7 +155,7 @@ enum : int { F_FIRST = 1, F_LAST = 2, F_POINT = 4, F_NOSTORE = 8, F_EXIT = 16, F
 struct StageHdr {
     int flags;
     int slot;      // centers items: whose tile this is (cready[slot] is signalled by the epilogue)
-    int r0;        // first row of the 64-row block
+    int r0;        // first row of the 64-row block, bits 0..29; bit 30: which workspace (Xbuf[0 / 1]) the centers go to
     int tile;
 };
 
@@ -178,7 +178,8 @@ struct ChainArgs {
     const double* tvec;     // [npad]
     const double* invr;     // [npad] 1 / R_ii (1 on the padding): centers are kept divided by their R_ii
     const SubPack* subs;    // [npad/8] sub-block constants, index = first coordinate / 8
-    double* Xt;             // tiled coefficient workspace
+    double* Xbuf[2];        // tiled coefficient workspace(s): Klein uses [0]; an IMHK step with Philox tag g draws its
+                            // proposal into Xbuf[g & 1]
     double* lp;             // [cap] per-sample accumulators (outputs)
     double* d2;
     double* lz;
@@ -193,6 +194,17 @@ struct ChainArgs {
     uint32_t tag;
     double inv_two_sigma2;  // 1 / (2 sigma^2)
     unsigned long long* stats;  // development counters (LGS_CHAIN_STATS=1), 8 per CTA, or nullptr
+    // IMHK (imhk.py:126-177): nsteps Metropolis-Hastings steps per chain in this launch, tags tag .. tag + nsteps - 1
+    int nsteps;             // Klein: 1
+    int first_is_init;      // the first step is _initialize_chain (tag 0): no accept test, no count
+    int exact;              // LGS_WEIGHT_EXACT
+    int flush;              // after the last step every chain's current state is moved into Xcur (and, with V, its
+                            // lattice point is contracted from there)
+    double sum_lognorm;
+    double* Xcur;           // tiled current states
+    uint8_t* loc;           // [cap] where a chain's current state lives: 0 = Xcur, 1 / 2 = Xbuf[0] / Xbuf[1]
+    double* lw_cur;         // [cap] current log importance weight
+    long long* counts;      // [cap][2] accepted, total
 };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -314,12 +326,13 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
                         }
                     }
             } else {
-                double* xt = P.Xt + (size_t)h.tile * P.npad * kRowLd;
+                double* xt = P.Xbuf[(h.r0 >> 30) & 1] + (size_t)h.tile * P.npad * kRowLd;
+                const int r0 = h.r0 & 0x3fffffff;
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++)
 #pragma unroll
                     for (int hh = 0; hh < 2; hh++) {
-                        const int row = h.r0 + wm * 32 + mt * 16 + g + hh * 8;
+                        const int row = r0 + wm * 32 + mt * 16 + g + hh * 8;
                         const double tv = P.tvec[row];
                         const double ir = (h.flags & F_PART_OUT) ? 1.0 : P.invr[row];
 #pragma unroll
@@ -379,30 +392,30 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     // centers of pair p (0 = top) of a tile, rows [lo, lo + 64):
     //   part A (p >= 2): the columns of pairs 0 .. p - 2, issued ahead (look-ahead), parks t - acc in the rows;
     //   part B (p >= 1): the 64 columns of pair p - 1, finishes the centers and wakes the panel warpgroup.
-    auto issue_range = [&](int flags, int slot, int lo, int tile, int c0, int c1) {
+    auto issue_range = [&](int flags, int slot, int lo, int tile, int xsel, int c0, int c1) {
         const int rt = lo / kPair;
         const int kt0 = c0 / kBK, kt1 = c1 / kBK;
         const double* a = P.Rpk + ((size_t)rt * nkt + kt0) * (kPair * kLdA);
-        const double* b = P.Xt + (size_t)tile * P.npad * kRowLd + (size_t)kt0 * kBK * kRowLd;
+        const double* b = P.Xbuf[xsel] + (size_t)tile * P.npad * kRowLd + (size_t)kt0 * kBK * kRowLd;
         for (int kt = kt0; kt < kt1; kt++, a += kPair * kLdA, b += kBK * kRowLd)
-            push(flags | (kt == kt0 ? F_FIRST : 0) | (kt == kt1 - 1 ? F_LAST : 0), slot, lo, tile, a, b);
+            push(flags | (kt == kt0 ? F_FIRST : 0) | (kt == kt1 - 1 ? F_LAST : 0), slot, lo | (xsel << 30), tile, a, b);
     };
-    auto issue_A = [&](int slot, int p, int tile) {
+    auto issue_A = [&](int slot, int p, int tile, int xsel) {
         const int lo = P.npad - kPair * (p + 1);
-        issue_range(F_PART_OUT, slot, lo, tile, lo + 2 * kPair, P.npad);
+        issue_range(F_PART_OUT, slot, lo, tile, xsel, lo + 2 * kPair, P.npad);
     };
-    auto issue_B = [&](int slot, int p, int tile) {
+    auto issue_B = [&](int slot, int p, int tile, int xsel) {
         const int lo = P.npad - kPair * (p + 1);
         if (p == 0) {
-            push(F_FIRST | F_LAST | F_NODATA, slot, lo, tile, nullptr, nullptr);
+            push(F_FIRST | F_LAST | F_NODATA, slot, lo | (xsel << 30), tile, nullptr, nullptr);
             return;
         }
-        issue_range(p >= 2 ? F_PART_IN : 0, slot, lo, tile, lo + kPair, lo + 2 * kPair);
+        issue_range(p >= 2 ? F_PART_IN : 0, slot, lo, tile, xsel, lo + kPair, lo + 2 * kPair);
     };
-    // 64 rows of the lattice points of a finished tile
+    // 64 rows of the lattice points of a finished tile (Klein: from its workspace; IMHK: from the current states)
     auto issue_point = [&](int tile, int rt) {
         const double* a = P.Bpk + (size_t)rt * nkt * (kPair * kLdA);
-        const double* b = P.Xt + (size_t)tile * P.npad * kRowLd;
+        const double* b = (P.flush ? P.Xcur : P.Xbuf[0]) + (size_t)tile * P.npad * kRowLd;
         for (int kt = 0; kt < nkt; kt++, a += kPair * kLdA, b += kBK * kRowLd)
             push(F_POINT | (kt == 0 ? F_FIRST : 0) | (kt == nkt - 1 ? F_LAST : 0), 0, rt * kPair, tile, a, b);
     };
@@ -410,17 +423,28 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     int next_tile = blockIdx.x;
     int s_pair[kSlots], s_tile[kSlots];   // s_pair: pairs whose centers have been completed (part B issued)
     int s_ahead[kSlots];                  // next pair whose part A has not been issued yet
+    int s_step[kSlots];                   // Metropolis-Hastings step of the launch the slot's tile is in (Klein: 0)
     uint32_t pd_par[kSlots];
     bool s_active[kSlots];
     int n_active = 0;
+    auto xsel_of = [&](int step) { return (int)((P.tag + (uint32_t)step) & 1u); };
+    auto start_step = [&](int s) {
+        s_pair[s] = 1;
+        s_ahead[s] = 2;
+        issue_B(s, 0, s_tile[s], xsel_of(s_step[s]));
+    };
     auto assign = [&](int s) {
         if (next_tile < P.ntiles) {
             s_tile[s] = next_tile;
             next_tile += G;
-            s_pair[s] = 1;
-            s_ahead[s] = 2;
+            s_step[s] = 0;
             sm.slot_tile[s] = s_tile[s];
-            issue_B(s, 0, s_tile[s]);
+            if (P.nsteps > 0) {
+                start_step(s);
+            } else {  // no step, only the flush (+ lattice points) of the current states: wake the panel warpgroup
+                s_pair[s] = npairs;
+                push(F_FIRST | F_LAST | F_NODATA | F_NOSTORE, s, 0, s_tile[s], nullptr, nullptr);
+            }
         } else {
             s_active[s] = false;
             n_active--;
@@ -447,15 +471,21 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
                 if (!s_active[s] || !mbar_test_wait(&sm.pdone[s], pd_par[s])) continue;
                 pd_par[s] ^= 1;
                 if (s_pair[s] == npairs) {
-                    if (P.V) { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
-                    assign(s);
+                    if (s_step[s] + 1 < P.nsteps) {  // next Metropolis-Hastings step of the same chains
+                        s_step[s]++;
+                        start_step(s);
+                    } else {
+                        if (P.V) { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
+                        assign(s);
+                    }
                 } else {
                     const int pr = s_pair[s];  // its panel may start once part B is through
+                    const int xs_ = xsel_of(s_step[s]);
                     if (pr >= 2 && s_ahead[s] <= pr) {
-                        issue_A(s, pr, s_tile[s]);
+                        issue_A(s, pr, s_tile[s], xs_);
                         s_ahead[s] = pr + 1;
                     }
-                    issue_B(s, pr, s_tile[s]);
+                    issue_B(s, pr, s_tile[s], xs_);
                     s_pair[s]++;
                 }
                 rr = s + 1;
@@ -469,7 +499,7 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
         for (int i = 0; i < kSlots; i++) {
             const int s = (ra + i) % kSlots;
             if (!s_active[s] || s_ahead[s] > s_pair[s] || s_ahead[s] >= npairs) continue;
-            issue_A(s, s_ahead[s], s_tile[s]);
+            issue_A(s, s_ahead[s], s_tile[s], xsel_of(s_step[s]));
             s_ahead[s]++;
             ra = s + 1;
             progressed = true;
@@ -510,7 +540,7 @@ __device__ __noinline__ double chain_samplez_fast_call(double mean, double inv2s
     return (double)samplez_fast(mean, fz, u, zsum);
 }
 
-template <bool WANT_LZ, bool WANT_D2>
+template <bool WANT_LZ, bool WANT_D2, bool IMHK>
 __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, const int slot) {
     const int sl = (threadIdx.x - kPanelBase) & 127;
     const int lane = threadIdx.x & 31;
@@ -534,20 +564,47 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
         cr_par ^= 1;
         const int tile = sm.slot_tile[slot];
         if (tile < 0) break;
-        // constants of sub-block i of a tile (i = 0 is the top one): SubPack nsub - 1 - i, rows below = 8 (7 - i % 8)
+        // constants of sub-block i of a step (i = 0 is the top one): SubPack nsub - 1 - i, rows below = 8 (7 - i % 8)
         auto load_sub = [&](int i, uint32_t qq) {
             const uint32_t nb = sub_bytes(kSubW * (7 - (i & 7)));
             mbar_arrive_expect_tx(&sm.cfull[slot][qq & 1], nb);
             bulk_g2s(&sm.sub[slot][qq & 1], &P.subs[nsub - 1 - i], nb, &sm.cfull[slot][qq & 1]);
         };
-        if (sl == 0) {  // every warp of the slot has finished the previous tile (pdone -> scheduler -> cready)
+        const int64_t s = (int64_t)tile * kTile + sl;
+        const uint64_t id = P.first_id + (uint64_t)s;
+        // IMHK chain state of this thread's chain (imhk.py:126-177)
+        double lw = 0.0;
+        int loc = 0, acc_n = 0, tot_n = 0;
+        if (IMHK && s < P.S) {
+            lw = P.lw_cur[s];
+            loc = P.loc[s];
+        }
+        // column copy of one chain's coefficients between tiled matrices (predicated per lane, coalesced per row)
+        auto copy_column = [&](const double* __restrict__ src, double* __restrict__ dst) {
+            const size_t o = (size_t)tile * P.npad * kRowLd + sl;
+#pragma unroll 8
+            for (int i = 0; i < P.npad; i++) dst[o + (size_t)i * kRowLd] = src[o + (size_t)i * kRowLd];
+        };
+        if (IMHK && P.nsteps == 0) {  // flush only
+            if (loc) copy_column(P.Xbuf[loc - 1], P.Xcur);
+            loc = 0;
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.pdone[slot]);
+        }
+#pragma unroll 1
+        for (int step = 0; step < P.nsteps; step++) {
+        if (step > 0) {
+            mbar_wait(&sm.cready[slot], cr_par);
+            cr_par ^= 1;
+        }
+        if (sl == 0) {  // every warp of the slot has finished the previous step (pdone -> scheduler -> cready)
             load_sub(0, q);
             load_sub(1, q + 1);
         }
         int isub = 0;
-        const int64_t s = (int64_t)tile * kTile + sl;
-        const uint64_t id = P.first_id + (uint64_t)s;
-        double* __restrict__ xtile = P.Xt + (size_t)tile * P.npad * kRowLd;
+        const uint32_t tagv = P.tag + (uint32_t)step;
+        double* __restrict__ xtile = P.Xbuf[tagv & 1] + (size_t)tile * P.npad * kRowLd;
         double* __restrict__ xt = xtile + sl;
         double d2a = 0.0, lza = 0.0;
         uint4 w = make_uint4(0, 0, 0, 0);
@@ -605,7 +662,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     } else {
                         if ((ci.z >> 1) != wpair) {
                             wpair = ci.z >> 1;
-                            w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, P.tag);
+                            w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, tagv);
                         }
                         const bool odd = ci.z & 1;
                         const uint32_t uhi = odd ? w.z : w.x, ulo = odd ? w.w : w.y;
@@ -710,17 +767,58 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
 #pragma unroll
                 for (int k = 0; k < kSubW; k++) c[k] = xs[k * kRowLd];
             }
+            if (IMHK && p == npairs - 1) {
+                // imhk.py:102-124 + 156-174.  Reference weights: log rho(v) - log q(v) is the constant sum_lognorm
+                // here (both are the same sum r_ii^2 (x_i - m_i)^2 / (2 sigma^2)): always accepted, as the reference.
+                const int buf = 1 + (int)(tagv & 1);
+                const double lw_prop = P.exact ? lza : P.sum_lognorm;
+                if (P.first_is_init && step == 0) {
+                    lw = lw_prop;
+                    loc = buf;
+                } else {
+                    bool acc = true;
+                    if (P.exact) {
+                        const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
+                        acc = philox_uniform(gen, id, kAcceptDraw, tagv) < ratio;
+                    }
+                    tot_n++;
+                    if (acc) {
+                        acc_n++;
+                        lw = lw_prop;
+                        loc = buf;
+                    }
+                }
+                // The accepted proposal is not copied: loc records the buffer it lives in.  A state still living in the
+                // buffer the NEXT step draws into moves to Xcur now (before that step's first centers are written);
+                // at a flush every state moves there.
+                const int nbuf = 1 + (int)((tagv + 1) & 1);
+                if (loc && (loc == nbuf || (P.flush && step == P.nsteps - 1))) {
+                    copy_column(P.Xbuf[loc - 1], P.Xcur);
+                    loc = 0;
+                }
+            }
             // the pair's coefficients are read next by bulk copies (async proxy)
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.pdone[slot]);
         }
-        // sum (x_i - m_i)^2 / (2 sigma_i^2) = sum r_ii^2 (x_i - m_i)^2 / (2 sigma^2)
-        if (WANT_D2) {
-            P.lp[s] = d2a * P.inv_two_sigma2;
-            P.d2[s] = d2a;
+        if (!IMHK) {
+            // sum (x_i - m_i)^2 / (2 sigma_i^2) = sum r_ii^2 (x_i - m_i)^2 / (2 sigma^2)
+            if (WANT_D2) {
+                P.lp[s] = d2a * P.inv_two_sigma2;
+                P.d2[s] = d2a;
+            }
+            if (WANT_LZ) P.lz[s] = lza;
         }
-        if (WANT_LZ) P.lz[s] = lza;
+        }  // steps
+        if (IMHK && s < P.S) {
+            P.lw_cur[s] = lw;
+            P.loc[s] = (uint8_t)loc;
+            if (tot_n) {
+                P.counts[2 * s] += acc_n;
+                P.counts[2 * s + 1] += tot_n;
+            }
+        }
     }
     if (rec) {
         P.stats[blockIdx.x * 8 + 5] = (unsigned long long)(clock64() - t_begin);
@@ -728,7 +826,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     }
 }
 
-template <bool WANT_LZ, bool WANT_D2>
+template <bool WANT_LZ, bool WANT_D2, bool IMHK>
 __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_constant__ ChainArgs P) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ChainSmem& sm = *reinterpret_cast<ChainSmem*>(smem_raw);
@@ -756,7 +854,7 @@ __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_c
         if (tid == kProdBase) producer_role(sm, P);
     } else {
         reg_dec<kRegsPanel>();
-        panel_role<WANT_LZ, WANT_D2>(sm, P, (tid - kPanelBase) >> 7);
+        panel_role<WANT_LZ, WANT_D2, IMHK>(sm, P, (tid - kPanelBase) >> 7);
     }
 }
 
@@ -893,14 +991,14 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     if ((e = up((void**)&cc.tp, tp.data(), sizeof(double) * tp.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.invr, invr.data(), sizeof(double) * invr.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.subs, subs.data(), sizeof(SubPack) * subs.size())) != cudaSuccess) return e;
-#define LGS_CHAIN_ATTR(LZ, D2)                                                                                     \
-    if ((e = cudaFuncSetAttribute(klein_chain_kernel<LZ, D2>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+#define LGS_CHAIN_ATTR(LZ, D2, MH)                                                                                 \
+    if ((e = cudaFuncSetAttribute(klein_chain_kernel<LZ, D2, MH>, cudaFuncAttributeMaxDynamicSharedMemorySize,    \
                                   (int)sizeof(ChainSmem))) != cudaSuccess)                                        \
         return e;
-    LGS_CHAIN_ATTR(false, false)
-    LGS_CHAIN_ATTR(false, true)
-    LGS_CHAIN_ATTR(true, false)
-    LGS_CHAIN_ATTR(true, true)
+    LGS_CHAIN_ATTR(false, false, false)
+    LGS_CHAIN_ATTR(false, true, false)
+    LGS_CHAIN_ATTR(false, false, true)
+    LGS_CHAIN_ATTR(true, false, true)
 #undef LGS_CHAIN_ATTR
     cc.batch = (int64_t)(bc.sm_count > 0 ? bc.sm_count : 148) * kTile * 3 * kSlots;
     cc.ready = true;
@@ -923,20 +1021,15 @@ static cudaError_t chain_ensure_work(ChainCtx& cc, BlockedWork& w, int64_t cap) 
     return cudaSuccess;
 }
 
-// one batch of S <= w.cap samples: coefficients into w.X (tiled), accumulators into w.lp / d2 / lz, lattice points
-// into V (may be nullptr)
-static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64_t seed, uint64_t first_id, uint32_t tag,
-                               bool want_lz, bool want_d2, double* V, int64_t ldv, cudaStream_t st) {
+// one launch of the chain kernel
+static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool want_lz, bool want_d2, cudaStream_t st) {
     ChainCtx& cc = bc.chain;
-    ChainArgs a{};
     a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.invr = cc.invr; a.subs = cc.subs;
     a.inv_two_sigma2 = 1.0 / bc.two_sigma2;
-    a.Xt = w.X; a.lp = w.lp; a.d2 = w.d2; a.lz = w.lz;
-    a.V = V; a.ldv = ldv; a.S = S;
+    a.sum_lognorm = bc.sum_lognorm;
     a.npad = cc.npad; a.n_valid = bc.n;
-    a.ntiles = (int)((S + kTile - 1) / kTile);
+    a.ntiles = (int)((a.S + kTile - 1) / kTile);
     a.want_lz = want_lz ? 1 : 0;
-    a.seed = seed; a.first_id = first_id; a.tag = tag;
     const int sms = bc.sm_count > 0 ? bc.sm_count : 148;
     const int grid = a.ntiles < sms ? a.ntiles : sms;
     static const bool want_stats = getenv("LGS_CHAIN_STATS") != nullptr;
@@ -945,10 +1038,10 @@ static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64
     a.stats = want_stats ? stats_dev : nullptr;
     {
         ProfScope ps(bc.prof, LGS_PROF_CHAIN, st);
-        if (want_lz && want_d2) klein_chain_kernel<true, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
-        else if (want_lz) klein_chain_kernel<true, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
-        else if (want_d2) klein_chain_kernel<false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
-        else klein_chain_kernel<false, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        if (imhk && want_lz) klein_chain_kernel<true, false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        else if (imhk) klein_chain_kernel<false, false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        else if (want_d2) klein_chain_kernel<false, true, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        else klein_chain_kernel<false, false, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
     }
     if (want_stats) {  // development only: synchronous read-back, mean over CTAs
         std::vector<unsigned long long> hs((size_t)grid * 8);
@@ -958,12 +1051,25 @@ static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64
         for (int b = 0; b < grid; b++)
             for (int k = 0; k < 8; k++) m[k] += (double)hs[(size_t)b * 8 + k] / grid;
         fprintf(stderr,
-                "[chain stats] grid %d tiles %d V=%d | dmma total %.0f kcyc, wait-full %.0f (%.1f%%), stages %.0f | producer "
-                "wait-empty %.0f idle %.0f | panel0 total %.0f wait-centers %.0f (%.1f%%)\n",
-                grid, a.ntiles, V ? 1 : 0, m[0] / 1e3, m[1] / 1e3, 100.0 * m[1] / (m[0] + 1), m[2], m[3] / 1e3, m[4] / 1e3,
-                m[5] / 1e3, m[6] / 1e3, 100.0 * m[6] / (m[5] + 1));
+                "[chain stats] grid %d tiles %d V=%d steps=%d | dmma total %.0f kcyc, wait-full %.0f (%.1f%%), stages %.0f | "
+                "producer wait-empty %.0f idle %.0f | panel0 total %.0f wait-centers %.0f (%.1f%%)\n",
+                grid, a.ntiles, a.V ? 1 : 0, a.nsteps, m[0] / 1e3, m[1] / 1e3, 100.0 * m[1] / (m[0] + 1), m[2], m[3] / 1e3,
+                m[4] / 1e3, m[5] / 1e3, m[6] / 1e3, 100.0 * m[6] / (m[5] + 1));
     }
     return cudaGetLastError();
+}
+
+// one batch of S <= w.cap samples: coefficients into w.X (tiled), accumulators into w.lp / d2, lattice points into V
+// (may be nullptr)
+static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64_t seed, uint64_t first_id,
+                               bool want_d2, double* V, int64_t ldv, cudaStream_t st) {
+    ChainArgs a{};
+    a.Xbuf[0] = a.Xbuf[1] = w.X;
+    a.lp = w.lp; a.d2 = w.d2; a.lz = w.lz;
+    a.V = V; a.ldv = ldv; a.S = S;
+    a.seed = seed; a.first_id = first_id; a.tag = 0u;
+    a.nsteps = 1;
+    return chain_launch(bc, a, false, false, want_d2, st);
 }
 
 cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
@@ -977,7 +1083,7 @@ cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_
     if ((e = chain_ensure_work(cc, w, cap)) != cudaSuccess) return e;
     for (int64_t s0 = 0; s0 < S; s0 += w.cap) {
         const int64_t cnt = (S - s0) < w.cap ? (S - s0) : w.cap;
-        if ((e = chain_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, 0u, false, logq != nullptr, V ? V + (size_t)s0 * n : nullptr, n,
+        if ((e = chain_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, logq != nullptr, V ? V + (size_t)s0 * n : nullptr, n,
                              st)) != cudaSuccess) return e;
         if (X) {
             ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
@@ -989,6 +1095,134 @@ cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_
             chain_finish_logq_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(w.lp, bc.sum_lognorm, cnt, logq + s0);
         }
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// IMHK on the chain kernel (imhk.py:126-229): all chains of the handle, `nsteps` Metropolis-Hastings steps per launch.
+// A launch ends at a kept step when kept states are wanted: its last step moves every current state into Xcur and
+// the lattice points are contracted from there inside the same launch.
+// ---------------------------------------------------------------------------------------------------------
+static cudaError_t chain_ensure_chains(BlockedCtx& bc, ChainSet& cs) {
+    ChainCtx& cc = bc.chain;
+    const int64_t cap = (cs.chains + kTile - 1) / kTile * kTile;
+    cudaError_t e;
+    if (!(cs.bl_cap >= cap && cs.Xcur)) {
+        cudaFree(cs.Xcur);
+        cudaFree(cs.flags);
+        cs.Xcur = nullptr;
+        cs.flags = nullptr;
+        cs.bl_cap = 0;
+        const size_t xbytes = sizeof(double) * (size_t)(cap / kTile) * cc.npad * kRowLd;
+        if ((e = cudaMalloc(&cs.Xcur, xbytes)) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&cs.flags, cap)) != cudaSuccess) return e;
+        if ((e = cudaMemset(cs.Xcur, 0, xbytes)) != cudaSuccess) return e;
+        if ((e = cudaMemset(cs.flags, 0, cap)) != cudaSuccess) return e;
+        cs.bl_cap = cap;
+    }
+    for (int b = 1; b <= 2; b++) {
+        BlockedWork& w = cc.work[b];
+        if (w.cap != cs.bl_cap) {
+            cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
+            w = BlockedWork{};
+            if ((e = chain_ensure_work(cc, w, cs.bl_cap)) != cudaSuccess) return e;
+        }
+    }
+    return cudaSuccess;
+}
+
+static void chain_imhk_args(BlockedCtx& bc, ChainSet& cs, ChainArgs& a, int weight_mode) {
+    ChainCtx& cc = bc.chain;
+    a.Xbuf[0] = cc.work[1].X;   // proposals of even tags (buffer id 1)
+    a.Xbuf[1] = cc.work[2].X;   // proposals of odd tags (buffer id 2)
+    a.Xcur = cs.Xcur;
+    a.loc = cs.flags;
+    a.lw_cur = cs.logw;
+    a.counts = reinterpret_cast<long long*>(cs.counts);
+    a.S = cs.chains;
+    a.seed = cs.seed;
+    a.first_id = cs.first_id;
+    a.exact = weight_mode == LGS_WEIGHT_EXACT ? 1 : 0;
+}
+
+cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
+                              double* V, int64_t* X, cudaStream_t st) {
+    cudaError_t e;
+    if ((e = chain_ensure_chains(bc, cs)) != cudaSuccess) return e;
+    const bool exact = weight_mode == LGS_WEIGHT_EXACT;
+    const int64_t C = cs.chains;
+    const int n = bc.n;
+    constexpr int64_t kMaxSteps = 64;  // steps per launch when nothing is kept (bounds one launch to well under a second)
+    // run `cnt` steps (the first may be the initial state); flush != 0: kept state number kidx ends the launch
+    auto segment = [&](int64_t cnt, bool flush, int64_t kidx) -> cudaError_t {
+        while (cnt > 0 || flush || !cs.bl_init) {
+            const bool init = !cs.bl_init;
+            int64_t now = cnt + (init ? 1 : 0);
+            bool last = true;
+            if (now > kMaxSteps) { now = kMaxSteps; last = false; }
+            ChainArgs a{};
+            chain_imhk_args(bc, cs, a, weight_mode);
+            a.first_is_init = init ? 1 : 0;
+            a.tag = init ? 0u : (uint32_t)(cs.bl_steps + 1);
+            a.nsteps = (int)now;
+            a.flush = (flush && last) ? 1 : 0;
+            if (a.flush && V) { a.V = V + (size_t)kidx * n; a.ldv = keep * (int64_t)n; }
+            cudaError_t er = chain_launch(bc, a, true, exact, false, st);
+            if (er != cudaSuccess) return er;
+            const int64_t done = now - (init ? 1 : 0);
+            cs.bl_steps += done;
+            cs.bl_init = true;
+            cnt -= done;
+            if (a.flush && X) {
+                ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+                dim3 grid((unsigned)((C + 31) / 32), (unsigned)((n + 31) / 32));
+                export_coeffs_tiled_kernel<<<grid, 256, 0, st>>>(cs.Xcur, bc.chain.npad, n, C, X + (size_t)kidx * n,
+                                                                 keep * (int64_t)n);
+                if ((er = cudaGetLastError()) != cudaSuccess) return er;
+            }
+            if (last) break;
+        }
+        return cudaSuccess;
+    };
+    if (!cs.bl_init) {
+        if ((e = cudaMemsetAsync(cs.flags, 0, (size_t)cs.bl_cap, st)) != cudaSuccess) return e;
+    }
+    const bool want_states = (V || X) && keep > 0;
+    if (!want_states) {
+        const int64_t steps = burn_in + keep * thin;
+        if (steps > 0 || !cs.bl_init) return segment(steps, false, 0);
+        return cudaSuccess;
+    }
+    if (burn_in > 0 || !cs.bl_init) {
+        if ((e = segment(burn_in, false, 0)) != cudaSuccess) return e;
+    }
+    for (int64_t k = 0; k < keep; k++)
+        if ((e = segment(thin, true, k)) != cudaSuccess) return e;
+    return cudaSuccess;
+}
+
+cudaError_t launch_imhk_chain_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
+                                        double* logw, cudaStream_t st) {
+    const int64_t C = cs.chains;
+    const int n = bc.n;
+    cudaError_t e;
+    if (counts && (e = cudaMemcpyAsync(counts, cs.counts, sizeof(int64_t) * 2 * C, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
+    if (logw && (e = cudaMemcpyAsync(logw, cs.logw, sizeof(double) * C, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
+    if (X || V) {
+        if ((e = chain_ensure_chains(bc, cs)) != cudaSuccess) return e;
+        ChainArgs a{};
+        chain_imhk_args(bc, cs, a, LGS_WEIGHT_REFERENCE);
+        a.nsteps = 0;
+        a.flush = 1;
+        a.V = V;
+        a.ldv = n;
+        if ((e = chain_launch(bc, a, true, false, false, st)) != cudaSuccess) return e;
+        if (X) {
+            dim3 grid((unsigned)((C + 31) / 32), (unsigned)((n + 31) / 32));
+            export_coeffs_tiled_kernel<<<grid, 256, 0, st>>>(cs.Xcur, bc.chain.npad, n, C, X, n);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        }
     }
     return cudaSuccess;
 }

@@ -210,5 +210,9 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc);
 void chain_free(BlockedCtx& bc);
 cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
                                double* logq, cudaStream_t st);
+cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
+                              double* V, int64_t* X, cudaStream_t st);
+cudaError_t launch_imhk_chain_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
+                                        double* logw, cudaStream_t st);
 
 }  // namespace lgs
