@@ -4,10 +4,11 @@
     python bench.py --gpus N --steps K --warmup W            # our arm (one process per GPU; torchrun for N > 1)
     python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithm (oracle port), rank 0 only
 
-One "step" of the Klein leg = one batch of 2^17 samples per GPU through the hot path (lgs_klein_sample: blocked fp64
-back-substitution + SampleZ + lattice points), output resident in HBM.  One step of the IMHK leg = 10 MH steps of 2^17
-chains per GPU (lgs_imhk_run, thin = 10, the kept state written as a lattice point), followed by the NCCL all-reduce of
-the accept counters and marginal histograms.  Independent samples / chains are sharded over ranks by global id
+One "step" of the Klein leg = one batch of 170 496 samples per GPU (lgs_preferred_batch: 148 SMs x 9 tiles x 128)
+through the hot path (lgs_klein_sample: blocked fp64 back-substitution + SampleZ + lattice points, one persistent
+kernel), output resident in HBM.  One step of the IMHK leg = 10 MH steps of as many chains per GPU (lgs_imhk_run,
+thin = 10, the kept state written as a lattice point), followed by the NCCL all-reduce of the accept counters and
+marginal histograms.  Independent samples / chains are sharded over ranks by global id
 (Philox key = seed, counter = global id): no data-path collective, weak scaling.
 
 Prints ONE JSON line (rank 0).  `value` = Klein samples/s over all GPUs; the IMHK figure rides in "imhk".
@@ -30,6 +31,8 @@ sys.path.insert(0, ROOT)
 N_RING, Q, SIGMA = 512, 12289, 165.74          # NTRU n = 512, q = 12289; sampler sigma = Falcon-512's
 DIM = 2 * N_RING
 KLEIN_FLOP = 3 * DIM * DIM - DIM                # back-substitution n(n-1) + lattice point 2n^2   
+NCU_TRAFFIC_BYTES = 37.72e9                     # dram read 33.74 GB + write 3.98 GB per launch of the chain kernel at
+                                                # S = 170 496 (profiles/r01c_ncu_full_summary.json)
 
 
 def imhk_flop(thin):                             # proposal back-substitution + two quadratic forms + kept point / thin
@@ -120,9 +123,9 @@ def run_reference(args, rank, world):
     lat = build_lattice()
     cores = os.cpu_count() or 1
     prob = oracle.Problem(lat.basis, SIGMA)
-    S = 256 * cores                                                    # bounded sample per step (~0.3 s)
+    S = 2048 * cores                                                   # bounded sample per step (~3 s on 16 cores)
     for w in range(args.warmup):
-        oracle.klein_seeded(prob, cores, seed=100 + w, chains=cores, threads=cores)
+        oracle.klein_seeded(prob, S // 8, seed=100 + w, chains=cores, want_v=True, threads=cores)
     t0 = time.perf_counter()
     for k in range(args.steps):
         oracle.klein_seeded(prob, S, seed=200 + k, chains=cores, want_v=True, threads=cores)
@@ -152,8 +155,8 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--log2-samples", type=int, default=17, help="Klein samples per GPU per step")
-    ap.add_argument("--log2-chains", type=int, default=17, help="IMHK chains per GPU")
+    ap.add_argument("--samples", type=int, default=0, help="Klein samples per GPU per step (0: lgs_preferred_batch)")
+    ap.add_argument("--chains", type=int, default=0, help="IMHK chains per GPU (0: lgs_preferred_batch)")
     ap.add_argument("--thin", type=int, default=10)
     ap.add_argument("--skip-imhk", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
@@ -181,12 +184,12 @@ def main():
 
     W = max(args.warmup, 3)
     K = args.steps
-    S = 1 << args.log2_samples
-    C = 1 << args.log2_chains
     n = DIM
     lat = build_lattice()
     smp = lgs.KleinSampler(lat, SIGMA, seed=2026, device=local, path="blocked")
     eng = smp._engine
+    S = args.samples or eng.preferred_batch
+    C = args.chains or eng.preferred_batch
     stream = torch.cuda.current_stream().cuda_stream
     V = torch.empty((S, n), dtype=torch.float64, device="cuda")
     clocks = ClockSampler(local)
@@ -234,9 +237,16 @@ def main():
     prof = eng.profile_read()
     eng.profile_enable(False)
     launches_per_step = sum(c for _, c in prof.values()) // K
-    pt_ms, pt_cnt = prof["point"]
     peak, peak_src = fp64_peak()
-    pt_flop = 2.0 * n * n * S                            # algorithmic flops of one lattice-point launch: 2 n^2 per sample
+    if prof["chain"][1] > 0:        # the persistent chain kernel does the whole sample: (3 n^2 - n) flop per sample
+        pt_ms, pt_cnt = prof["chain"]
+        pt_flop = float(KLEIN_FLOP) * S
+        kernel_name = ("klein_chain_kernel (persistent, warp-specialised: centers + SampleZ panels + lattice points; "
+                       "fp64 DMMA fed by cp.async.bulk)")
+    else:                           # LGS_CHAIN=0: the multi-kernel v1 path, dominant kernel = the lattice-point contraction
+        pt_ms, pt_cnt = prof["point"]
+        pt_flop = 2.0 * n * n * S
+        kernel_name = "contract_kernel<64, MODE_POINT> (V = X B^T, fp64 DMMA)"
     pt_tf = pt_flop / (pt_ms / pt_cnt * 1e-3) * 1e-12
     share = {k: round(v[0] / max(sum(x[0] for x in prof.values()), 1e-9), 4) for k, v in prof.items()}
 
@@ -326,18 +336,17 @@ def main():
             "config": {"workload": f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim, exact NTRUSolve, seed 0), "
                                    f"sampler sigma={SIGMA}, Klein sampling + IMHK",
                        "samples_per_gpu_per_step": S, "cond_sigma_range": [float(SIGMA / gs.max()), float(SIGMA / gs.min())],
-                       "l2_policy": "each step writes S x n fp64 = %.2f GB of fresh output (> 126 MB L2) and re-reads "
-                                    "its 1 GB coefficient matrix" % (S * n * 8 / 1e9),
+                       "l2_policy": "each step writes S x n fp64 = %.2f GB of fresh output (> 126 MB L2) and streams "
+                                    "its %.2f GB tiled coefficient workspace" % (S * n * 8 / 1e9, S * n * 8.25 / 1e9),
                        "parallelism": f"independent sample ranges per GPU x{world}, no data-path collective"},
             "fp64_tflops_per_gpu": klein_rate / world * KLEIN_FLOP * 1e-12,
             "fp64_frac_of_peak": klein_rate / world * KLEIN_FLOP * 1e-12 / peak,
-            "roofline": {"bound": "tensor", "kernel": "contract_kernel<64, MODE_POINT> (V = X B^T, fp64 DMMA)",
+            "roofline": {"bound": "tensor", "kernel": kernel_name,
                          "achieved": pt_tf, "peak": peak, "unit": "TFLOP/s", "frac": pt_tf / peak,
                          "peak_source": peak_src,
                          # dram__bytes_read.sum + dram__bytes_write.sum of this kernel per launch from the ncu
-                         # --set full capture of this command at S = 2^17 (profiles/r01b_ncu_full_summary.json):
-                         # 1.084 GB + 1.041 GB, against 2 * 8 n S = 2.147 GB of algorithmic X-read + V-write
-                         "traffic": 2.125e9 if (S == 1 << 17 and n == 1024) else None,
+                         # --set full capture of this command (profiles/r01c_ncu_full_summary.json)
+                         "traffic": NCU_TRAFFIC_BYTES if (S == 170496 and n == 1024 and prof["chain"][1] > 0) else None,
                          "algorithmic_flop_per_launch": pt_flop, "avg_launch_ms": pt_ms / pt_cnt,
                          "share_of_step": share},
             "gpu_launches": int(launches_per_step * K),

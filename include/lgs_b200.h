@@ -92,6 +92,13 @@ LGS_API const char *lgs_last_error(const lgs_handle *h); /* h may be NULL: last 
 LGS_API int lgs_uniforms_per_sample(const lgs_handle *h);
 
 /*
+ * Samples (or chains) per call that fill the device evenly: the blocked path works on tiles of 128 samples and a
+ * full batch gives every SM the same whole number of tiles (148 SMs x 9 tiles x 128 = 170 496 on a B200).  Any S is
+ * accepted by the sampling calls; multiples of this figure run at the quoted throughput.  No reference counterpart.
+ */
+LGS_API int64_t lgs_preferred_batch(const lgs_handle *h);
+
+/*
  * KleinSampler.sample(S) (klein.py:324-337 -> sample_single 181-220), native RNG.
  * Sample s uses Philox4x32-10 with key = seed and counter = (first_sample_id + s, draw pair, 0): the output does
  * not depend on how [0, S) is split over calls, streams or GPUs.

@@ -52,6 +52,7 @@ PROTOTYPES = {
     "lgs_destroy": (None, [vp]),
     "lgs_last_error": (ctypes.c_char_p, [vp]),
     "lgs_uniforms_per_sample": (ctypes.c_int, [vp]),
+    "lgs_preferred_batch": (ctypes.c_int64, [vp]),
     "lgs_klein_sample": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, vp, vp, vp, vp]),
     "lgs_klein_replay": (ctypes.c_int, [vp, ctypes.c_int64, vp, vp, vp, vp, vp, vp]),
     "lgs_klein_sample_host": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, vp, vp, vp]),

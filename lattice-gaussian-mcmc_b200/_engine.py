@@ -48,6 +48,7 @@ class Engine:
         self._h = h
         self.device = int(device)
         self.ups = int(self._lib.lgs_uniforms_per_sample(self._h))
+        self.preferred_batch = int(self._lib.lgs_preferred_batch(self._h))
         self.chains = 0
 
     def close(self):

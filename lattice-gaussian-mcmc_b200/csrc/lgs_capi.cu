@@ -211,6 +211,13 @@ void lgs_destroy(lgs_handle* h) {
 
 int lgs_uniforms_per_sample(const lgs_handle* h) { return h ? h->ctx.ups : LGS_E_INVALID; }
 
+int64_t lgs_preferred_batch(const lgs_handle* h) {
+    if (!h) return LGS_E_INVALID;
+    if (h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready) return h->blocked.chain.batch;
+    if (h->blocked.ready) return h->blocked.wave * 4;
+    return 65536;
+}
+
 int lgs_klein_sample(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez, double* V_dev,
                      int64_t* X_dev, double* logq_dev, void* stream) {
     if (!h) return LGS_E_INVALID;
@@ -265,6 +272,8 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
     }
     // chunk = two full waves of contraction tiles on the blocked path (75 776 samples on a B200), else 64 Ki
     int64_t chunk = h->blocked.ready && h->blocked.wave > 0 ? 2 * h->blocked.wave : (int64_t)65536;
+    if (h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready)
+        chunk = h->blocked.chain.batch / 3;  // three tiles per SM (one per slot): short chunks overlap the PCIe copy best
     if (chunk > S) chunk = S;
     const size_t bV = V_host ? align256(sizeof(double) * chunk * n) : 0;
     const size_t bX = X_host ? align256(sizeof(int64_t) * chunk * n) : 0;

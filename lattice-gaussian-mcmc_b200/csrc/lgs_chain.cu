@@ -1000,7 +1000,12 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     LGS_CHAIN_ATTR(false, false, true)
     LGS_CHAIN_ATTR(true, false, true)
 #undef LGS_CHAIN_ATTR
-    cc.batch = (int64_t)(bc.sm_count > 0 ? bc.sm_count : 148) * kTile * 3 * kSlots;
+    {
+        // a full batch gives every SM the same whole number of rounds of its kSlots tiles
+        const char* env = getenv("LGS_CHAIN_ROUNDS");
+        const int rounds = env ? atoi(env) : 3;
+        cc.batch = (int64_t)(bc.sm_count > 0 ? bc.sm_count : 148) * kTile * kSlots * (rounds > 0 ? rounds : 3);
+    }
     cc.ready = true;
     return cudaSuccess;
 }
