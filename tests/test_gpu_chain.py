@@ -1,0 +1,127 @@
+"""The persistent chain kernel (lgs_chain.cu) against the ordered path, and against the multi-kernel blocked path it
+replaced (LGS_CHAIN=0), on the cases its own machinery adds: the FP32 SampleZ screen and its FP64 fallback over the
+sigma_i regimes, look-ahead over many coordinate pairs, partial tiles, IMHK launches split at kept steps and at the
+64-step cap, the flush-only state read-out.
+
+Same Philox key per (sample, draw) and the same map u -> x everywhere, so integer coefficients must be equal sample
+for sample (see test_gpu_blocked.py for why a mismatch has probability ~1e-12 per draw).
+"""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lgs():
+    import __graft_entry__ as g
+    g.build()
+    import lattice_gaussian_mcmc_b200 as m
+    return m
+
+
+def _with_chain(flag, make):
+    """the choice between the chain kernel and the v1 kernels is read when a handle is created"""
+    old = os.environ.get("LGS_CHAIN")
+    os.environ["LGS_CHAIN"] = str(flag)
+    try:
+        return make()
+    finally:
+        if old is None:
+            del os.environ["LGS_CHAIN"]
+        else:
+            os.environ["LGS_CHAIN"] = old
+
+
+@pytest.mark.parametrize("n,S", [(64, 129), (200, 1000), (520, 300)])
+def test_chain_equals_v1_blocked_path(lgs, n, S):
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(n, seed=200 + n)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    center = np.random.RandomState(n).uniform(-40, 40, n)
+    a = _with_chain(1, lambda: lgs.KleinSampler(lat, sigma, center, seed=11, path="blocked", samplez="fast"))
+    b = _with_chain(0, lambda: lgs.KleinSampler(lat, sigma, center, seed=11, path="blocked", samplez="fast"))
+    assert a._engine.preferred_batch % 128 == 0 and a._engine.preferred_batch != b._engine.preferred_batch
+    Va, Xa, la = a.sample_with_coefficients(S)
+    Vb, Xb, lb = b.sample_with_coefficients(S)
+    assert int(np.sum(np.any(Xa != Xb, axis=1))) == 0
+    assert np.array_equal(Va, Vb)
+    assert np.max(np.abs(la - lb) / np.abs(la)) < 1e-10
+    # lattice points only (the kernel variant without the log-density accumulation) give the same points
+    assert np.array_equal(a._engine.klein_sample(S, 11, 0, "fast")[0], Va)
+
+
+@pytest.mark.parametrize("sigma", [0.8, 1.2, 5.0, 14.0, 20.0, 60.0])
+def test_chain_sigma_regimes_equal_ordered(lgs, sigma):
+    """sigma_i < 1 (summed normaliser), 1 <= sigma_i < 1.45 (theta-series term), the FP32-screened regime, beyond its
+    sigma_i <= 16 eligibility (FP64 smooth), and the truncated 1001-entry window (sigma_i > 50)"""
+    n = 72
+    rng = np.random.RandomState(5)
+    B = np.triu(rng.uniform(-0.4, 0.4, (n, n)), 1) + np.eye(n)
+    lat = lgs.SimpleLattice(B)
+    center = rng.uniform(-3, 3, n)
+    a = lgs.KleinSampler(lat, sigma, center, seed=4, path="ordered", samplez="fast")
+    b = lgs.KleinSampler(lat, sigma, center, seed=4, path="blocked", samplez="fast")
+    S = 3000
+    Va, Xa, la = a.sample_with_coefficients(S)
+    Vb, Xb, lb = b.sample_with_coefficients(S)
+    assert int(np.sum(np.any(Xa != Xb, axis=1))) == 0
+    ref = Xb.astype(np.float64) @ B.T
+    assert np.max(np.abs(Vb - ref)) <= 1e-12 * np.max(np.abs(ref))
+    assert np.max(np.abs(la - lb) / np.abs(la)) < 1e-10
+
+
+def test_chain_half_integer_centers_take_the_fp64_path(lgs):
+    """means on exact .5 ties (Z^n, c = 1/2): rint's half-to-even decides c0, in FP32 and in FP64 alike"""
+    from lattice_gaussian_mcmc_b200.lattices import identity_lattice
+    lat = identity_lattice(66)
+    center = np.full(66, 0.5)
+    a = lgs.KleinSampler(lat, 3.0, center, seed=9, path="ordered", samplez="fast")
+    b = lgs.KleinSampler(lat, 3.0, center, seed=9, path="blocked", samplez="fast")
+    Xa = a.sample_with_coefficients(4000)[1]
+    Xb = b.sample_with_coefficients(4000)[1]
+    assert np.array_equal(Xa, Xb)
+    assert abs(Xb.mean() - 0.5) < 0.05
+
+
+@pytest.mark.parametrize("weight_mode", ["reference", "exact"])
+def test_chain_imhk_long_burn_in_split_over_launches(lgs, weight_mode):
+    """burn-in longer than the 64-step launch cap, kept states every 3 steps: launches end at every kept step and the
+    chains continue across them exactly like the per-thread ordered chains"""
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    n, chains = 40, 200
+    lat = dd_lattice(n, seed=77)
+    sigma = (0.6 if weight_mode == "exact" else 1.5) * lat.max_gram_schmidt_norm
+    center = np.random.RandomState(3).uniform(-10, 10, n)
+    kw = dict(burn_in=0, n_chains=chains, seed=23, weight_mode=weight_mode, samplez="fast")
+    a = lgs.IMHKSampler(lat, sigma, center, path="ordered", **kw)
+    b = lgs.IMHKSampler(lat, sigma, center, path="blocked", **kw)
+    Va = a.sample(n_samples=3, burn_in=150, thin=3)
+    Vb = b.sample(n_samples=3, burn_in=150, thin=3)
+    assert np.array_equal(Va, Vb)
+    assert a.total_proposals == b.total_proposals == chains * 159
+    assert a.accepted_proposals == b.accepted_proposals
+    if weight_mode == "exact":
+        assert 0.05 < b.acceptance_rate < 0.999          # rejections exercise the deferred commit
+    assert np.array_equal(a.current_coeffs, b.current_coeffs)          # flush-only launch
+    assert np.array_equal(a.per_chain_acceptance, b.per_chain_acceptance)
+    # a state read-out does not disturb the chains
+    Va2 = a.sample(n_samples=1, thin=1)
+    Vb2 = b.sample(n_samples=1, thin=1)
+    assert np.array_equal(Va2, Vb2)
+
+
+def test_chain_imhk_equals_v1_at_full_dimension(lgs):
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(1024, seed=2)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    kw = dict(burn_in=0, n_chains=300, seed=5, path="blocked")
+    a = _with_chain(1, lambda: lgs.IMHKSampler(lat, sigma, **kw))
+    b = _with_chain(0, lambda: lgs.IMHKSampler(lat, sigma, **kw))
+    Va = a.sample(n_samples=2, burn_in=2, thin=2)
+    Vb = b.sample(n_samples=2, burn_in=2, thin=2)
+    assert np.array_equal(Va, Vb)
+    assert np.array_equal(a.current_coeffs, b.current_coeffs)
+    assert a.total_proposals == b.total_proposals == 300 * 6
