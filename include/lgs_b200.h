@@ -193,6 +193,26 @@ LGS_API int lgs_histogram(lgs_handle *h, const double *V_dev, int64_t S, const i
                   double lo, double width, int32_t nbins, int64_t *hist_dev, void *stream);
 
 /*
+ * Chain diagnostics on kept states that stay on the device (V_dev[chains][keep][n], the layout lgs_imhk_run writes).
+ * For every chain and every tracked coordinate dims_host[d] the time series x_t = V[chain][t][dim] gives
+ *   stats_dev[chain][d][LGS_DIAG_FIELDS] = { mean, variance (ddof = 1), tau_int, window, acf[1] }
+ * with the reference's arithmetic: compute_autocorrelation (src/diagnostics/convergence_diag.py:75-112,
+ * mcmc_diag.py:12-33: biased autocovariance normalised by lag 0) and integrated_autocorrelation_time
+ * (convergence_diag.py:115-145, mcmc_diag.py:36-57: tau = 1 + 2 sum acf[k] up to the first k >= c_window * sum, or
+ * max_lag).  max_lag <= 0 selects len // 4 (convergence_diag.py:86).  effective_sample_size (mcmc_diag.py:59-104) is
+ * keep / tau_int.  acf_dev (may be NULL) receives acf[0 .. acf_len) per series.
+ * lgs_gelman_rubin_sums adds, per coordinate, { sum of chain means, sum of squared chain means, sum of chain
+ * variances } over the chains into sums_dev[n_dims][3] -- the only quantities gelman_rubin_statistic
+ * (convergence_diag.py:176-213) needs, so that ranks can all-reduce them (a few doubles) and form R-hat on the host.
+ */
+#define LGS_DIAG_FIELDS 5
+LGS_API int lgs_chain_diagnostics(lgs_handle *h, const double *V_dev, int64_t chains, int64_t keep,
+                                  const int32_t *dims_host, int32_t n_dims, double c_window, int32_t max_lag,
+                                  double *stats_dev, double *acf_dev, int32_t acf_len, void *stream);
+LGS_API int lgs_gelman_rubin_sums(lgs_handle *h, const double *stats_dev, int64_t chains, int32_t n_dims,
+                                  double *sums_dev, void *stream);
+
+/*
  * Measurement hooks (no reference counterpart; used by bench.py for the roofline figures).
  * While enabled, every kernel launch of the blocked path is bracketed by CUDA events on its own stream;
  * lgs_profile_read() synchronises the device, returns the summed device time [ms] and the launch count per kernel

@@ -67,6 +67,9 @@ PROTOTYPES = {
     "lgs_imhk_replay_host": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, vp, ctypes.c_int64, vp, vp, vp, vp, vp]),
     "lgs_imhk_get_state_host": (ctypes.c_int, [vp, vp, vp, vp, vp]),
     "lgs_imhk_counts_host": (ctypes.c_int, [vp, c_i64p, c_i64p]),
+    "lgs_chain_diagnostics": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int64, c_i32p, ctypes.c_int32, ctypes.c_double,
+                                             ctypes.c_int32, vp, vp, ctypes.c_int32, vp]),
+    "lgs_gelman_rubin_sums": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int32, vp, vp]),
     "lgs_profile_enable": (ctypes.c_int, [vp, ctypes.c_int]),
     "lgs_profile_read": (ctypes.c_int, [vp, c_f64p, c_i64p]),
     "lgs_histogram": (ctypes.c_int, [vp, vp, ctypes.c_int64, c_i32p, ctypes.c_int32, ctypes.c_double, ctypes.c_double, ctypes.c_int32, vp, vp]),

@@ -163,6 +163,19 @@ class Engine:
         check(self._h, self._lib.lgs_imhk_get_state(self._h, counts or None, X or None, V or None, logw or None,
                                                     stream or None))
 
+    DIAG_FIELDS = ("mean", "var", "tau_int", "window", "acf1")
+
+    def chain_diagnostics_dev(self, V, chains, keep, dims, stats, c_window=5.0, max_lag=0, acf=0, acf_len=0, stream=0):
+        """stats[chains][len(dims)][5] (device pointer) <- per-chain mean / var / tau_int / window / acf[1] of the
+        tracked coordinates of V[chains][keep][n] (device pointer); see lgs_chain_diagnostics in include/lgs_b200.h"""
+        dims = np.ascontiguousarray(dims, dtype=np.int32)
+        check(self._h, self._lib.lgs_chain_diagnostics(self._h, V, int(chains), int(keep),
+                                                       dims.ctypes.data_as(_capi.c_i32p), dims.size, float(c_window),
+                                                       int(max_lag), stats, acf or None, int(acf_len), stream or None))
+
+    def gelman_rubin_sums_dev(self, stats, chains, n_dims, sums, stream=0):
+        check(self._h, self._lib.lgs_gelman_rubin_sums(self._h, stats, int(chains), int(n_dims), sums, stream or None))
+
     def histogram_dev(self, V, S, dims, lo, width, nbins, hist, stream=0):
         dims = np.ascontiguousarray(dims, dtype=np.int32)
         check(self._h, self._lib.lgs_histogram(self._h, V, int(S), dims.ctypes.data_as(_capi.c_i32p), dims.size,

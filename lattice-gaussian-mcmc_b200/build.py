@@ -24,6 +24,7 @@ UNITS = [
     ("lgs_ordered.cu", ["-fmad=false"]),
     ("lgs_blocked.cu", []),
     ("lgs_chain.cu", []),
+    ("lgs_diag.cu", []),
     ("lgs_capi.cu", []),
 ]
 

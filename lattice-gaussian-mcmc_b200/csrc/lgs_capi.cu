@@ -199,6 +199,7 @@ void lgs_destroy(lgs_handle* h) {
     cudaFree(h->scratch.Xw);
     cudaFree(h->stage_dev);
     cudaFree(h->hist_dims);
+    cudaFree(h->diag_scratch);
     cudaFree(h->arena);
     if (h->host_compute) cudaStreamDestroy(h->host_compute);
     if (h->host_copy) cudaStreamDestroy(h->host_copy);
@@ -580,6 +581,45 @@ int lgs_histogram(lgs_handle* h, const double* V_dev, int64_t S, const int32_t* 
                                 (cudaStream_t)stream));
     LGS_CUDA(h, launch_histogram(h->ctx, V_dev, S, h->hist_dims, n_dims, lo, width, nbins, hist_dev,
                                  (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+int lgs_chain_diagnostics(lgs_handle* h, const double* V_dev, int64_t chains, int64_t keep, const int32_t* dims_host,
+                          int32_t n_dims, double c_window, int32_t max_lag, double* stats_dev, double* acf_dev,
+                          int32_t acf_len, void* stream) {
+    if (!h) return LGS_E_INVALID;
+    if (!V_dev || !dims_host || !stats_dev || chains <= 0 || keep < 2 || n_dims <= 0 || n_dims > 256 || !(c_window > 0.0))
+        return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics: bad arguments (need keep >= 2, 1 <= n_dims <= 256)");
+    if (acf_dev && acf_len <= 0) return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics: acf_len must be positive");
+    for (int i = 0; i < n_dims; i++)
+        if (dims_host[i] < 0 || dims_host[i] >= h->n) return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics: dim out of range");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    if (max_lag <= 0) max_lag = (int32_t)(keep / 4);                 // convergence_diag.py:86
+    if (max_lag > keep - 1) max_lag = (int32_t)(keep - 1);
+    if (acf_dev && acf_len > max_lag + 1) return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics: acf_len > max_lag + 1");
+    if (!h->hist_dims) LGS_CUDA(h, cudaMalloc(&h->hist_dims, sizeof(int32_t) * 256));
+    const size_t need = sizeof(double) * (size_t)chains * n_dims * keep;
+    if (h->diag_cap < need) {
+        cudaFree(h->diag_scratch);
+        h->diag_scratch = nullptr;
+        h->diag_cap = 0;
+        LGS_CUDA(h, cudaMalloc(&h->diag_scratch, need));
+        h->diag_cap = need;
+    }
+    LGS_CUDA(h, cudaMemcpyAsync(h->hist_dims, dims_host, sizeof(int32_t) * n_dims, cudaMemcpyHostToDevice,
+                                (cudaStream_t)stream));
+    LGS_CUDA(h, launch_chain_diagnostics(V_dev, chains, keep, h->n, h->hist_dims, n_dims, c_window, max_lag,
+                                         h->diag_scratch, stats_dev, acf_dev, acf_dev ? acf_len : 0,
+                                         (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+int lgs_gelman_rubin_sums(lgs_handle* h, const double* stats_dev, int64_t chains, int32_t n_dims, double* sums_dev,
+                          void* stream) {
+    if (!h) return LGS_E_INVALID;
+    if (!stats_dev || !sums_dev || chains <= 0 || n_dims <= 0) return fail(h, LGS_E_INVALID, "lgs_gelman_rubin_sums: bad arguments");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    LGS_CUDA(h, launch_gelman_rubin_sums(stats_dev, chains, n_dims, sums_dev, (cudaStream_t)stream));
     return LGS_OK;
 }
 

@@ -174,6 +174,8 @@ struct lgs_handle {
     void* stage_dev = nullptr;
     size_t stage_cap = 0;
     int32_t* hist_dims = nullptr;  // device copy of the tracked coordinates of the last lgs_histogram call
+    double* diag_scratch = nullptr;  // series-major copy of the tracked coordinates (lgs_chain_diagnostics)
+    size_t diag_cap = 0;
     cudaStream_t host_compute = nullptr, host_copy = nullptr;  // compute / transfer overlap of the *_host calls
     cudaEvent_t ev_done[2] = {}, ev_free[2] = {};
     std::string err;
@@ -204,6 +206,13 @@ cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, i
                                 int weight_mode, double* V, int64_t* X, cudaStream_t st);
 cudaError_t launch_imhk_blocked_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
                                           double* logw, cudaStream_t st);
+
+// lgs_diag.cu  (device-side chain diagnostics)
+constexpr int kDiagFields = LGS_DIAG_FIELDS;
+cudaError_t launch_chain_diagnostics(const double* V, int64_t chains, int64_t keep, int n, const int32_t* dims_dev,
+                                     int n_dims, double cwin, int max_lag, double* scratch, double* stats, double* acf,
+                                     int acf_len, cudaStream_t st);
+cudaError_t launch_gelman_rubin_sums(const double* stats, int64_t chains, int n_dims, double* sums, cudaStream_t st);
 
 // lgs_chain.cu  (persistent warp-specialised kernel)
 cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc);

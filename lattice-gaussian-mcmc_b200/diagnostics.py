@@ -1,0 +1,66 @@
+"""Chain diagnostics on device-resident IMHK output: the callers' next step on the sampler output
+(src/diagnostics/convergence_diag.py, mcmc_diag.py) without moving the chains to the host.
+
+`ChainDiagnostics(sampler_or_engine).run(V, dims)` takes the kept states as a CUDA tensor `[chains, keep, n]` (what
+`lgs_imhk_run` writes) and returns, per chain and tracked coordinate, what the reference computes per series:
+
+  reference function                                   here
+  compute_autocorrelation   (convergence_diag.py:75)   `acf`      [chains, dims, acf_len]   (optional)
+  integrated_autocorrelation_time  (:115)              `tau_int`  [chains, dims]
+  effective_sample_size     (mcmc_diag.py:59)          `ess`      [chains, dims]; multivariate = min over dims (:98-105)
+  gelman_rubin_statistic    (convergence_diag.py:176)  `r_hat`    [dims], chains = the reference's list of chains
+  np.mean / np.var(ddof=1) of a chain                  `mean`, `var`
+
+Across ranks only `3 * dims` doubles travel (one SUM all-reduce of the chain-mean / chain-variance sums).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def r_hat_from_sums(sums: torch.Tensor, chains: int, keep: int) -> torch.Tensor:
+    """gelman_rubin_statistic (convergence_diag.py:176-213) from per-coordinate sums over chains
+    `[sum mean_c, sum mean_c^2, sum var_c]`: B = n/(m-1) sum (mean_c - mean)^2, W = mean var_c,
+    R = sqrt(((n-1)/n W + B/n) / W)."""
+    s = sums.to(torch.float64).reshape(-1, 3)
+    m, n = float(chains), float(keep)
+    overall = s[:, 0] / m
+    between = n / (m - 1.0) * (s[:, 1] - m * overall * overall)
+    within = s[:, 2] / m
+    pooled = (n - 1.0) / n * within + between / n
+    return torch.sqrt(pooled / within)
+
+
+class ChainDiagnostics:
+    def __init__(self, sampler_or_engine):
+        self.eng = getattr(sampler_or_engine, "_engine", sampler_or_engine)
+
+    def run(self, V: torch.Tensor, dims, c_window: float = 5.0, max_lag: int = 0, acf_len: int = 0, group=None):
+        if not (V.is_cuda and V.dtype == torch.float64 and V.dim() == 3 and V.is_contiguous()):
+            raise ValueError("V must be a contiguous CUDA float64 tensor [chains, keep, n]")
+        chains, keep, n = V.shape
+        if n != self.eng.n:
+            raise ValueError("last dimension of V must be the lattice dimension")
+        dims = np.ascontiguousarray(dims, dtype=np.int32)
+        st = torch.cuda.current_stream(V.device).cuda_stream
+        stats = torch.empty((chains, dims.size, len(self.eng.DIAG_FIELDS)), dtype=torch.float64, device=V.device)
+        acf = torch.empty((chains, dims.size, acf_len), dtype=torch.float64, device=V.device) if acf_len > 0 else None
+        self.eng.chain_diagnostics_dev(V.data_ptr(), chains, keep, dims, stats.data_ptr(), c_window, max_lag,
+                                       acf.data_ptr() if acf is not None else 0, acf_len, st)
+        sums = torch.zeros((dims.size, 3), dtype=torch.float64, device=V.device)
+        self.eng.gelman_rubin_sums_dev(stats.data_ptr(), chains, dims.size, sums.data_ptr(), st)
+        total_chains = chains
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            buf = torch.cat([sums.reshape(-1), torch.tensor([float(chains)], dtype=torch.float64, device=V.device)])
+            dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+            sums = buf[:-1].reshape(dims.size, 3)
+            total_chains = int(round(float(buf[-1])))
+        out = {k: stats[:, :, i] for i, k in enumerate(self.eng.DIAG_FIELDS)}
+        out["ess"] = keep / out["tau_int"]                      # mcmc_diag.py:76-78
+        out["ess_min"] = out["ess"].min(dim=1).values           # mcmc_diag.py:98-105
+        out["r_hat"] = r_hat_from_sums(sums, total_chains, keep) if total_chains > 1 else None
+        out["acf"] = acf
+        out["gr_sums"] = sums
+        return out

@@ -99,3 +99,33 @@ def test_marginal_tvd_and_acceptance_formulas():
     # single process: all-reduce is the identity
     tot, h = D.allreduce_stats(torch.tensor([[1, 2], [3, 4]]), a)
     assert tot.tolist() == [4, 6] and torch.equal(h, a)
+
+
+def _gr_worker(rank, world_size, port, out_dir):
+    """each rank holds half of the chains: per-chain mean / variance sums -> one all-reduce -> R-hat"""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world_size)
+    from lattice_gaussian_mcmc_b200 import distributed as D
+    from lattice_gaussian_mcmc_b200.diagnostics import r_hat_from_sums
+    g = np.load(os.path.join(ROOT, "tests", "golden", "diag_ar1.npz"))
+    X = torch.from_numpy(g["X"])                       # [series kinds = "coordinates", chains, keep]
+    A, C, K = X.shape
+    start, count = D.shard_range(C, rank, world_size)
+    mine = X[:, start:start + count]
+    means = mine.mean(dim=2)
+    sums = torch.stack([means.sum(dim=1), (means * means).sum(dim=1), mine.var(dim=2, unbiased=True).sum(dim=1)], dim=1)
+    buf = torch.cat([sums.reshape(-1), torch.tensor([float(count)], dtype=torch.float64)])
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+    rhat = r_hat_from_sums(buf[:-1].reshape(A, 3), int(buf[-1]), K)
+    np.save(os.path.join(out_dir, f"rhat{rank}.npy"), rhat.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_gelman_rubin_matches_reference_golden(tmp_path):
+    """convergence_diag.py:176-213 from all-reduced per-rank sums == the reference's value on all chains"""
+    mp.spawn(_gr_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    g = np.load(os.path.join(ROOT, "tests", "golden", "diag_ar1.npz"))
+    for r in range(2):
+        assert np.max(np.abs(np.load(tmp_path / f"rhat{r}.npy") - g["rhat"])) < 1e-12

@@ -1,0 +1,99 @@
+"""Device-side chain diagnostics (lgs_chain_diagnostics / lgs_gelman_rubin_sums) against the reference's
+own numbers (tests/golden/diag_ar1.npz) and the oracle restatement, through the C-ABI.
+
+Tolerances: the kernel sums the lagged products directly, the reference goes through an FFT: acf agrees to 1e-11
+absolute, tau_int to 1e-10 relative unless the Sokal window lands on a different lag (it cannot here: the margin
+k - c * tau is checked), R-hat to 1e-12.
+"""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lgs():
+    import __graft_entry__ as g
+    g.build()
+    import lattice_gaussian_mcmc_b200 as m
+    return m
+
+
+def test_diagnostics_match_reference_golden(lgs):
+    import torch
+    from lattice_gaussian_mcmc_b200.diagnostics import ChainDiagnostics
+    from lattice_gaussian_mcmc_b200.lattices import identity_lattice
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "diag_ar1.npz"))
+    X = g["X"]                                   # [4 correlation strengths, 12 chains, 400 steps]
+    A, C, K = X.shape
+    n = 6
+    smp = lgs.KleinSampler(identity_lattice(n), 3.0, seed=1)
+    # coordinate a of "lattice point" t of chain c carries series a; the other coordinates are noise
+    V = np.random.RandomState(0).normal(size=(C, K, n))
+    dims = [4, 0, 2, 5]
+    for a in range(A):
+        V[:, :, dims[a]] = X[a]
+    Vd = torch.from_numpy(V).cuda()
+    out = ChainDiagnostics(smp).run(Vd, dims, c_window=5.0, acf_len=K // 4 + 1)
+    acf = out["acf"].cpu().numpy()
+    tau = out["tau_int"].cpu().numpy()
+    for a in range(A):
+        assert np.max(np.abs(acf[:, a, :] - g["acf"][a])) < 1e-11
+        assert np.max(np.abs(tau[:, a] - g["tau"][a]) / np.abs(g["tau"][a])) < 1e-10
+        assert np.max(np.abs(out["ess"][:, a].cpu().numpy() - g["ess"][a]) / g["ess"][a]) < 1e-10
+        assert np.allclose(out["mean"][:, a].cpu().numpy(), X[a].mean(axis=1), rtol=0, atol=1e-12)
+        assert np.allclose(out["var"][:, a].cpu().numpy(), X[a].var(axis=1, ddof=1), rtol=1e-13)
+        assert abs(float(out["r_hat"][a]) - g["rhat"][a]) < 1e-12
+    assert np.array_equal(out["ess_min"].cpu().numpy(), out["ess"].cpu().numpy().min(axis=1))
+    # without the ACF output the kernel stops at the Sokal window: same tau
+    out2 = ChainDiagnostics(smp).run(Vd, dims)
+    assert np.array_equal(out2["tau_int"].cpu().numpy(), tau)
+    assert out2["acf"] is None
+
+
+def test_diagnostics_on_imhk_output_match_oracle(lgs):
+    """kept states straight from lgs_imhk_run on the device -> diagnostics, against the oracle on the copied states"""
+    import torch
+    from oracle import diag_oracle as do
+    from lattice_gaussian_mcmc_b200.diagnostics import ChainDiagnostics
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    n, chains, keep = 24, 64, 200
+    lat = dd_lattice(n, seed=5)
+    sigma = 0.3 * lat.max_gram_schmidt_norm           # exact weights reject here: correlated chains
+    im = lgs.IMHKSampler(lat, sigma, burn_in=0, n_chains=chains, seed=3, weight_mode="exact", path="blocked")
+    eng = im._engine
+    V = torch.empty((chains, keep, n), dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    eng.imhk_run_dev(20, keep, 1, "fast", "exact", V=V.data_ptr(), stream=st)
+    dims = [0, n // 2, n - 1]
+    out = ChainDiagnostics(im).run(V, dims, acf_len=11)
+    Vh = V.cpu().numpy()
+    tau = out["tau_int"].cpu().numpy()
+    win = out["window"].cpu().numpy()
+    for c in range(0, chains, 7):
+        for j, d in enumerate(dims):
+            t_ref, w_ref = do.integrated_autocorrelation_time(Vh[c, :, d])
+            assert win[c, j] == w_ref
+            assert abs(tau[c, j] - t_ref) < 1e-10 * abs(t_ref)
+            assert np.max(np.abs(out["acf"][c, j].cpu().numpy() - do.compute_autocorrelation(Vh[c, :, d])[:11])) < 1e-11
+    for j, d in enumerate(dims):
+        r_ref = do.gelman_rubin_statistic([Vh[c, :, d] for c in range(chains)])
+        assert abs(float(out["r_hat"][j]) - r_ref) < 1e-11
+    assert 0.05 < im.acceptance_rate < 0.999
+
+
+def test_diagnostics_argument_errors(lgs):
+    import torch
+    from lattice_gaussian_mcmc_b200.diagnostics import ChainDiagnostics
+    from lattice_gaussian_mcmc_b200.lattices import identity_lattice
+    smp = lgs.KleinSampler(identity_lattice(4), 2.0, seed=1)
+    d = ChainDiagnostics(smp)
+    V = torch.zeros((3, 8, 4), dtype=torch.float64, device="cuda")
+    with pytest.raises(Exception):
+        d.run(V, [4])                              # coordinate out of range
+    with pytest.raises(ValueError):
+        d.run(V.cpu(), [0])
+    with pytest.raises(Exception):
+        d.run(torch.zeros((3, 1, 4), dtype=torch.float64, device="cuda"), [0])   # a series needs two points

@@ -87,3 +87,22 @@ def test_samplez_draws_match_reference_draw_log():
                 x, used = oracle.samplez(float(g["draw_mean"][s, k]), float(g["draw_sigma"][s, k]), float(U[s, k]))
                 bad += (x != int(g["draw_x"][s, k])) or not used
         assert bad == 0, fname
+
+
+def test_diagnostics_oracle_reproduces_reference_golden():
+    """oracle/diag_oracle.py against outputs of the reference's own convergence_diag / mcmc_diag functions
+    (tests/golden/diag_ar1.npz, minted by tests/golden/make_golden_diag.py)"""
+    from oracle import diag_oracle as do
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "diag_ar1.npz"))
+    X = g["X"]
+    for a in range(X.shape[0]):
+        for c in range(X.shape[1]):
+            acf = do.compute_autocorrelation(X[a, c])
+            assert np.max(np.abs(acf - g["acf"][a, c])) < 1e-12
+            tau, _ = do.integrated_autocorrelation_time(X[a, c])
+            assert abs(tau - g["tau"][a, c]) < 1e-11 * max(1.0, abs(g["tau"][a, c]))
+            assert abs(do.effective_sample_size(X[a, c]) - g["ess"][a, c]) < 1e-9 * g["ess"][a, c]
+        assert abs(do.gelman_rubin_statistic(list(X[a])) - g["rhat"][a]) < 1e-13
+    # multivariate ESS = minimum over coordinates (mcmc_diag.py:98-105)
+    xm = np.stack([X[0, 0], X[3, 0]], axis=1)
+    assert do.effective_sample_size(xm) == min(do.effective_sample_size(xm[:, 0]), do.effective_sample_size(xm[:, 1]))

@@ -9,6 +9,7 @@ NV="/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -linein
 $NV -fmad=false "$@" -c $C/lgs_ordered.cu -o tools/bin/obj_$name/ordered.o &
 $NV "$@" -c $C/lgs_blocked.cu -o tools/bin/obj_$name/blocked.o &
 $NV "$@" -c $C/lgs_chain.cu -o tools/bin/obj_$name/chain.o &
+$NV "$@" -c $C/lgs_diag.cu -o tools/bin/obj_$name/diag.o &
 $NV "$@" -c $C/lgs_capi.cu -o tools/bin/obj_$name/capi.o &
 wait
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o tools/bin/liblgs_$name.so tools/bin/obj_$name/*.o -Xcompiler -fPIC
