@@ -41,7 +41,9 @@ enum {
     LGS_E_CUDA = -2,    /* CUDA runtime error; text in lgs_last_error() */
     LGS_E_NOMEM = -3,   /* device allocation failed */
     LGS_E_STATE = -4,   /* call not valid in the current chain state */
-    LGS_E_FALLBACK = -5 /* replay: a draw hit the reference's no-uniform fallback (klein.py:176-179) */
+    LGS_E_FALLBACK = -5, /* replay: a draw hit the reference's no-uniform fallback (klein.py:176-179) */
+    LGS_E_RANGE = -6,    /* basis reduction: an integer left the exact range (|entry| >= 2^56 or a transform overflow) */
+    LGS_E_PRECISION = -7 /* basis reduction: the floating-point Gram-Schmidt data was not accurate enough */
 };
 
 /* 1-D sampler used for each coordinate */
@@ -211,6 +213,27 @@ LGS_API int lgs_chain_diagnostics(lgs_handle *h, const double *V_dev, int64_t ch
                                   double *stats_dev, double *acf_dev, int32_t acf_len, void *stream);
 LGS_API int lgs_gelman_rubin_sums(lgs_handle *h, const double *stats_dev, int64_t chains, int32_t n_dims,
                                   double *sums_dev, void *stream);
+
+/*
+ * Basis reduction on the host (no handle, no CUDA): the step before the sampling path.  Replaces the reference's
+ * LatticeReduction.lll_reduce / bkz_reduce (src/lattices/reduction.py:68-133, 238-300), which call Sage's
+ * Matrix.LLL(delta) / Matrix.BKZ(block_size) (fplll; also klein_scaling_analysis.py:95-108).  ROWS are basis vectors
+ * (Sage's convention there).  `rows` [n*m] int64 row-major is reduced in place; `U` [n*n] (or NULL) receives the
+ * unimodular transform with reduced = U * input (reduction.py:104 `B.solve_left(B_reduced)`); `stats` [5] (or NULL)
+ * receives {swaps, size-reduction passes, BKZ insertions, enumeration nodes, float precision used (53 | 64 | 106)}.
+ * precision: 0 = automatic (double for n <= 96, else x87 extended, then double-double; a tier whose Gram-Schmidt data
+ *   proves too inaccurate hands its exact basis to the next), or one fixed tier 53 / 64 / 106.
+ *   lgs_lll_reduce   L2-style LLL, (delta, eta)-reduced output, e.g. (0.99, 0.501) = Sage's LLL(delta=0.99).
+ *   lgs_bkz_reduce   Schnorr-Euchner BKZ with block size `block_size`; max_tours <= 0: run until no block improves;
+ *                    prune: 0 full enumeration, 1 linear pruning, < 0 automatic (pruned above block size 32).
+ *   lgs_gso_norms    ||b*_i|| of the rows (reduction.py:386-391 GSO(B).update_gso()).
+ * Errors: LGS_E_INVALID (NULL, m < n, linearly dependent rows, bad delta / eta), LGS_E_RANGE, LGS_E_PRECISION.
+ */
+LGS_API int lgs_lll_reduce(int64_t *rows, int32_t n, int32_t m, double delta, double eta, int32_t precision,
+                           int64_t *U, int64_t *stats);
+LGS_API int lgs_bkz_reduce(int64_t *rows, int32_t n, int32_t m, int32_t block_size, double delta, int32_t max_tours,
+                           int32_t prune, int32_t precision, int64_t *U, int64_t *stats);
+LGS_API int lgs_gso_norms(const int64_t *rows, int32_t n, int32_t m, double *norms);
 
 /*
  * Measurement hooks (no reference counterpart; used by bench.py for the roofline figures).

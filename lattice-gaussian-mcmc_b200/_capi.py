@@ -11,6 +11,7 @@ LIB_PATH = os.environ.get("LGS_B200_LIB") or os.path.join(HERE, "liblgs_b200.so"
 
 LGS_OK = 0
 LGS_E_INVALID, LGS_E_CUDA, LGS_E_NOMEM, LGS_E_STATE, LGS_E_FALLBACK = -1, -2, -3, -4, -5
+LGS_E_RANGE, LGS_E_PRECISION = -6, -7
 SAMPLEZ = {"table": 0, "fast": 1}
 WEIGHT = {"reference": 0, "exact": 1}
 PATH = {"auto": 0, "ordered": 1, "blocked": 2}
@@ -70,6 +71,10 @@ PROTOTYPES = {
     "lgs_chain_diagnostics": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int64, c_i32p, ctypes.c_int32, ctypes.c_double,
                                              ctypes.c_int32, vp, vp, ctypes.c_int32, vp]),
     "lgs_gelman_rubin_sums": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int32, vp, vp]),
+    "lgs_lll_reduce": (ctypes.c_int, [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_double, ctypes.c_double, ctypes.c_int32, vp, vp]),
+    "lgs_bkz_reduce": (ctypes.c_int, [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
+                                      ctypes.c_int32, ctypes.c_int32, vp, vp]),
+    "lgs_gso_norms": (ctypes.c_int, [vp, ctypes.c_int32, ctypes.c_int32, vp]),
     "lgs_profile_enable": (ctypes.c_int, [vp, ctypes.c_int]),
     "lgs_profile_read": (ctypes.c_int, [vp, c_f64p, c_i64p]),
     "lgs_histogram": (ctypes.c_int, [vp, vp, ctypes.c_int64, c_i32p, ctypes.c_int32, ctypes.c_double, ctypes.c_double, ctypes.c_int32, vp, vp]),

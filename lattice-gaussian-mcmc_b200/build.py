@@ -26,6 +26,7 @@ UNITS = [
     ("lgs_chain.cu", []),
     ("lgs_diag.cu", []),
     ("lgs_capi.cu", []),
+    ("lgs_reduce.cpp", ["-Xcompiler", "-mfma"]),   # host-only C++ (LLL / BKZ); nvcc hands it to g++
 ]
 
 
@@ -52,7 +53,7 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
         s = os.path.join(CSRC, src)
         if not os.path.exists(s):
             continue
-        o = os.path.join(OBJ, src.replace(".cu", ".o"))
+        o = os.path.join(OBJ, os.path.splitext(src)[0] + ".o")
         objs.append(o)
         if force or not os.path.exists(o) or os.path.getmtime(o) < max(os.path.getmtime(s), hdr_time):
             cmd = [nvcc, *ARCH, *COMMON, *extra, "-c", s, "-o", o]

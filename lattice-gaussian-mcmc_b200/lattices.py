@@ -116,51 +116,16 @@ def lattice_from_rows(rows: np.ndarray, name: str = "SimpleLattice") -> SimpleLa
 
 
 # ---------------------------------------------------------------------------------------------------------
-# LLL stand-in.  The reference reduces through Sage's Matrix.LLL() (fplll; src/lattices/reduction.py:103,
-# klein_scaling_analysis.py:95-108), which is not vendored and not installable here; no reference test stores a
-# reduced basis, so parity for the reduction itself is unpinned.  This is a textbook floating-point
-# LLL on an exact integer row basis -- host setup for the n <= 64 configurations, not part of the sampling path.
+# LLL.  The reference reduces through Sage's Matrix.LLL() (fplll; src/lattices/reduction.py:103,
+# klein_scaling_analysis.py:95-108), which is not vendored and not installable here.  The reduction is host C++
+# behind the C ABI (csrc/lgs_reduce.cpp, reduction.py); with (delta, eta) = (0.99, 0.501) it lands on the
+# Gram-Schmidt profiles the reference recorded for its n = 16 / 32 / 64 runs (tests/test_host_setup.py).
 # ---------------------------------------------------------------------------------------------------------
 def lll_reduce(rows: np.ndarray, delta: float = 0.99, eta: float = 0.501) -> np.ndarray:
-    """LLL-reduce the ROWS of an integer matrix (Lenstra-Lenstra-Lovasz with parameters (delta, eta)).
-    The basis is kept in exact Python integers; Gram-Schmidt data in float64 (adequate for the n <= 64,
-    |entries| <= 50 inputs of the reference's scaling runs).  Returns the reduced row basis as float64."""
-    B = np.array(np.rint(np.asarray(rows, dtype=np.float64)), dtype=object)
-    n = B.shape[0]
-    Bf = np.array(B, dtype=np.float64)
-    Bs = np.zeros((n, B.shape[1]))
-    mu = np.zeros((n, n))
-    nrm = np.zeros(n)
-
-    def gso_row(k):
-        v = Bf[k].copy()
-        if k:
-            mu[k, :k] = (Bs[:k] @ Bf[k]) / nrm[:k]
-            v -= mu[k, :k] @ Bs[:k]
-        Bs[k] = v
-        nrm[k] = v @ v
-
-    gso_row(0)
-    k = 1
-    while k < n:
-        gso_row(k)
-        for j in range(k - 1, -1, -1):          # size reduction
-            if abs(mu[k, j]) > eta:
-                q = int(np.rint(mu[k, j]))
-                B[k] = B[k] - q * B[j]
-                Bf[k] = np.array(B[k], dtype=np.float64)
-                mu[k, :j] -= q * mu[j, :j]
-                mu[k, j] -= q
-        gso_row(k)
-        if nrm[k] >= (delta - mu[k, k - 1] ** 2) * nrm[k - 1]:   # Lovasz condition
-            k += 1
-        else:
-            B[[k, k - 1]] = B[[k - 1, k]]
-            Bf[[k, k - 1]] = Bf[[k - 1, k]]
-            k = max(k - 1, 1)
-            if k == 1:
-                gso_row(0)
-    return np.array(B, dtype=np.float64)
+    """LLL-reduce the ROWS of an integer matrix; returns the reduced row basis as float64."""
+    from .reduction import lll
+    red, _, _ = lll(rows, delta=delta, eta=eta, with_transform=False)
+    return red.astype(np.float64)
 
 
 def lll_lattice(n: int, seed: int | None = None, delta: float = 0.99) -> SimpleLattice:
