@@ -271,10 +271,17 @@ def main():
         windows.append((t0, time.perf_counter()))
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        transport = int(eng._lib.lgs_host_transport(eng._h))
+        tname = {0: "fp64 copies", 1: "int16 pack kernel + chunked copies, widened to float64 by the host pool",
+                 2: "int16 written by the chain kernel into mapped pinned memory (zero-copy), widened to float64 by "
+                    "the host pool tile by tile while the kernel runs"}[transport]
+        d2h = S2 * n * 8 if transport == 0 else S2 * n * 2 + 4 * ((S2 + 127) // 128)
         e2e = {"value": world * S2 * K / float(dt.item()), "unit": "samples/s", "h2d_bytes_per_step": 16,
-               "d2h_bytes_per_step": S2 * n * 8,
+               "d2h_bytes_per_step": d2h, "host_bytes_delivered_per_step": S2 * n * 8, "transport": tname,
+               "host_threads": int(os.environ.get("LGS_HOST_THREADS", os.cpu_count() or 1)),
                "note": "lgs_klein_sample_host: the sampler's only inputs are (seed, first id) scalars; every step "
-                       "copies its S x n fp64 lattice points to pinned host memory"}
+                       "delivers its S x n float64 lattice points (the reference's return array) into a pinned host "
+                       "buffer; for this integer basis they cross PCIe as int16, bit-identical after widening"}
         del Vh
 
     # ---------------------------------------------------------------- IMHK leg

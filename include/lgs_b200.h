@@ -121,7 +121,21 @@ LGS_API int lgs_klein_sample(lgs_handle *h, int64_t S, uint64_t seed, uint64_t f
 LGS_API int lgs_klein_replay(lgs_handle *h, int64_t S, const double *U_dev, double *V_dev, int64_t *X_dev,
                      double *logq_dev, int32_t *fallback_count_dev, void *stream);
 
-/* Host-buffer forms (pageable or pinned host memory; copies inside; synchronous). */
+/* Host-buffer forms (pageable or pinned host memory; copies inside; synchronous).
+ *
+ * Transport of lattice points to the host.  The caller always receives the reference's float64 [S, n] array
+ * (klein.py:322).  For an integer basis every lattice point is an integer vector, so when only V_host is requested the
+ * bytes that cross PCIe are int16 (a quarter of fp64) and are widened into V_host by a pool of host threads:
+ *   LGS_TRANSPORT_INT16_ZEROCOPY  chain kernel, n % 8 == 0: the kernel's lattice-point epilogue writes int16 straight into
+ *                                 mapped pinned host memory and publishes a completion word per 128-sample tile; the
+ *                                 host widens finished tiles while the kernel is still running (one launch per batch);
+ *   LGS_TRANSPORT_INT16_COPY      any other kernel path: sample + pack kernel + copy in chunks, widened two chunks behind;
+ *   LGS_TRANSPORT_FP64            real-valued basis, or X_host / logq_host requested: plain fp64 copies.
+ * A batch in which a value does not fit int16 is delivered through the fp64 route instead (same samples).  The array
+ * handed back is bit-identical in all three (tests/test_gpu_hostpack.py).  LGS_HOST_THREADS sets the pool size
+ * (default: hardware concurrency); LGS_HOST_PACK=0 / LGS_HOST_ZEROCOPY=0 select the plainer routes (development A/B). */
+enum { LGS_TRANSPORT_FP64 = 0, LGS_TRANSPORT_INT16_COPY = 1, LGS_TRANSPORT_INT16_ZEROCOPY = 2 };
+LGS_API int lgs_host_transport(const lgs_handle *h); /* the route lgs_klein_sample_host(V_host only) takes on this handle */
 LGS_API int lgs_klein_sample_host(lgs_handle *h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez,
                           double *V_host, int64_t *X_host, double *logq_host);
 LGS_API int lgs_klein_replay_host(lgs_handle *h, int64_t S, const double *U_host, double *V_host, int64_t *X_host,

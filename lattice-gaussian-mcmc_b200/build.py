@@ -26,7 +26,8 @@ UNITS = [
     ("lgs_chain.cu", []),
     ("lgs_diag.cu", []),
     ("lgs_capi.cu", []),
-    ("lgs_reduce.cpp", ["-Xcompiler", "-mfma"]),   # host-only C++ (LLL / BKZ); nvcc hands it to g++
+    ("lgs_reduce.cpp", ["-Xcompiler", "-mfma"]),
+    ("lgs_hostpack.cpp", ["-Xcompiler", "-mavx2"]),   # host-only: widening of the packed D2H transport   # host-only C++ (LLL / BKZ); nvcc hands it to g++
 ]
 
 

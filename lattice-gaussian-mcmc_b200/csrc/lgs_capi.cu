@@ -1,6 +1,8 @@
 // C ABI of liblgs_b200.so (include/lgs_b200.h): handle management, per-sampler constants, dispatch.
+#include <atomic>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -56,6 +58,39 @@ void free_chains(ChainSet& cs) {
 }
 
 inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+// fp64 lattice points -> int16 for the trip over PCIe; *flag is set if any value does not survive the round trip
+// (non-integer or outside int16).  Pure streaming: 8 doubles in, one 16-byte store out per thread and iteration.
+__global__ void __launch_bounds__(256) pack_points_i16(const double* __restrict__ V, int16_t* __restrict__ P,
+                                                       size_t count, int32_t* __restrict__ flag) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 8;
+    bool bad = false;
+    for (size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 8; i + 8 <= count; i += stride) {
+        const double2* src = reinterpret_cast<const double2*>(V + i);
+        const double2 a = src[0], b = src[1], c = src[2], d = src[3];
+        const double v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
+        unsigned w[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int lo = __double2int_rn(v[2 * k]), hi = __double2int_rn(v[2 * k + 1]);
+            bad |= (double)lo != v[2 * k] || (double)hi != v[2 * k + 1] || lo < -32768 || lo > 32767 || hi < -32768 ||
+                   hi > 32767;
+            w[k] = ((unsigned)lo & 0xffffu) | ((unsigned)hi << 16);
+        }
+        *reinterpret_cast<uint4*>(P + i) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    const size_t tail = count & ~(size_t)7;
+    if (blockIdx.x == 0 && tail + threadIdx.x < count) {
+        const double x = V[tail + threadIdx.x];
+        const int r = __double2int_rn(x);
+        bad |= (double)r != x || r < -32768 || r > 32767;
+        P[tail + threadIdx.x] = (int16_t)r;
+    }
+    if (bad) atomicOr(flag, 1);
+}
+
+constexpr int kPackDev = 3;   // device slots: the GPU runs up to two chunks ahead of the host-side widening
+constexpr int kPackHost = 3;  // pinned slots
 
 }  // namespace
 
@@ -187,6 +222,10 @@ int lgs_create(const lgs_desc* d, lgs_handle** out) {
             return cuda_fail(nullptr, e, "blocked_init");
         }
     }
+    h->pack_ok = true;
+    for (size_t i = 0; i < (size_t)n * n && h->pack_ok; i++)
+        h->pack_ok = d->B[i] == std::nearbyint(d->B[i]) && std::fabs(d->B[i]) < 9007199254740992.0;
+    if (const char* e = getenv("LGS_HOST_PACK")) h->pack_ok = h->pack_ok && atoi(e) != 0;
     *out = h;
     return LGS_OK;
 }
@@ -201,6 +240,20 @@ void lgs_destroy(lgs_handle* h) {
     cudaFree(h->hist_dims);
     cudaFree(h->diag_scratch);
     cudaFree(h->arena);
+    cudaFree(h->pack_dev);
+    if (h->pack_host) cudaFreeHost(h->pack_host);
+    for (int i = 0; i < 3; i++) {
+        if (h->pk_done[i]) cudaEventDestroy(h->pk_done[i]);
+        if (h->pk_copied[i]) cudaEventDestroy(h->pk_copied[i]);
+    }
+    hostpool_destroy(h->pool);
+    for (int i = 0; i < 2; i++) {
+        if (h->zc_v16[i]) cudaFreeHost(h->zc_v16[i]);
+        if (h->zc_done[i]) cudaFreeHost(h->zc_done[i]);
+        if (h->zc_ev[i]) cudaEventDestroy(h->zc_ev[i]);
+    }
+    cudaFree(h->zc_cnt);
+    cudaFree(h->zc_ovf);
     if (h->host_compute) cudaStreamDestroy(h->host_compute);
     if (h->host_copy) cudaStreamDestroy(h->host_copy);
     for (int i = 0; i < 2; i++) {
@@ -251,12 +304,197 @@ int lgs_klein_replay(lgs_handle* h, int64_t S, const double* U_dev, double* V_de
     return LGS_OK;
 }
 
+// Host-buffer Klein call for an integer basis, lattice points only: chunk k is sampled and packed to int16 on the
+// compute stream, crosses PCIe on the copy stream (a quarter of the fp64 bytes) into a pinned ring, and is widened
+// into the caller's float64 buffer by the host pool while the GPU is already two chunks ahead.  A chunk whose pack
+// kernel raised its flag (a value outside int16) is fetched again as fp64 from its device slot, which is only
+// reused after the flag has been read.  Output is bit-identical to the plain fp64 copy.
+static int klein_host_packed(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_id, int samplez, double* V_host,
+                             int64_t chunk) {
+    const size_t n = h->n;
+    const size_t bV = align256(sizeof(double) * chunk * n);
+    const size_t bP = align256(sizeof(int16_t) * chunk * n) + 256;  // + flag
+    if (h->pack_dev_cap < kPackDev * (bV + bP)) {
+        cudaFree(h->pack_dev);
+        h->pack_dev = nullptr, h->pack_dev_cap = 0;
+        LGS_CUDA(h, cudaMalloc(&h->pack_dev, kPackDev * (bV + bP)));
+        h->pack_dev_cap = kPackDev * (bV + bP);
+    }
+    if (h->pack_host_cap < kPackHost * bP) {
+        if (h->pack_host) cudaFreeHost(h->pack_host);
+        h->pack_host = nullptr, h->pack_host_cap = 0;
+        LGS_CUDA(h, cudaHostAlloc(&h->pack_host, kPackHost * bP, cudaHostAllocDefault));
+        h->pack_host_cap = kPackHost * bP;
+    }
+    if (!h->pool) h->pool = hostpool_create(0);
+    if (!h->pk_done[0])
+        for (int i = 0; i < 3; i++) {
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->pk_done[i], cudaEventDisableTiming));
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->pk_copied[i], cudaEventDisableTiming));
+        }
+    cudaStream_t cs = h->host_compute, ps = h->host_copy;
+    const int64_t K = (S + chunk - 1) / chunk;
+    const int lag = 2;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    for (int64_t k = 0; k < K + lag; k++) {
+        if (k < K) {
+            const int64_t s0 = k * chunk, cnt = (S - s0) < chunk ? (S - s0) : chunk;
+            const int b = (int)(k % kPackDev);
+            uint8_t* slot = (uint8_t*)h->pack_dev + (size_t)b * (bV + bP);
+            double* dV = (double*)slot;
+            int16_t* dP = (int16_t*)(slot + bV);
+            int32_t* dflag = (int32_t*)(slot + bV + bP - 256);
+            // slot b was last used by chunk k-3: its packed copy completed before the host widened it (iteration k-1)
+            int rc = lgs_klein_sample(h, cnt, seed, first_id + (uint64_t)s0, samplez, dV, nullptr, nullptr, cs);
+            if (rc) return rc;
+            LGS_CUDA(h, cudaMemsetAsync(dflag, 0, sizeof(int32_t), cs));
+            pack_points_i16<<<sms * 8, 256, 0, cs>>>(dV, dP, (size_t)cnt * n, dflag);
+            LGS_CUDA(h, cudaGetLastError());
+            LGS_CUDA(h, cudaEventRecord(h->pk_done[b], cs));
+            LGS_CUDA(h, cudaStreamWaitEvent(ps, h->pk_done[b], 0));
+            uint8_t* hp = (uint8_t*)h->pack_host + (size_t)(k % kPackHost) * bP;
+            const size_t payload = align256(sizeof(int16_t) * cnt * n);
+            LGS_CUDA(h, cudaMemcpyAsync(hp, dP, sizeof(int16_t) * cnt * n, cudaMemcpyDeviceToHost, ps));
+            LGS_CUDA(h, cudaMemcpyAsync(hp + bP - 256, dflag, sizeof(int32_t), cudaMemcpyDeviceToHost, ps));
+            (void)payload;
+            LGS_CUDA(h, cudaEventRecord(h->pk_copied[k % kPackHost], ps));
+        }
+        const int64_t j = k - lag;
+        if (j >= 0) {
+            const int64_t s0 = j * chunk, cnt = (S - s0) < chunk ? (S - s0) : chunk;
+            LGS_CUDA(h, cudaEventSynchronize(h->pk_copied[j % kPackHost]));
+            const uint8_t* hp = (const uint8_t*)h->pack_host + (size_t)(j % kPackHost) * bP;
+            if (*(const int32_t*)(hp + bP - 256)) {  // out of int16 range: take the fp64 chunk itself
+                const double* dV = (const double*)((uint8_t*)h->pack_dev + (size_t)(j % kPackDev) * (bV + bP));
+                LGS_CUDA(h, cudaMemcpyAsync(V_host + (size_t)s0 * n, dV, sizeof(double) * cnt * n, cudaMemcpyDeviceToHost, ps));
+                LGS_CUDA(h, cudaStreamSynchronize(ps));
+            } else {
+                hostpool_expand_i16(h->pool, (const int16_t*)hp, V_host + (size_t)s0 * n, (size_t)cnt * n);
+            }
+        }
+    }
+    LGS_CUDA(h, cudaStreamSynchronize(cs));
+    return LGS_OK;
+}
+
+static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uint64_t seed, uint64_t first_id,
+                             int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host,
+                             bool allow_pack);
+
+// Host-buffer Klein call on the chain kernel for an integer basis with n % 8 == 0, lattice points only.  ONE launch per
+// full batch: the kernel's lattice-point epilogue writes int16 straight into mapped pinned host memory and publishes a
+// per-tile completion word; the host pool picks finished tiles up in order and widens them into the caller's float64
+// buffer while the kernel is still running, so what remains after the kernel ends is the last tile of every SM.  The
+// next batch is launched before the current one is drained.  A batch in which a value left int16 is re-run through
+// the plain fp64 route (same Philox keys, same samples).
+static int klein_host_zerocopy(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_id, double* V_host) {
+    const size_t n = h->n;
+    const int64_t batch = h->blocked.chain.batch;
+    const int64_t cap = S < batch ? (S + 127) / 128 * 128 : batch;
+    const int tiles_cap = (int)(cap / 128);
+    if (h->zc_cap < (size_t)cap) {
+        for (int i = 0; i < 2; i++) {
+            if (h->zc_v16[i]) cudaFreeHost(h->zc_v16[i]);
+            if (h->zc_done[i]) cudaFreeHost(h->zc_done[i]);
+            h->zc_v16[i] = nullptr, h->zc_done[i] = nullptr;
+        }
+        cudaFree(h->zc_cnt);
+        h->zc_cnt = nullptr, h->zc_cap = 0;
+        for (int i = 0; i < 2; i++) {
+            LGS_CUDA(h, cudaHostAlloc(&h->zc_v16[i], sizeof(int16_t) * cap * n, cudaHostAllocMapped));
+            LGS_CUDA(h, cudaHostAlloc((void**)&h->zc_done[i], sizeof(unsigned) * tiles_cap, cudaHostAllocMapped));
+            memset(h->zc_done[i], 0, sizeof(unsigned) * tiles_cap);
+        }
+        LGS_CUDA(h, cudaMalloc((void**)&h->zc_cnt, sizeof(unsigned) * 2 * tiles_cap));
+        if (!h->zc_ovf) LGS_CUDA(h, cudaMalloc((void**)&h->zc_ovf, sizeof(int) * 2));
+        h->zc_cap = (size_t)cap;
+        h->zc_epoch = 0;
+    }
+    if (!h->zc_ev[0])
+        for (int i = 0; i < 2; i++) LGS_CUDA(h, cudaEventCreateWithFlags(&h->zc_ev[i], cudaEventDisableTiming));
+    if (!h->pool) h->pool = hostpool_create(0);
+    cudaStream_t cs = h->host_compute;
+    const int64_t K = (S + cap - 1) / cap;
+    const int tiles_stride = (int)(h->zc_cap / 128);
+    unsigned epochs[2] = {0, 0};
+    auto launch = [&](int64_t k) -> int {
+        const int b = (int)(k & 1);
+        const int64_t s0 = k * cap, cnt = (S - s0) < cap ? (S - s0) : cap;
+        ChainZeroCopy zc;
+        void* dv = nullptr;
+        void* dd = nullptr;
+        LGS_CUDA(h, cudaHostGetDevicePointer(&dv, h->zc_v16[b], 0));
+        static void* dev_dummy = nullptr;   // development: LGS_ZC_DEVMEM=1 times the kernel with the int16 output in HBM
+        if (getenv("LGS_ZC_DEVMEM")) {
+            if (!dev_dummy) LGS_CUDA(h, cudaMalloc(&dev_dummy, sizeof(int16_t) * h->zc_cap * n));
+            dv = dev_dummy;
+        }
+        LGS_CUDA(h, cudaHostGetDevicePointer(&dd, h->zc_done[b], 0));
+        zc.v16 = (int16_t*)dv;
+        zc.tile_done = (unsigned*)dd;
+        zc.tile_cnt = h->zc_cnt + (size_t)b * tiles_stride;
+        zc.ovf = h->zc_ovf + b;
+        zc.epoch = epochs[b] = ++h->zc_epoch;
+        LGS_CUDA(h, cudaMemsetAsync(zc.ovf, 0, sizeof(int), cs));
+        LGS_CUDA(h, launch_klein_chain_zc(h->blocked, cnt, seed, first_id + (uint64_t)s0, zc, cs));
+        LGS_CUDA(h, cudaEventRecord(h->zc_ev[b], cs));
+        return LGS_OK;
+    };
+    int rc = launch(0);
+    if (rc) return rc;
+    for (int64_t k = 0; k < K; k++) {
+        if (k + 1 < K && (rc = launch(k + 1))) return rc;  // its buffers were drained in iteration k - 1
+        const int b = (int)(k & 1);
+        const int64_t s0 = k * cap, cnt = (S - s0) < cap ? (S - s0) : cap;
+        const int ntiles = (int)((cnt + 127) / 128);
+        const int16_t* src = (const int16_t*)h->zc_v16[b];
+        volatile unsigned* done = h->zc_done[b];
+        const unsigned epoch = epochs[b];
+        cudaEvent_t ev = h->zc_ev[b];
+        std::atomic<int> next{0};
+        std::atomic<int> failed{0};
+        const int device = h->device;
+        hostpool_run(h->pool, [&, src, done, epoch, ev, ntiles, cnt, s0, device](int, int) {
+            cudaSetDevice(device);
+            for (;;) {
+                const int t = next.fetch_add(1);
+                if (t >= ntiles || failed.load()) return;
+                unsigned spins = 0;
+                while (done[t] != epoch) {
+                    __builtin_ia32_pause();
+                    if ((++spins & 0xfffu) == 0 && cudaEventQuery(ev) != cudaErrorNotReady) {
+                        if (done[t] == epoch) break;  // the kernel has ended: every word is out, or it failed
+                        failed.store(1);
+                        return;
+                    }
+                }
+                std::atomic_thread_fence(std::memory_order_acquire);
+                const int64_t r0 = (int64_t)t * 128, r1 = r0 + 128 < cnt ? r0 + 128 : cnt;
+                expand_i16_range(src + (size_t)r0 * n, V_host + (size_t)(s0 + r0) * n, (size_t)(r1 - r0) * n);
+            }
+        });
+        LGS_CUDA(h, cudaEventSynchronize(ev));
+        if (failed.load()) return fail(h, LGS_E_CUDA, "lgs_klein_sample_host: the chain kernel ended without publishing every tile");
+        int ovf = 0;
+        LGS_CUDA(h, cudaMemcpy(&ovf, h->zc_ovf + b, sizeof(int), cudaMemcpyDeviceToHost));
+        if (ovf) {  // a value outside int16: this batch again, as fp64 (cudaMemcpy above has drained the stream)
+            rc = klein_host_common(h, cnt, nullptr, seed, first_id + (uint64_t)s0, LGS_SAMPLEZ_FAST, V_host + (size_t)s0 * n,
+                                   nullptr, nullptr, nullptr, false);
+            if (rc) return rc;
+        }
+    }
+    LGS_CUDA(h, cudaStreamSynchronize(cs));
+    return LGS_OK;
+}
+
 // Host-buffer Klein call.  The batch is cut into chunks; chunk k is computed on the compute stream into one of two
 // staging slots while chunk k-1 travels to the host on the copy stream, so the PCIe transfer (the larger cost:
 // 8n bytes per sample) hides the sampling.  Works with pageable host memory too (the copy then blocks the host, not
 // the device).
 static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uint64_t seed, uint64_t first_id,
-                             int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host) {
+                             int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host,
+                             bool allow_pack) {
     if (!h) return LGS_E_INVALID;
     if (S < 0) return fail(h, LGS_E_INVALID, "S < 0");
     if (S == 0) return LGS_OK;
@@ -276,6 +514,14 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
     if (h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready)
         chunk = h->blocked.chain.batch / 3;  // three tiles per SM (one per slot): short chunks overlap the PCIe copy best
     if (chunk > S) chunk = S;
+    if (allow_pack && h->pack_ok && V_host && !X_host && !logq_host && !U_host) {
+        const char* zc_env = getenv("LGS_HOST_ZEROCOPY");  // development A/B: 0 = chunked packed copies instead
+        const bool zc_off = zc_env && atoi(zc_env) == 0;
+        const bool chain = h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready &&
+                           samplez == LGS_SAMPLEZ_FAST && h->path != LGS_PATH_ORDERED;
+        if (chain && n % 8 == 0 && !zc_off) return klein_host_zerocopy(h, S, seed, first_id, V_host);
+        return klein_host_packed(h, S, seed, first_id, samplez, V_host, chunk);
+    }
     const size_t bV = V_host ? align256(sizeof(double) * chunk * n) : 0;
     const size_t bX = X_host ? align256(sizeof(int64_t) * chunk * n) : 0;
     const size_t bq = logq_host ? align256(sizeof(double) * chunk) : 0;
@@ -322,15 +568,23 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
     return LGS_OK;
 }
 
+int lgs_host_transport(const lgs_handle* h) {
+    if (!h) return LGS_E_INVALID;
+    if (!h->pack_ok) return LGS_TRANSPORT_FP64;
+    const char* zc_env = getenv("LGS_HOST_ZEROCOPY");
+    const bool chain = h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready && h->path != LGS_PATH_ORDERED;
+    return chain && h->n % 8 == 0 && !(zc_env && atoi(zc_env) == 0) ? LGS_TRANSPORT_INT16_ZEROCOPY : LGS_TRANSPORT_INT16_COPY;
+}
+
 int lgs_klein_sample_host(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez,
                           double* V_host, int64_t* X_host, double* logq_host) {
-    return klein_host_common(h, S, nullptr, seed, first_sample_id, samplez, V_host, X_host, logq_host, nullptr);
+    return klein_host_common(h, S, nullptr, seed, first_sample_id, samplez, V_host, X_host, logq_host, nullptr, true);
 }
 
 int lgs_klein_replay_host(lgs_handle* h, int64_t S, const double* U_host, double* V_host, int64_t* X_host,
                           double* logq_host, int32_t* fallback_count_host) {
     if (S > 0 && !U_host) return fail(h, LGS_E_INVALID, "lgs_klein_replay_host: NULL uniform stream");
-    return klein_host_common(h, S, U_host, 0, 0, LGS_SAMPLEZ_TABLE, V_host, X_host, logq_host, fallback_count_host);
+    return klein_host_common(h, S, U_host, 0, 0, LGS_SAMPLEZ_TABLE, V_host, X_host, logq_host, fallback_count_host, true);
 }
 
 int lgs_klein_logdensity(lgs_handle* h, int64_t S, const int64_t* X_dev, double* logq_dev, void* stream) {

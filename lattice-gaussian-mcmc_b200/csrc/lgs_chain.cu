@@ -170,7 +170,11 @@ struct ChainSmem {
     uint64_t cready[kSlots], pdone[kSlots], cfull[kSlots][2];
     int slot_tile[kSlots];
     int cdone[kSlots][2];              // warps of the slot that have finished with a constants buffer
+    // packed lattice-point output (ChainArgs::V16): per DMMA warp, its 32 samples x 32 rows as int16, one 80-byte
+    // row per sample so that a lane reads its sample's 64 bytes as four conflict-free 16-byte words
+    alignas(16) int16_t pk16[kDmmaThreads / 32][32][40];
 };
+static_assert(sizeof(ChainSmem) <= 232448, "ChainSmem exceeds the 227 KB of shared memory a CTA can opt into");
 
 struct ChainArgs {
     const double* Rpk;      // packed slivers of R: [npad/64][npad/16][64][20]
@@ -185,6 +189,16 @@ struct ChainArgs {
     double* lz;
     double* V;              // lattice points [S][ldv] or nullptr
     int64_t ldv;
+    // Packed zero-copy output (lgs_klein_sample_host on an integer basis, n % 8 == 0): lattice points as int16
+    // [S][n_valid] written straight into MAPPED PINNED HOST memory by the lattice-point epilogue, 64 contiguous bytes
+    // per sample and warp; tile_cnt[tile] (device) counts the DMMA warps that have stored the tile's last rows, and the warp that
+    // completes a tile publishes tile_done[tile] = epoch (mapped host memory) after a system-scope fence, so host
+    // threads widen finished tiles into the caller's float64 buffer while the kernel is still running.
+    int16_t* V16;
+    unsigned* tile_cnt;
+    unsigned* tile_done;
+    int* ovf;               // set if a value does not survive the trip through int16 (the host then re-runs in fp64)
+    unsigned tile_target, epoch;
     int64_t S;
     int npad;               // multiple of 64
     int n_valid;            // n
@@ -206,6 +220,25 @@ struct ChainArgs {
     double* lw_cur;         // [cap] current log importance weight
     long long* counts;      // [cap][2] accepted, total
 };
+
+#ifndef LGS_ZC_NOFENCE
+#define LGS_ZC_NOFENCE 0   // development: time the zero-copy epilogue without its system-scope fences (NOT correct)
+#endif
+// An integer-valued double with |v| < 2^15 as an int, by integer arithmetic on its bit pattern -- the DMMA warps own the
+// FP64 pipe, and F2I / I2F / DSETP would each take one of its slots.  `bad` is raised for anything else (a fraction,
+// |v| >= 2^15, inf, nan), in which case the host re-runs the batch through the fp64 route.
+__device__ __forceinline__ int pack_i16(double v, bool& bad) {
+    const int a = __double2hiint(v);
+    const unsigned b = (unsigned)__double2loint(v);
+    const int e = ((a >> 20) & 0x7ff) - 1023;
+    const unsigned m = ((unsigned)a & 0xfffffu) | 0x100000u;   // leading 21 bits of the significand
+    const bool in = (unsigned)e <= 14u;
+    const unsigned sh = in ? (unsigned)(20 - e) : 20u;
+    const unsigned mag = in ? (m >> sh) : 0u;
+    const bool exact = in ? ((m & ((1u << sh) - 1u)) == 0u) : (((unsigned)a << 1) == 0u);   // else branch: +-0
+    bad |= !exact || b != 0u;
+    return a < 0 ? -(int)mag : (int)mag;
+}
 
 // ---------------------------------------------------------------------------------------------------------
 // DMMA warps: consume stages until the producer sends F_EXIT
@@ -310,7 +343,54 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
 #else
 #define LGS_ACC(mt, hh, nt, c) acc[mt][nt][(hh) * 2 + (c)]
 #endif
-            if (h.flags & F_POINT) {
+            if ((h.flags & F_POINT) && P.V16) {
+                const int64_t s0 = (int64_t)h.tile * kTile;
+                int16_t (*stg)[40] = sm.pk16[warp];
+                bool bad = false;
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                        for (int nt = 0; nt < 4; nt++)
+#pragma unroll
+                            for (int c = 0; c < 2; c++) {
+                                stg[nt * 8 + t * 2 + c][mt * 16 + hh * 8 + g] = (short)pack_i16(LGS_ACC(mt, hh, nt, c), bad);
+                            }
+                __syncwarp();
+                // store j: lane L carries 16 bytes (8 rows) of sample 8 j + L / 4 -- four neighbouring lanes write the
+                // 64 contiguous bytes of one sample, i.e. whole 32-byte sectors go out over PCIe
+                const int row0 = h.r0 + wm * 32 + (lane & 3) * 8;
+                if (row0 + 8 <= P.n_valid) {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const int sl = j * 8 + (lane >> 2);
+                        const int64_t col = s0 + wn * 32 + sl;
+                        if (col < P.S)
+                            *reinterpret_cast<uint4*>(P.V16 + (size_t)col * P.n_valid + row0) =
+                                *reinterpret_cast<const uint4*>(&stg[sl][(lane & 3) * 8]);
+                    }
+                }
+                if (bad) atomicOr(P.ovf, 1);
+                __syncwarp();   // the staging rows are rewritten by the warp's next lattice-point item
+                if (h.r0 + kPair == P.npad) {
+                    // the tile's last 64 rows (its items arrive in row order): everything this warp has stored for
+                    // the tile becomes visible system-wide, then the warp is counted; the eighth warp publishes
+#if !LGS_ZC_NOFENCE
+                    __threadfence_system();
+#endif
+                    __syncwarp();
+                    if (lane == 0) {
+                        const unsigned prev = atomicAdd(&P.tile_cnt[h.tile], 1u);
+                        if (prev + 1 == P.tile_target) {
+#if !LGS_ZC_NOFENCE
+                            __threadfence_system();
+#endif
+                            *reinterpret_cast<volatile unsigned*>(&P.tile_done[h.tile]) = P.epoch;
+                        }
+                    }
+                }
+            } else if (h.flags & F_POINT) {
                 const int64_t s0 = (int64_t)h.tile * kTile;
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++)
@@ -475,7 +555,7 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
                         s_step[s]++;
                         start_step(s);
                     } else {
-                        if (P.V) { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
+                        if (P.V || P.V16) { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
                         assign(s);
                     }
                 } else {
@@ -1075,6 +1155,28 @@ static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64
     a.seed = seed; a.first_id = first_id; a.tag = 0u;
     a.nsteps = 1;
     return chain_launch(bc, a, false, false, want_d2, st);
+}
+
+// one batch (S <= chain.batch) with the packed zero-copy output described at ChainArgs::V16
+cudaError_t launch_klein_chain_zc(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, const ChainZeroCopy& zc,
+                                  cudaStream_t st) {
+    ChainCtx& cc = bc.chain;
+    if (S <= 0 || S > cc.batch || bc.n % 8) return cudaErrorInvalidValue;
+    cudaError_t e;
+    BlockedWork& w = cc.work[0];
+    const int64_t cap = S < cc.batch ? (S + kTile - 1) / kTile * kTile : cc.batch;
+    if ((e = chain_ensure_work(cc, w, cap)) != cudaSuccess) return e;
+    const int ntiles = (int)((S + kTile - 1) / kTile);
+    if ((e = cudaMemsetAsync(zc.tile_cnt, 0, sizeof(unsigned) * ntiles, st)) != cudaSuccess) return e;
+    ChainArgs a{};
+    a.Xbuf[0] = a.Xbuf[1] = w.X;
+    a.lp = w.lp; a.d2 = w.d2; a.lz = w.lz;
+    a.V = nullptr; a.ldv = 0; a.S = S;
+    a.V16 = zc.v16; a.tile_cnt = zc.tile_cnt; a.tile_done = zc.tile_done; a.ovf = zc.ovf; a.epoch = zc.epoch;
+    a.tile_target = kDmmaThreads / 32;
+    a.seed = seed; a.first_id = first_id; a.tag = 0u;
+    a.nsteps = 1;
+    return chain_launch(bc, a, false, false, false, st);
 }
 
 cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,

@@ -1,0 +1,118 @@
+// lgs_hostpack.cpp -- host side of the packed device-to-host transport used by lgs_klein_sample_host.
+//
+// For an integer basis every lattice point has integer coordinates, so the fp64 [S, n] result (klein.py:322) crosses
+// PCIe as int16 (a quarter of the bytes; the device-side pack kernel proves that every value round-trips, otherwise the
+// chunk is re-sent as fp64) and is widened back into the caller's float64 buffer here, by a small pool of host threads
+// with non-temporal stores.  This is transport only: the values delivered are bit-identical to the fp64 copy.
+#include <immintrin.h>
+
+#include <condition_variable>
+#include <cstdint>
+#include <cstdlib>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#include "lgs_internal_host.h"
+
+namespace lgs {
+
+struct HostPool {
+    std::vector<std::thread> workers;
+    std::mutex mtx;
+    std::condition_variable cv_go, cv_done;
+    std::function<void(int, int)> job;
+    uint64_t generation = 0;
+    int pending = 0;
+    bool stop = false;
+
+    explicit HostPool(int threads) {
+        for (int t = 0; t < threads; t++) workers.emplace_back([this, t, threads] { loop(t, threads); });
+    }
+    ~HostPool() {
+        {
+            std::lock_guard<std::mutex> lk(mtx);
+            stop = true;
+        }
+        cv_go.notify_all();
+        for (auto& w : workers) w.join();
+    }
+    void loop(int tid, int threads) {
+        uint64_t seen = 0;
+        for (;;) {
+            std::function<void(int, int)> f;
+            {
+                std::unique_lock<std::mutex> lk(mtx);
+                cv_go.wait(lk, [&] { return stop || generation != seen; });
+                if (stop) return;
+                seen = generation;
+                f = job;
+            }
+            f(tid, threads);
+            {
+                std::lock_guard<std::mutex> lk(mtx);
+                if (--pending == 0) cv_done.notify_one();
+            }
+        }
+    }
+    void run(std::function<void(int, int)> f) {
+        std::unique_lock<std::mutex> lk(mtx);
+        job = std::move(f);
+        pending = (int)workers.size();
+        generation++;
+        cv_go.notify_all();
+        cv_done.wait(lk, [&] { return pending == 0; });
+    }
+};
+
+HostPool* hostpool_create(int threads) {
+    if (threads <= 0) {
+        const char* e = std::getenv("LGS_HOST_THREADS");
+        threads = e ? std::atoi(e) : (int)std::thread::hardware_concurrency();
+        if (threads <= 0) threads = 4;
+        if (threads > 64) threads = 64;
+    }
+    return new HostPool(threads);
+}
+
+void hostpool_destroy(HostPool* p) { delete p; }
+
+int hostpool_threads(const HostPool* p) { return p ? (int)p->workers.size() : 0; }
+
+// dst[i] = (double)src[i] for i in [0, count)
+void expand_i16_range(const int16_t* src, double* dst, size_t count) {
+    size_t i = 0;
+    while (i < count && ((uintptr_t)(dst + i) & 31)) {  // reach a 32-byte boundary of the destination
+        dst[i] = (double)src[i];
+        i++;
+    }
+    for (; i + 8 <= count; i += 8) {
+        const __m128i v = _mm_loadu_si128((const __m128i*)(src + i));
+        const __m256i w = _mm256_cvtepi16_epi32(v);
+        const __m256d lo = _mm256_cvtepi32_pd(_mm256_castsi256_si128(w));
+        const __m256d hi = _mm256_cvtepi32_pd(_mm256_extracti128_si256(w, 1));
+        _mm256_stream_pd(dst + i, lo);
+        _mm256_stream_pd(dst + i + 4, hi);
+    }
+    for (; i < count; i++) dst[i] = (double)src[i];
+    _mm_sfence();
+}
+
+void hostpool_run(HostPool* p, const std::function<void(int, int)>& job) { p->run(job); }
+
+void hostpool_expand_i16(HostPool* p, const int16_t* src, double* dst, size_t count) {
+    if (!p || count < (size_t)1 << 16) {
+        expand_i16_range(src, dst, count);
+        return;
+    }
+    p->run([=](int tid, int threads) {
+        const size_t per = ((count + threads - 1) / threads + 63) & ~(size_t)63;
+        const size_t lo = per * (size_t)tid;
+        if (lo >= count) return;
+        const size_t hi = lo + per < count ? lo + per : count;
+        expand_i16_range(src + lo, dst + lo, hi - lo);
+    });
+}
+
+}  // namespace lgs

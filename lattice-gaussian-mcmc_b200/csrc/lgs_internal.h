@@ -161,6 +161,8 @@ struct Scratch {
 
 }  // namespace lgs
 
+#include "lgs_internal_host.h"
+
 struct lgs_handle {
     int device = 0;
     int path = LGS_PATH_AUTO;
@@ -178,6 +180,22 @@ struct lgs_handle {
     size_t diag_cap = 0;
     cudaStream_t host_compute = nullptr, host_copy = nullptr;  // compute / transfer overlap of the *_host calls
     cudaEvent_t ev_done[2] = {}, ev_free[2] = {};
+    // packed transport of lattice points to host buffers (integer bases only; lgs_hostpack.cpp)
+    bool pack_ok = false;             // every basis entry is an integer => every lattice point is
+    void* pack_dev = nullptr;         // device ring: kPackDev slots of {fp64 chunk, int16 chunk + flag}
+    size_t pack_dev_cap = 0;
+    void* pack_host = nullptr;        // pinned host ring: kPackHost slots of {int16 chunk + flag}
+    size_t pack_host_cap = 0;
+    cudaEvent_t pk_done[3] = {}, pk_copied[3] = {};
+    lgs::HostPool* pool = nullptr;
+    // zero-copy variant (chain kernel, n % 8 == 0): the kernel writes int16 lattice points into mapped pinned memory
+    void* zc_v16[2] = {};             // mapped pinned: [batch][n] int16, double-buffered over batches
+    unsigned* zc_done[2] = {};        // mapped pinned: per-tile completion epochs
+    unsigned* zc_cnt = nullptr;       // device: [2][tiles] arrival counters
+    int* zc_ovf = nullptr;            // device: [2]
+    size_t zc_cap = 0;                // samples per buffer
+    unsigned zc_epoch = 0;
+    cudaEvent_t zc_ev[2] = {};
     std::string err;
 };
 
@@ -200,6 +218,16 @@ cudaError_t launch_reduce_counts(const ChainSet& cs, int64_t* out2, cudaStream_t
 cudaError_t blocked_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc);
 void blocked_free(BlockedCtx& bc);
 cudaError_t blocked_profile_read(BlockedCtx& bc, double* ms, int64_t* launches, int nclass);
+// packed zero-copy output of one chain-kernel batch (lgs_chain.cu, ChainArgs::V16)
+struct ChainZeroCopy {
+    int16_t* v16;         // mapped pinned host memory, device-side address: [S][n] int16
+    unsigned* tile_cnt;   // device: [tiles]
+    unsigned* tile_done;  // mapped pinned host memory, device-side address: [tiles]
+    int* ovf;             // device
+    unsigned epoch;
+};
+cudaError_t launch_klein_chain_zc(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, const ChainZeroCopy& zc,
+                                  cudaStream_t st);
 cudaError_t launch_klein_blocked(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
                                  double* logq, cudaStream_t st);
 cudaError_t launch_imhk_blocked(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin,

@@ -1,0 +1,21 @@
+// Host-only helpers shared by lgs_capi.cu and lgs_hostpack.cpp (no CUDA types here).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <functional>
+
+namespace lgs {
+
+struct HostPool;
+HostPool* hostpool_create(int threads);  // threads <= 0: LGS_HOST_THREADS or the hardware concurrency
+void hostpool_destroy(HostPool* p);
+int hostpool_threads(const HostPool* p);
+// dst[i] = (double)src[i], split over the pool, non-temporal stores
+void hostpool_expand_i16(HostPool* p, const int16_t* src, double* dst, size_t count);
+
+// run job(thread id, thread count) on every pool thread and wait for all of them
+void hostpool_run(HostPool* p, const std::function<void(int, int)>& job);
+// dst[i] = (double)src[i] on the calling thread, non-temporal stores
+void expand_i16_range(const int16_t* src, double* dst, size_t count);
+
+}  // namespace lgs

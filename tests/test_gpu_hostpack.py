@@ -1,0 +1,100 @@
+"""Packed device-to-host transport of lgs_klein_sample_host (integer bases: lattice points cross PCIe as int16 and are
+widened by the host pool).  Two routes: the chain kernel writing int16 straight into mapped pinned memory with per-tile
+completion words (n % 8 == 0), and chunked pack-kernel + copy (everything else, LGS_HOST_ZEROCOPY=0).  It is transport
+only: the float64 array handed back must be bit-identical to the plain fp64 copy (LGS_HOST_PACK=0), including batches
+that fall back to fp64 because a value leaves int16."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lgs():
+    import __graft_entry__ as g
+    g.build()
+    import lattice_gaussian_mcmc_b200 as m
+    return m
+
+
+def _with_pack(flag, make):
+    """LGS_HOST_PACK is read when a handle is created"""
+    old = os.environ.get("LGS_HOST_PACK")
+    os.environ["LGS_HOST_PACK"] = str(flag)
+    try:
+        return make()
+    finally:
+        if old is None:
+            del os.environ["LGS_HOST_PACK"]
+        else:
+            os.environ["LGS_HOST_PACK"] = old
+
+
+@pytest.mark.parametrize("n,S", [(10, 10000), (64, 4097), (200, 70001), (1024, 3 * 18944 + 77)])
+def test_packed_transport_is_bit_identical_to_the_fp64_copy(lgs, n, S):
+    """several chunks, a ragged last chunk, n not a multiple of 8 (scalar tail of the pack kernel and of the widening)"""
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(n, seed=300 + n)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    a = _with_pack(1, lambda: lgs.KleinSampler(lat, sigma, seed=21))
+    b = _with_pack(0, lambda: lgs.KleinSampler(lat, sigma, seed=21))
+    Va = a._engine.klein_sample(S, 21, 5, "fast")[0]
+    Vb = b._engine.klein_sample(S, 21, 5, "fast")[0]
+    assert Va.dtype == np.float64 and Va.shape == (S, n)
+    assert np.array_equal(Va, Vb)
+    os.environ["LGS_HOST_ZEROCOPY"] = "0"        # read per call: the chunked pack-kernel route
+    try:
+        assert np.array_equal(a._engine.klein_sample(S, 21, 5, "fast")[0], Vb)
+    finally:
+        del os.environ["LGS_HOST_ZEROCOPY"]
+    # a second call reuses the mapped buffers with a new epoch
+    assert np.array_equal(a._engine.klein_sample(S // 2 + 1, 22, 0, "fast")[0], b._engine.klein_sample(S // 2 + 1, 22, 0, "fast")[0])
+    assert np.array_equal(Va, np.rint(Va)) and np.abs(Va).max() < 32768
+    # with coefficients requested the call takes the unpacked route: same points again, V = B x
+    Vc, Xc, _ = a.sample_with_coefficients(257)
+    assert np.array_equal(Vc, Xc.astype(np.float64) @ lat.basis.T)
+
+
+def test_zero_copy_over_several_full_batches(lgs):
+    """S larger than two chain-kernel batches: double-buffered mapped memory, the next launch queued while the pool
+    drains the previous batch, ragged last batch"""
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(64, seed=364)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    a = _with_pack(1, lambda: lgs.KleinSampler(lat, sigma, seed=8))
+    b = _with_pack(0, lambda: lgs.KleinSampler(lat, sigma, seed=8))
+    S = 2 * a._engine.preferred_batch + 12345
+    Va = a._engine.klein_sample(S, 8, 0, "fast")[0]
+    assert np.array_equal(Va, b._engine.klein_sample(S, 8, 0, "fast")[0])
+    # split invariance through the host route: the same ids in two calls
+    Vh = a._engine.klein_sample(1000, 8, S - 1000, "fast")[0]
+    assert np.array_equal(Vh, Va[-1000:])
+
+
+def test_values_outside_int16_fall_back_to_the_fp64_chunk(lgs):
+    from lattice_gaussian_mcmc_b200.lattices import identity_lattice
+    big = lgs.SimpleLattice(1000.0 * np.eye(16))
+    a = _with_pack(1, lambda: lgs.KleinSampler(big, 30000.0, seed=3))
+    b = _with_pack(0, lambda: lgs.KleinSampler(big, 30000.0, seed=3))
+    lat = identity_lattice(16)
+    c = np.full(16, 32760.5)      # straddles the int16 bound: a few values per chunk leave the range
+    a2 = _with_pack(1, lambda: lgs.KleinSampler(lat, 5.0, c, seed=3))
+    b2 = _with_pack(0, lambda: lgs.KleinSampler(lat, 5.0, c, seed=3))
+    for x, y in ((a, b), (a2, b2)):
+        Vx = x._engine.klein_sample(200000, 3, 0, "fast")[0]
+        Vy = y._engine.klein_sample(200000, 3, 0, "fast")[0]
+        assert np.abs(Vy).max() > 32767
+        assert np.array_equal(Vx, Vy)
+
+
+def test_real_valued_basis_is_never_packed(lgs):
+    rng = np.random.RandomState(9)
+    B = np.eye(12) * 7 + rng.uniform(-1, 1, (12, 12))
+    lat = lgs.SimpleLattice(B)
+    a = _with_pack(1, lambda: lgs.KleinSampler(lat, 30.0, seed=4))
+    b = _with_pack(0, lambda: lgs.KleinSampler(lat, 30.0, seed=4))
+    Va = a._engine.klein_sample(50000, 4, 0, "fast")[0]
+    assert not np.array_equal(Va, np.rint(Va))
+    assert np.array_equal(Va, b._engine.klein_sample(50000, 4, 0, "fast")[0])
