@@ -252,6 +252,12 @@ void lgs_destroy(lgs_handle* h) {
         if (h->zc_done[i]) cudaFreeHost(h->zc_done[i]);
         if (h->zc_ev[i]) cudaEventDestroy(h->zc_ev[i]);
     }
+    for (int i = 0; i < 2; i++) {
+        cudaFree(h->zs_dev[i]);
+        if (h->zs_reset[i]) cudaEventDestroy(h->zs_reset[i]);
+        if (h->zs_copied[i]) cudaEventDestroy(h->zs_copied[i]);
+    }
+    cudaFree(h->zs_gcnt);
     cudaFree(h->zc_cnt);
     cudaFree(h->zc_ovf);
     if (h->host_compute) cudaStreamDestroy(h->host_compute);
@@ -388,57 +394,119 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
 // buffer while the kernel is still running, so what remains after the kernel ends is the last tile of every SM.  The
 // next batch is launched before the current one is drained.  A batch in which a value left int16 is re-run through
 // the plain fp64 route (same Philox keys, same samples).
+// cuStreamWaitValue32 / cuStreamWriteValue32 through the runtime's driver entry point query (no link-time libcuda)
+typedef int (*StreamValue32Fn)(cudaStream_t, unsigned long long, unsigned, unsigned);
+struct StreamMemOps {
+    StreamValue32Fn wait = nullptr, write = nullptr;
+    bool ok = false;
+};
+static const StreamMemOps& stream_mem_ops() {
+    static StreamMemOps ops = [] {
+        StreamMemOps o;
+        void *w = nullptr, *x = nullptr;
+        cudaDriverEntryPointQueryResult q1, q2;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &w, cudaEnableDefault, &q1) == cudaSuccess &&
+            cudaGetDriverEntryPoint("cuStreamWriteValue32", &x, cudaEnableDefault, &q2) == cudaSuccess &&
+            q1 == cudaDriverEntryPointSuccess && q2 == cudaDriverEntryPointSuccess && w && x) {
+            o.wait = (StreamValue32Fn)w;
+            o.write = (StreamValue32Fn)x;
+            o.ok = true;
+        }
+        return o;
+    }();
+    return ops;
+}
+
 static int klein_host_zerocopy(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_id, double* V_host) {
     const size_t n = h->n;
     const int64_t batch = h->blocked.chain.batch;
     const int64_t cap = S < batch ? (S + 127) / 128 * 128 : batch;
     const int tiles_cap = (int)(cap / 128);
+    // Two hand-over mechanisms (both measured, tools/quick_e2e.py):
+    //   mapped    the kernel stores int16 into mapped pinned memory, one completion word per tile -- the finest-grained
+    //             hand-over and the shortest tail, but stores into host memory throttle the DMMA warps (~13 %);
+    //   streamed  the kernel keeps its int16 output in HBM; the copy engine ships finished groups of tiles behind
+    //             cuStreamWaitValue32 -- the kernel runs at full speed and batch k's transfer overlaps batch k+1.
+    // A call of one batch is bound by first-tile latency + host widening, where mapped wins (20.3 vs 21.3 ms at
+    // n = 1024); from two batches on streamed wins (18.4 vs 20.1 ms per batch).  LGS_HOST_ZEROCOPY=2 / 3 force one.
+    const char* zc_env = getenv("LGS_HOST_ZEROCOPY");
+    const int zc_mode = zc_env ? atoi(zc_env) : 1;
+    const bool streamed = stream_mem_ops().ok && zc_mode != 2 && (zc_mode == 3 || S > cap);
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    int G = sms >= 4 ? sms / 4 : 1;   // tiles per group: a quarter of one round of tiles over the SMs
+    if (const char* ge = getenv("LGS_ZC_GROUP")) G = atoi(ge) > 0 ? atoi(ge) : G;   // development
     if (h->zc_cap < (size_t)cap) {
         for (int i = 0; i < 2; i++) {
             if (h->zc_v16[i]) cudaFreeHost(h->zc_v16[i]);
             if (h->zc_done[i]) cudaFreeHost(h->zc_done[i]);
-            h->zc_v16[i] = nullptr, h->zc_done[i] = nullptr;
+            cudaFree(h->zs_dev[i]);
+            h->zc_v16[i] = nullptr, h->zc_done[i] = nullptr, h->zs_dev[i] = nullptr;
         }
         cudaFree(h->zc_cnt);
-        h->zc_cnt = nullptr, h->zc_cap = 0;
+        cudaFree(h->zs_gcnt);
+        h->zc_cnt = nullptr, h->zs_gcnt = nullptr, h->zc_cap = 0;
         for (int i = 0; i < 2; i++) {
             LGS_CUDA(h, cudaHostAlloc(&h->zc_v16[i], sizeof(int16_t) * cap * n, cudaHostAllocMapped));
             LGS_CUDA(h, cudaHostAlloc((void**)&h->zc_done[i], sizeof(unsigned) * tiles_cap, cudaHostAllocMapped));
             memset(h->zc_done[i], 0, sizeof(unsigned) * tiles_cap);
+            LGS_CUDA(h, cudaMalloc(&h->zs_dev[i], sizeof(int16_t) * cap * n));
         }
         LGS_CUDA(h, cudaMalloc((void**)&h->zc_cnt, sizeof(unsigned) * 2 * tiles_cap));
+        LGS_CUDA(h, cudaMalloc((void**)&h->zs_gcnt, sizeof(unsigned) * 2 * tiles_cap));
         if (!h->zc_ovf) LGS_CUDA(h, cudaMalloc((void**)&h->zc_ovf, sizeof(int) * 2));
         h->zc_cap = (size_t)cap;
         h->zc_epoch = 0;
     }
     if (!h->zc_ev[0])
-        for (int i = 0; i < 2; i++) LGS_CUDA(h, cudaEventCreateWithFlags(&h->zc_ev[i], cudaEventDisableTiming));
+        for (int i = 0; i < 2; i++) {
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->zc_ev[i], cudaEventDisableTiming));
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->zs_reset[i], cudaEventDisableTiming));
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->zs_copied[i], cudaEventDisableTiming));
+        }
     if (!h->pool) h->pool = hostpool_create(0);
-    cudaStream_t cs = h->host_compute;
+    cudaStream_t cs = h->host_compute, ps = h->host_copy;
     const int64_t K = (S + cap - 1) / cap;
     const int tiles_stride = (int)(h->zc_cap / 128);
     unsigned epochs[2] = {0, 0};
     auto launch = [&](int64_t k) -> int {
         const int b = (int)(k & 1);
         const int64_t s0 = k * cap, cnt = (S - s0) < cap ? (S - s0) : cap;
-        ChainZeroCopy zc;
+        const int ntiles = (int)((cnt + 127) / 128);
+        ChainZeroCopy zc{};
         void* dv = nullptr;
         void* dd = nullptr;
         LGS_CUDA(h, cudaHostGetDevicePointer(&dv, h->zc_v16[b], 0));
-        static void* dev_dummy = nullptr;   // development: LGS_ZC_DEVMEM=1 times the kernel with the int16 output in HBM
-        if (getenv("LGS_ZC_DEVMEM")) {
-            if (!dev_dummy) LGS_CUDA(h, cudaMalloc(&dev_dummy, sizeof(int16_t) * h->zc_cap * n));
-            dv = dev_dummy;
-        }
         LGS_CUDA(h, cudaHostGetDevicePointer(&dd, h->zc_done[b], 0));
-        zc.v16 = (int16_t*)dv;
+        zc.v16 = streamed ? (int16_t*)h->zs_dev[b] : (int16_t*)dv;
         zc.tile_done = (unsigned*)dd;
         zc.tile_cnt = h->zc_cnt + (size_t)b * tiles_stride;
         zc.ovf = h->zc_ovf + b;
         zc.epoch = epochs[b] = ++h->zc_epoch;
+        zc.group_cnt = streamed ? h->zs_gcnt + (size_t)b * tiles_stride : nullptr;
+        zc.group_tiles = G;
         LGS_CUDA(h, cudaMemsetAsync(zc.ovf, 0, sizeof(int), cs));
+        if (streamed) {
+            LGS_CUDA(h, cudaMemsetAsync(zc.group_cnt, 0, sizeof(unsigned) * ((ntiles + G - 1) / G), cs));
+            LGS_CUDA(h, cudaEventRecord(h->zs_reset[b], cs));
+        }
         LGS_CUDA(h, launch_klein_chain_zc(h->blocked, cnt, seed, first_id + (uint64_t)s0, zc, cs));
         LGS_CUDA(h, cudaEventRecord(h->zc_ev[b], cs));
+        if (streamed) {
+            const StreamMemOps& ops = stream_mem_ops();
+            LGS_CUDA(h, cudaStreamWaitEvent(ps, h->zs_reset[b], 0));   // the counters have been cleared
+            for (int g0 = 0, g = 0; g0 < ntiles; g0 += G, g++) {
+                const int gt = ntiles - g0 < G ? ntiles - g0 : G;
+                const int64_t r0 = (int64_t)g0 * 128, r1 = (int64_t)(g0 + gt) * 128 < cnt ? (int64_t)(g0 + gt) * 128 : cnt;
+                if (ops.wait(ps, (unsigned long long)(uintptr_t)(zc.group_cnt + g), (unsigned)gt, 0x1 /* GEQ */))
+                    return fail(h, LGS_E_CUDA, "cuStreamWaitValue32 failed");
+                LGS_CUDA(h, cudaMemcpyAsync((int16_t*)h->zc_v16[b] + (size_t)r0 * n, (const int16_t*)h->zs_dev[b] + (size_t)r0 * n,
+                                            sizeof(int16_t) * (size_t)(r1 - r0) * n, cudaMemcpyDeviceToHost, ps));
+                if (ops.write(ps, (unsigned long long)(uintptr_t)((unsigned*)dd + g), zc.epoch, 0))
+                    return fail(h, LGS_E_CUDA, "cuStreamWriteValue32 failed");
+            }
+            LGS_CUDA(h, cudaEventRecord(h->zs_copied[b], ps));
+        }
         return LGS_OK;
     };
     int rc = launch(0);
@@ -451,20 +519,22 @@ static int klein_host_zerocopy(lgs_handle* h, int64_t S, uint64_t seed, uint64_t
         const int16_t* src = (const int16_t*)h->zc_v16[b];
         volatile unsigned* done = h->zc_done[b];
         const unsigned epoch = epochs[b];
-        cudaEvent_t ev = h->zc_ev[b];
+        cudaEvent_t ev = streamed ? h->zs_copied[b] : h->zc_ev[b];
+        const int fdiv = streamed ? G : 1;   // one completion word per group / per tile
         std::atomic<int> next{0};
         std::atomic<int> failed{0};
         const int device = h->device;
-        hostpool_run(h->pool, [&, src, done, epoch, ev, ntiles, cnt, s0, device](int, int) {
+        hostpool_run(h->pool, [&, src, done, epoch, ev, ntiles, cnt, s0, device, fdiv](int, int) {
             cudaSetDevice(device);
             for (;;) {
                 const int t = next.fetch_add(1);
                 if (t >= ntiles || failed.load()) return;
+                const int f = t / fdiv;
                 unsigned spins = 0;
-                while (done[t] != epoch) {
+                while (done[f] != epoch) {
                     __builtin_ia32_pause();
                     if ((++spins & 0xfffu) == 0 && cudaEventQuery(ev) != cudaErrorNotReady) {
-                        if (done[t] == epoch) break;  // the kernel has ended: every word is out, or it failed
+                        if (done[f] == epoch) break;  // everything has been issued: the word is out, or the run failed
                         failed.store(1);
                         return;
                     }
@@ -474,7 +544,8 @@ static int klein_host_zerocopy(lgs_handle* h, int64_t S, uint64_t seed, uint64_t
                 expand_i16_range(src + (size_t)r0 * n, V_host + (size_t)(s0 + r0) * n, (size_t)(r1 - r0) * n);
             }
         });
-        LGS_CUDA(h, cudaEventSynchronize(ev));
+        LGS_CUDA(h, cudaEventSynchronize(h->zc_ev[b]));
+        if (streamed) LGS_CUDA(h, cudaEventSynchronize(h->zs_copied[b]));
         if (failed.load()) return fail(h, LGS_E_CUDA, "lgs_klein_sample_host: the chain kernel ended without publishing every tile");
         int ovf = 0;
         LGS_CUDA(h, cudaMemcpy(&ovf, h->zc_ovf + b, sizeof(int), cudaMemcpyDeviceToHost));
@@ -485,6 +556,7 @@ static int klein_host_zerocopy(lgs_handle* h, int64_t S, uint64_t seed, uint64_t
         }
     }
     LGS_CUDA(h, cudaStreamSynchronize(cs));
+    LGS_CUDA(h, cudaStreamSynchronize(ps));
     return LGS_OK;
 }
 

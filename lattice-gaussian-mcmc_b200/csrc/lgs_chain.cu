@@ -199,6 +199,12 @@ struct ChainArgs {
     unsigned* tile_done;
     int* ovf;               // set if a value does not survive the trip through int16 (the host then re-runs in fp64)
     unsigned tile_target, epoch;
+    // Streamed variant of the same (preferred: stores into host memory throttle the DMMA warps): V16 is DEVICE memory
+    // and a finished tile is counted in group_cnt[tile / group_tiles] (device); the copy stream sits on
+    // cuStreamWaitValue32(group_cnt[g] >= tiles of the group), then copies the group's int16 block to pinned host memory
+    // with the copy engine and writes the group's completion word for the host pool -- all while the kernel runs.
+    unsigned* group_cnt;
+    int group_tiles;
     int64_t S;
     int npad;               // multiple of 64
     int n_valid;            // n
@@ -386,7 +392,8 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
 #if !LGS_ZC_NOFENCE
                             __threadfence_system();
 #endif
-                            *reinterpret_cast<volatile unsigned*>(&P.tile_done[h.tile]) = P.epoch;
+                            if (P.group_cnt) atomicAdd(&P.group_cnt[h.tile / P.group_tiles], 1u);
+                            else *reinterpret_cast<volatile unsigned*>(&P.tile_done[h.tile]) = P.epoch;
                         }
                     }
                 }
@@ -1174,6 +1181,7 @@ cudaError_t launch_klein_chain_zc(BlockedCtx& bc, int64_t S, uint64_t seed, uint
     a.V = nullptr; a.ldv = 0; a.S = S;
     a.V16 = zc.v16; a.tile_cnt = zc.tile_cnt; a.tile_done = zc.tile_done; a.ovf = zc.ovf; a.epoch = zc.epoch;
     a.tile_target = kDmmaThreads / 32;
+    a.group_cnt = zc.group_cnt; a.group_tiles = zc.group_tiles;
     a.seed = seed; a.first_id = first_id; a.tag = 0u;
     a.nsteps = 1;
     return chain_launch(bc, a, false, false, false, st);

@@ -196,6 +196,10 @@ struct lgs_handle {
     size_t zc_cap = 0;                // samples per buffer
     unsigned zc_epoch = 0;
     cudaEvent_t zc_ev[2] = {};
+    // streamed variant: int16 in device memory, groups of tiles moved by the copy engine behind cuStreamWaitValue32
+    void* zs_dev[2] = {};             // device: [batch][n] int16
+    unsigned* zs_gcnt = nullptr;      // device: [2][groups]
+    cudaEvent_t zs_reset[2] = {}, zs_copied[2] = {};
     std::string err;
 };
 
@@ -225,6 +229,8 @@ struct ChainZeroCopy {
     unsigned* tile_done;  // mapped pinned host memory, device-side address: [tiles]
     int* ovf;             // device
     unsigned epoch;
+    unsigned* group_cnt;  // streamed variant (v16 in device memory): device [groups]; nullptr = publish tile_done instead
+    int group_tiles;
 };
 cudaError_t launch_klein_chain_zc(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, const ChainZeroCopy& zc,
                                   cudaStream_t st);

@@ -1,6 +1,7 @@
 """Packed device-to-host transport of lgs_klein_sample_host (integer bases: lattice points cross PCIe as int16 and are
-widened by the host pool).  Two routes: the chain kernel writing int16 straight into mapped pinned memory with per-tile
-completion words (n % 8 == 0), and chunked pack-kernel + copy (everything else, LGS_HOST_ZEROCOPY=0).  It is transport
+widened by the host pool).  Routes: the chain kernel packing int16 in its epilogue, finished groups of tiles shipped by the copy engine behind
+cuStreamWaitValue32 while the kernel runs (n % 8 == 0; calls of several batches, LGS_HOST_ZEROCOPY=3) or stored by the kernel into mapped
+pinned memory (single batch, LGS_HOST_ZEROCOPY=2), and chunked pack-kernel + copy (everything else, LGS_HOST_ZEROCOPY=0).  It is transport
 only: the float64 array handed back must be bit-identical to the plain fp64 copy (LGS_HOST_PACK=0), including batches
 that fall back to fp64 because a value leaves int16."""
 import os
@@ -44,11 +45,12 @@ def test_packed_transport_is_bit_identical_to_the_fp64_copy(lgs, n, S):
     Vb = b._engine.klein_sample(S, 21, 5, "fast")[0]
     assert Va.dtype == np.float64 and Va.shape == (S, n)
     assert np.array_equal(Va, Vb)
-    os.environ["LGS_HOST_ZEROCOPY"] = "0"        # read per call: the chunked pack-kernel route
-    try:
-        assert np.array_equal(a._engine.klein_sample(S, 21, 5, "fast")[0], Vb)
-    finally:
-        del os.environ["LGS_HOST_ZEROCOPY"]
+    for route in ("0", "2", "3"):     # read per call: chunked pack-kernel copies / mapped-memory stores / copy engine
+        os.environ["LGS_HOST_ZEROCOPY"] = route
+        try:
+            assert np.array_equal(a._engine.klein_sample(S, 21, 5, "fast")[0], Vb)
+        finally:
+            del os.environ["LGS_HOST_ZEROCOPY"]
     # a second call reuses the mapped buffers with a new epoch
     assert np.array_equal(a._engine.klein_sample(S // 2 + 1, 22, 0, "fast")[0], b._engine.klein_sample(S // 2 + 1, 22, 0, "fast")[0])
     assert np.array_equal(Va, np.rint(Va)) and np.abs(Va).max() < 32768
