@@ -278,7 +278,8 @@ def main():
         d2h = S2 * n * 8 if transport == 0 else S2 * n * 2 + 4 * ((S2 + 127) // 128)
         e2e = {"value": world * S2 * K / float(dt.item()), "unit": "samples/s", "h2d_bytes_per_step": 16,
                "d2h_bytes_per_step": d2h, "host_bytes_delivered_per_step": S2 * n * 8, "transport": tname,
-               "host_threads": int(os.environ.get("LGS_HOST_THREADS", os.cpu_count() or 1)),
+               "host_threads_per_rank": int(os.environ.get("LGS_HOST_THREADS", 0)) or max(
+                   1, len(os.sched_getaffinity(0)) // int(os.environ.get("LOCAL_WORLD_SIZE", "1"))),
                "note": "lgs_klein_sample_host: the sampler's only inputs are (seed, first id) scalars; every step "
                        "delivers its S x n float64 lattice points (the reference's return array) into a pinned host "
                        "buffer; for this integer basis they cross PCIe as int16, bit-identical after widening"}

@@ -133,7 +133,7 @@ LGS_API int lgs_klein_replay(lgs_handle *h, int64_t S, const double *U_dev, doub
  *   LGS_TRANSPORT_FP64            real-valued basis, or X_host / logq_host requested: plain fp64 copies.
  * A batch in which a value does not fit int16 is delivered through the fp64 route instead (same samples).  The array
  * handed back is bit-identical in all three (tests/test_gpu_hostpack.py).  LGS_HOST_THREADS sets the pool size
- * (default: hardware concurrency); LGS_HOST_PACK=0 / LGS_HOST_ZEROCOPY=0 select the plainer routes (development A/B). */
+ * (default: usable CPUs / LOCAL_WORLD_SIZE; with fewer than four threads the fp64 route is used); LGS_HOST_PACK=0 / LGS_HOST_ZEROCOPY=0 select the plainer routes (development A/B). */
 enum { LGS_TRANSPORT_FP64 = 0, LGS_TRANSPORT_INT16_COPY = 1, LGS_TRANSPORT_INT16_ZEROCOPY = 2 };
 LGS_API int lgs_host_transport(const lgs_handle *h); /* the route lgs_klein_sample_host(V_host only) takes on this handle */
 LGS_API int lgs_klein_sample_host(lgs_handle *h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez,

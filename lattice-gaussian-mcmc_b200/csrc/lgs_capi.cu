@@ -586,7 +586,8 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
     if (h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready)
         chunk = h->blocked.chain.batch / 3;  // three tiles per SM (one per slot): short chunks overlap the PCIe copy best
     if (chunk > S) chunk = S;
-    if (allow_pack && h->pack_ok && V_host && !X_host && !logq_host && !U_host) {
+    // widening needs host threads: below four per rank the plain fp64 copy (copy engine only) is the faster delivery
+    if (allow_pack && h->pack_ok && V_host && !X_host && !logq_host && !U_host && hostpool_default_threads() >= 4) {
         const char* zc_env = getenv("LGS_HOST_ZEROCOPY");  // development A/B: 0 = chunked packed copies instead
         const bool zc_off = zc_env && atoi(zc_env) == 0;
         const bool chain = h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready &&
@@ -642,7 +643,7 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
 
 int lgs_host_transport(const lgs_handle* h) {
     if (!h) return LGS_E_INVALID;
-    if (!h->pack_ok) return LGS_TRANSPORT_FP64;
+    if (!h->pack_ok || hostpool_default_threads() < 4) return LGS_TRANSPORT_FP64;
     const char* zc_env = getenv("LGS_HOST_ZEROCOPY");
     const bool chain = h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready && h->path != LGS_PATH_ORDERED;
     return chain && h->n % 8 == 0 && !(zc_env && atoi(zc_env) == 0) ? LGS_TRANSPORT_INT16_ZEROCOPY : LGS_TRANSPORT_INT16_COPY;

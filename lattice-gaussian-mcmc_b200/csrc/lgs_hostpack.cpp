@@ -5,6 +5,7 @@
 // chunk is re-sent as fp64) and is widened back into the caller's float64 buffer here, by a small pool of host threads
 // with non-temporal stores.  This is transport only: the values delivered are bit-identical to the fp64 copy.
 #include <immintrin.h>
+#include <sched.h>
 
 #include <condition_variable>
 #include <cstdint>
@@ -66,13 +67,27 @@ struct HostPool {
     }
 };
 
-HostPool* hostpool_create(int threads) {
-    if (threads <= 0) {
-        const char* e = std::getenv("LGS_HOST_THREADS");
-        threads = e ? std::atoi(e) : (int)std::thread::hardware_concurrency();
-        if (threads <= 0) threads = 4;
-        if (threads > 64) threads = 64;
+// LGS_HOST_THREADS, else the CPUs this process may run on divided by the ranks sharing the host (LOCAL_WORLD_SIZE of
+// torchrun): every rank of a multi-GPU job brings its own pool, and the pool threads spin on completion words
+int hostpool_default_threads() {
+    if (const char* e = std::getenv("LGS_HOST_THREADS")) {
+        const int t = std::atoi(e);
+        if (t > 0) return t > 64 ? 64 : t;
     }
+    int cpus = 0;
+    cpu_set_t set;
+    if (sched_getaffinity(0, sizeof(set), &set) == 0) cpus = CPU_COUNT(&set);
+    if (cpus <= 0) cpus = (int)std::thread::hardware_concurrency();
+    if (cpus <= 0) cpus = 4;
+    int ranks = 1;
+    if (const char* e = std::getenv("LOCAL_WORLD_SIZE")) ranks = std::atoi(e) > 0 ? std::atoi(e) : 1;
+    int t = cpus / ranks;
+    if (t < 1) t = 1;
+    return t > 64 ? 64 : t;
+}
+
+HostPool* hostpool_create(int threads) {
+    if (threads <= 0) threads = hostpool_default_threads();
     return new HostPool(threads);
 }
 

@@ -7,7 +7,8 @@
 namespace lgs {
 
 struct HostPool;
-HostPool* hostpool_create(int threads);  // threads <= 0: LGS_HOST_THREADS or the hardware concurrency
+int hostpool_default_threads();          // LGS_HOST_THREADS, else usable CPUs / LOCAL_WORLD_SIZE
+HostPool* hostpool_create(int threads);  // threads <= 0: hostpool_default_threads()
 void hostpool_destroy(HostPool* p);
 int hostpool_threads(const HostPool* p);
 // dst[i] = (double)src[i], split over the pool, non-temporal stores
