@@ -136,6 +136,9 @@ LGS_API int lgs_klein_replay(lgs_handle *h, int64_t S, const double *U_dev, doub
  * (default: usable CPUs / LOCAL_WORLD_SIZE; with fewer than four threads the fp64 route is used); LGS_HOST_PACK=0 / LGS_HOST_ZEROCOPY=0 select the plainer routes (development A/B). */
 enum { LGS_TRANSPORT_FP64 = 0, LGS_TRANSPORT_INT16_COPY = 1, LGS_TRANSPORT_INT16_ZEROCOPY = 2 };
 LGS_API int lgs_host_transport(const lgs_handle *h); /* the route lgs_klein_sample_host(V_host only) takes on this handle */
+/* the host half of the int16 transport on its own (no handle, no CUDA): dst[i] = (double)src[i], non-temporal stores,
+ * split over `threads` pool threads (0 or 1: the calling thread) */
+LGS_API int lgs_host_widen_i16(const int16_t *src, double *dst, int64_t count, int32_t threads);
 LGS_API int lgs_klein_sample_host(lgs_handle *h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez,
                           double *V_host, int64_t *X_host, double *logq_host);
 LGS_API int lgs_klein_replay_host(lgs_handle *h, int64_t S, const double *U_host, double *V_host, int64_t *X_host,

@@ -641,6 +641,18 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
     return LGS_OK;
 }
 
+int lgs_host_widen_i16(const int16_t* src, double* dst, int64_t count, int32_t threads) {
+    if (count < 0 || (count > 0 && (!src || !dst)) || threads < 0) return LGS_E_INVALID;
+    if (threads <= 1) {
+        expand_i16_range(src, dst, (size_t)count);
+        return LGS_OK;
+    }
+    HostPool* pool = hostpool_create(threads);
+    hostpool_expand_i16(pool, src, dst, (size_t)count);
+    hostpool_destroy(pool);
+    return LGS_OK;
+}
+
 int lgs_host_transport(const lgs_handle* h) {
     if (!h) return LGS_E_INVALID;
     if (!h->pack_ok || hostpool_default_threads() < 4) return LGS_TRANSPORT_FP64;

@@ -94,3 +94,21 @@ def test_lll_stand_in_reproduces_the_reference_recorded_basis_profile(n):
     assert np.all(np.abs(np.tril(mu, -1)) <= 0.5011)
     d = np.diag(R) ** 2
     assert all(d[k] >= (0.99 - mu[k, k - 1] ** 2) * d[k - 1] * (1 - 1e-12) for k in range(1, n))
+
+
+@pytest.mark.parametrize("threads", [0, 3, 8])
+def test_host_widening_of_the_int16_transport(threads):
+    """lgs_host_widen_i16 (csrc/lgs_hostpack.cpp): the host half of the packed lattice-point transport -- unaligned
+    destinations, lengths that are not a multiple of the vector width, the threaded split (no GPU involved)."""
+    from lattice_gaussian_mcmc_b200 import _capi
+    L = _capi.lib()
+    rng = np.random.RandomState(threads)
+    for count in (0, 1, 7, 8, 63, 1000, (1 << 16) + 5, 300001):
+        for off in (0, 1, 3):
+            src = rng.randint(-32768, 32768, count + 8).astype(np.int16)
+            dst = np.full(count + off + 4, np.nan)
+            rc = L.lgs_host_widen_i16(src.ctypes.data, dst[off:].ctypes.data, count, threads)
+            assert rc == 0
+            assert np.array_equal(dst[off:off + count], src[:count].astype(np.float64))
+            assert np.all(np.isnan(dst[:off])) and np.all(np.isnan(dst[off + count:]))      # nothing outside the range
+    assert L.lgs_host_widen_i16(None, None, 5, 1) == _capi.LGS_E_INVALID
