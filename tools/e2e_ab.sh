@@ -1,5 +1,10 @@
 mkdir -p gpurun_out
 {
-for g in 4 9 18 74 148; do LGS_ZC_GROUP=$g python tools/quick_e2e.py 1024 1; done
-for g in 9 18; do LGS_ZC_GROUP=$g python tools/quick_e2e.py 1024 3; done
-} > gpurun_out/quick_e2e.log 2>&1
+python -m pytest tests/test_gpu_chain.py tests/test_gpu_blocked.py -x -q 2>&1 | tail -2
+for v in "" notripred; do
+  echo "=== variant '$v'"
+  if [ -n "$v" ]; then export LGS_B200_LIB=$PWD/tools/bin/liblgs_$v.so; fi
+  python tools/quick_klein.py 1024 170496 6 2>&1 | grep -v "^setup\|smoothing\|Poorly"
+  python tools/quick_imhk.py 2>&1 | grep -v "^setup\|smoothing\|Poorly" | tail -4
+done
+} > gpurun_out/ab.log 2>&1
