@@ -530,6 +530,7 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
                 start_step(s);
             } else {  // no step, only the flush (+ lattice points) of the current states: wake the panel warpgroup
                 s_pair[s] = npairs;
+                s_ahead[s] = npairs;   // nothing to look ahead to
                 push(F_FIRST | F_LAST | F_NODATA | F_NOSTORE, s, 0, s_tile[s], nullptr, nullptr);
             }
         } else {

@@ -36,3 +36,12 @@ eng.profile_enable(False)
 ms, cnt = prof["chain"]
 print(f"n={n} S={S} host call {dt*1e3:.2f} ms = {S/dt/1e6:.2f} M samples/s | chain kernel {ms/max(cnt,1):.2f} ms x {cnt/reps:.1f} per call"
       f" | env pack={os.environ.get('LGS_HOST_PACK')} zc={os.environ.get('LGS_HOST_ZEROCOPY')} threads={os.environ.get('LGS_HOST_THREADS')}")
+
+# the user-facing call: KleinSampler.sample(S) returns a FRESH pageable float64 array (klein.py:322)
+for _ in range(2):
+    smp.sample(S)
+t0 = time.perf_counter()
+for r in range(3):
+    out = smp.sample(S)
+dt = (time.perf_counter() - t0) / 3
+print(f"KleinSampler.sample({S}) -> {out.shape} {out.dtype}: {dt*1e3:.2f} ms = {S/dt/1e6:.2f} M samples/s (fresh pageable array per call)")
