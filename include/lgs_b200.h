@@ -131,6 +131,8 @@ LGS_API int lgs_klein_replay(lgs_handle *h, int64_t S, const double *U_dev, doub
  *                                 host widens finished tiles while the kernel is still running (one launch per batch);
  *   LGS_TRANSPORT_INT16_COPY      any other kernel path: sample + pack kernel + copy in chunks, widened two chunks behind;
  *   LGS_TRANSPORT_FP64            real-valued basis, or X_host / logq_host requested: plain fp64 copies.
+ * lgs_imhk_run_host ships kept states of an integer basis the same way (pack kernel + chunked copies + widening) once
+ * they exceed 4 Mi values.
  * A batch in which a value does not fit int16 is delivered through the fp64 route instead (same samples).  The array
  * handed back is bit-identical in all three (tests/test_gpu_hostpack.py).  LGS_HOST_THREADS sets the pool size
  * (default: usable CPUs / LOCAL_WORLD_SIZE; with fewer than four threads the fp64 route is used); LGS_HOST_PACK=0 / LGS_HOST_ZEROCOPY=0 select the plainer routes (development A/B). */

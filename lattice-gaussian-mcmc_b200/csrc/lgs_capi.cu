@@ -388,6 +388,87 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
                              int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host,
                              bool allow_pack);
 
+static int ensure_host_streams(lgs_handle* h) {
+    if (h->host_compute) return LGS_OK;
+    LGS_CUDA(h, cudaStreamCreateWithFlags(&h->host_compute, cudaStreamNonBlocking));
+    LGS_CUDA(h, cudaStreamCreateWithFlags(&h->host_copy, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+        LGS_CUDA(h, cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+        LGS_CUDA(h, cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
+    }
+    return LGS_OK;
+}
+
+// Lattice points that already sit in device memory as fp64 [rows][n] (complete: the producing work has been
+// synchronised) -> the caller's float64 host array, over the int16 transport: pack kernel and copy in chunks on two
+// streams, widened by the host pool two chunks behind; a chunk with a value outside int16 is copied as fp64.
+static int ship_points_packed(lgs_handle* h, const double* dV, int64_t rows, double* V_host) {
+    const size_t n = h->n;
+    int rc = ensure_host_streams(h);
+    if (rc) return rc;
+    int64_t chunk = (int64_t)((size_t)48 << 20) / (int64_t)n;   // ~48 M values = 96 MB of int16 per chunk
+    if (chunk < 1024) chunk = 1024;
+    if (chunk > rows) chunk = rows;
+    const size_t bP = align256(sizeof(int16_t) * chunk * n) + 256;  // + flag
+    if (h->pack_dev_cap < kPackDev * bP) {
+        cudaFree(h->pack_dev);
+        h->pack_dev = nullptr, h->pack_dev_cap = 0;
+        LGS_CUDA(h, cudaMalloc(&h->pack_dev, kPackDev * bP));
+        h->pack_dev_cap = kPackDev * bP;
+    }
+    if (h->pack_host_cap < kPackHost * bP) {
+        if (h->pack_host) cudaFreeHost(h->pack_host);
+        h->pack_host = nullptr, h->pack_host_cap = 0;
+        LGS_CUDA(h, cudaHostAlloc(&h->pack_host, kPackHost * bP, cudaHostAllocDefault));
+        h->pack_host_cap = kPackHost * bP;
+    }
+    if (!h->pool) h->pool = hostpool_create(0);
+    if (!h->pk_done[0])
+        for (int i = 0; i < 3; i++) {
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->pk_done[i], cudaEventDisableTiming));
+            LGS_CUDA(h, cudaEventCreateWithFlags(&h->pk_copied[i], cudaEventDisableTiming));
+        }
+    cudaStream_t cs = h->host_compute, ps = h->host_copy;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    const int64_t K = (rows + chunk - 1) / chunk;
+    const int lag = 2;
+    for (int64_t k = 0; k < K + lag; k++) {
+        if (k < K) {
+            const int64_t r0 = k * chunk, cnt = (rows - r0) < chunk ? (rows - r0) : chunk;
+            const int b = (int)(k % kPackDev);
+            uint8_t* slot = (uint8_t*)h->pack_dev + (size_t)b * bP;   // last used by chunk k-3, widened at iteration k-1
+            int16_t* dP = (int16_t*)slot;
+            int32_t* dflag = (int32_t*)(slot + bP - 256);
+            LGS_CUDA(h, cudaMemsetAsync(dflag, 0, sizeof(int32_t), cs));
+            pack_points_i16<<<sms * 8, 256, 0, cs>>>(dV + (size_t)r0 * n, dP, (size_t)cnt * n, dflag);
+            LGS_CUDA(h, cudaGetLastError());
+            LGS_CUDA(h, cudaEventRecord(h->pk_done[b], cs));
+            LGS_CUDA(h, cudaStreamWaitEvent(ps, h->pk_done[b], 0));
+            uint8_t* hp = (uint8_t*)h->pack_host + (size_t)(k % kPackHost) * bP;
+            LGS_CUDA(h, cudaMemcpyAsync(hp, dP, sizeof(int16_t) * cnt * n, cudaMemcpyDeviceToHost, ps));
+            LGS_CUDA(h, cudaMemcpyAsync(hp + bP - 256, dflag, sizeof(int32_t), cudaMemcpyDeviceToHost, ps));
+            LGS_CUDA(h, cudaEventRecord(h->pk_copied[k % kPackHost], ps));
+        }
+        const int64_t j = k - lag;
+        if (j >= 0) {
+            const int64_t r0 = j * chunk, cnt = (rows - r0) < chunk ? (rows - r0) : chunk;
+            LGS_CUDA(h, cudaEventSynchronize(h->pk_copied[j % kPackHost]));
+            const uint8_t* hp = (const uint8_t*)h->pack_host + (size_t)(j % kPackHost) * bP;
+            if (*(const int32_t*)(hp + bP - 256)) {
+                LGS_CUDA(h, cudaMemcpyAsync(V_host + (size_t)r0 * n, dV + (size_t)r0 * n, sizeof(double) * cnt * n,
+                                            cudaMemcpyDeviceToHost, ps));
+                LGS_CUDA(h, cudaStreamSynchronize(ps));
+            } else {
+                hostpool_expand_i16(h->pool, (const int16_t*)hp, V_host + (size_t)r0 * n, (size_t)cnt * n);
+            }
+        }
+    }
+    LGS_CUDA(h, cudaStreamSynchronize(cs));
+    LGS_CUDA(h, cudaStreamSynchronize(ps));
+    return LGS_OK;
+}
+
 // Host-buffer Klein call on the chain kernel for an integer basis with n % 8 == 0, lattice points only.  ONE launch per
 // full batch: the kernel's lattice-point epilogue writes int16 straight into mapped pinned host memory and publishes a
 // per-tile completion word; the host pool picks finished tiles up in order and widens them into the caller's float64
@@ -573,13 +654,9 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
     LGS_CUDA(h, cudaSetDevice(h->device));
     const size_t n = h->n;
     const int ups = h->ctx.ups;
-    if (!h->host_compute) {
-        LGS_CUDA(h, cudaStreamCreateWithFlags(&h->host_compute, cudaStreamNonBlocking));
-        LGS_CUDA(h, cudaStreamCreateWithFlags(&h->host_copy, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; i++) {
-            LGS_CUDA(h, cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
-            LGS_CUDA(h, cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
-        }
+    {
+        const int rcs = ensure_host_streams(h);
+        if (rcs) return rcs;
     }
     // chunk = two full waves of contraction tiles on the blocked path (75 776 samples on a B200), else 64 Ki
     int64_t chunk = h->blocked.ready && h->blocked.wave > 0 ? 2 * h->blocked.wave : (int64_t)65536;
@@ -831,7 +908,17 @@ static int imhk_host_common(lgs_handle* h, int64_t burn_in, int64_t keep, int64_
         rc = lgs_imhk_run(h, burn_in, keep, thin, samplez, weight_mode, dV, dX, nullptr);
     }
     if (rc) return rc;
-    if (V_host && keep) LGS_CUDA(h, cudaMemcpy(V_host, dV, sizeof(double) * C * keep * n, cudaMemcpyDeviceToHost));
+    if (V_host && keep) {
+        // kept states of an integer basis travel as int16 (same transport as lgs_klein_sample_host), once they are
+        // large enough for the pipeline to matter
+        if (h->pack_ok && hostpool_default_threads() >= 4 && (size_t)C * keep * n >= ((size_t)1 << 22)) {
+            LGS_CUDA(h, cudaDeviceSynchronize());
+            rc = ship_points_packed(h, dV, C * keep, V_host);
+            if (rc) return rc;
+        } else {
+            LGS_CUDA(h, cudaMemcpy(V_host, dV, sizeof(double) * C * keep * n, cudaMemcpyDeviceToHost));
+        }
+    }
     if (X_host && keep) LGS_CUDA(h, cudaMemcpy(X_host, dX, sizeof(int64_t) * C * keep * n, cudaMemcpyDeviceToHost));
     if (accept_host && steps) LGS_CUDA(h, cudaMemcpy(accept_host, dA, (size_t)C * steps, cudaMemcpyDeviceToHost));
     if (logw_host) LGS_CUDA(h, cudaMemcpy(logw_host, dW, sizeof(double) * C * (steps + 1), cudaMemcpyDeviceToHost));

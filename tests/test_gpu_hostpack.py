@@ -100,3 +100,21 @@ def test_real_valued_basis_is_never_packed(lgs):
     Va = a._engine.klein_sample(50000, 4, 0, "fast")[0]
     assert not np.array_equal(Va, np.rint(Va))
     assert np.array_equal(Va, b._engine.klein_sample(50000, 4, 0, "fast")[0])
+
+
+def test_imhk_kept_states_travel_packed_and_match_the_fp64_copy(lgs):
+    """lgs_imhk_run_host: kept states [chains, keep, n] of an integer basis over the int16 transport (several chunks),
+    and a centre that pushes some values out of int16 (those chunks fall back to fp64)"""
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice, identity_lattice
+    lat = dd_lattice(64, seed=77)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    cases = [(lat, sigma, None, 4096, 500), (identity_lattice(16), 5.0, np.full(16, 32760.5), 8192, 48)]
+    for L, sg, c, chains, keep in cases:
+        mk = lambda: lgs.IMHKSampler(L, sg, c, burn_in=0, n_chains=chains, seed=13)   # noqa: E731
+        a = _with_pack(1, mk)
+        b = _with_pack(0, mk)
+        Va = a.sample(keep, thin=1)
+        Vb = b.sample(keep, thin=1)
+        assert Va.shape == Vb.shape and Va.dtype == np.float64 and Va.size >= 1 << 22
+        assert np.array_equal(Va, Vb)
+        assert a.acceptance_rate == b.acceptance_rate
