@@ -745,8 +745,11 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     const int4 ci = sp.ci[j];
                     const double mean = c[kSubW - 1];  // 1/r_ii is folded into the centers and the triangle
                     double x;
+                    // rounded once for all three uses (ptxas if-converts the deterministic-coordinate branch below and used
+                    // to issue a second, predicated-off FRND.F64 on every coordinate)
+                    const double rmean = rint(mean);
                     if (ci.w) {
-                        x = rint(mean);
+                        x = rmean;
                     } else {
                         if ((ci.z >> 1) != wpair) {
                             wpair = ci.z >> 1;
@@ -761,14 +764,14 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                         const bool dl_ok = rint_delta_f32(mean, &dlf);
 #else
                         const bool dl_ok = true;
-                        dlf = (float)(rint(mean) - mean);
+                        dlf = (float)(rmean - mean);
 #endif
                         if (ci.x <= 1 && dl_ok) {  // smooth regime, eligible for the FP32 screen
                             // no FP64 instruction between the window update above and x below: a panel warp's first
                             // FP64 instruction after a stretch of other work waits for a whole DMMA burst
                             float off, corr;
                             done = samplez_smooth_screen(dlf, sp.cf[j], kind, ci.y, uhi, &off, &corr);
-                            x = rint(mean) + (double)off;
+                            x = rmean + (double)off;
                             if (WANT_LZ && done) lza += cc.lognz + (double)corr;
                         }
                         if (!done) {
