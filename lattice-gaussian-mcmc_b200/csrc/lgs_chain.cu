@@ -94,7 +94,7 @@ __device__ __forceinline__ void dmma_16x8x8(double (&d)[4], const double (&a)[4]
 
 // DMMA.8x8x4, the SASS unit an m16n8k8 is split into.  volatile: the issue order of these is chosen by hand, see
 // LGS_CHAIN_DEPDIST.  Fragments: a = A[g][t], b = B[t][g], d = C[g][2t], C[g][2t+1]  (g = lane / 4, t = lane % 4)
-__device__ __forceinline__ void dmma_8x8x4(double (&d)[2], const double a, const double b) {
+[[maybe_unused]] __device__ __forceinline__ void dmma_8x8x4(double (&d)[2], const double a, const double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
                  : "+d"(d[0]), "+d"(d[1])
                  : "d"(a), "d"(b));
@@ -508,9 +508,9 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     };
 
     int next_tile = blockIdx.x;
-    int s_pair[kSlots], s_tile[kSlots];   // s_pair: pairs whose centers have been completed (part B issued)
-    int s_ahead[kSlots];                  // next pair whose part A has not been issued yet
-    int s_step[kSlots];                   // Metropolis-Hastings step of the launch the slot's tile is in (Klein: 0)
+    int s_pair[kSlots] = {}, s_tile[kSlots] = {};   // s_pair: pairs whose centers have been completed (part B issued)
+    int s_ahead[kSlots] = {};             // next pair whose part A has not been issued yet
+    int s_step[kSlots] = {};              // Metropolis-Hastings step of the launch the slot's tile is in (Klein: 0)
     uint32_t pd_par[kSlots];
     bool s_active[kSlots];
     int n_active = 0;
