@@ -3,6 +3,7 @@
 // MEASURED_PEAKS.json carries no FP64 figure, so bench.py reads the number this prints.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/bin/fp64_peak tools/fp64_peak.cu
 #include <cstdio>
+#include <string>
 #include <cstdlib>
 #include <cuda_runtime.h>
 
@@ -117,6 +118,51 @@ __global__ void __launch_bounds__(256) k_i2d(double* out, int iters, int a) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s0 + s1 + s2 + s3;
 }
 
+// --occupancy: how many DMMA warps per SM sub-partition does it take to fill the pipe?  Register-resident operands
+// (k_occ<false>) and the chain kernel's k8-step shape -- 8 + 8 LDS.64 fragment loads, then 8 m16n8k8 on 8 independent
+// accumulator tiles -- with operands in shared memory (k_occ<true>); one CTA per SM.
+template <bool LDS>
+__global__ void __launch_bounds__(1024, 1) k_occ(double* out, int iters, double a, double b) {
+    extern __shared__ double sm[];
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    for (int i = threadIdx.x; i < 64 * 20 + 16 * 132; i += blockDim.x) sm[i] = a + i * 1e-9;
+    __syncthreads();
+    const double* A = sm;            // [64][20]
+    const double* B = sm + 64 * 20;  // [16][132]
+    double c[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { c[i][0] = threadIdx.x; c[i][1] = i; c[i][2] = 1; c[i][3] = 2; }
+    double af[2][4] = {{a, a * 0.5, a * 0.25, a * 0.125}, {b, b * 0.5, b * 0.25, b * 0.125}};
+    double bf[4][2] = {{b, a}, {b * 0.5, a}, {b * 0.25, a}, {b * 0.125, a}};
+    for (int it = 0; it < iters; it++) {
+        if (LDS) {
+            asm volatile("" ::: "memory");   // reload every iteration, but let ptxas schedule the loads as it likes
+            const int kk = (it & 1) * 8;
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+                const double* ap = &A[(mt * 16 + g) * 20 + kk + t];
+                af[mt][0] = ap[0]; af[mt][1] = ap[8 * 20]; af[mt][2] = ap[4]; af[mt][3] = ap[8 * 20 + 4];
+            }
+#pragma unroll
+            for (int nt = 0; nt < 4; nt++) {
+                const double* bp = &B[(kk + t) * 132 + nt * 8 + g];
+                bf[nt][0] = bp[0]; bf[nt][1] = bp[4 * 132];
+            }
+        }
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+            for (int nt = 0; nt < 4; nt++)
+                asm volatile("mma.sync.aligned.m16n8k8.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                             : "+d"(c[mt * 4 + nt][0]), "+d"(c[mt * 4 + nt][1]), "+d"(c[mt * 4 + nt][2]), "+d"(c[mt * 4 + nt][3])
+                             : "d"(af[mt][0]), "d"(af[mt][1]), "d"(af[mt][2]), "d"(af[mt][3]), "d"(bf[nt][0]), "d"(bf[nt][1]));
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <typename F>
 static double time_ms(F launch, int reps) {
     cudaEvent_t e0, e1;
@@ -148,6 +194,25 @@ int main(int argc, char** argv) {
     auto gf = [&](double flops_per_thread_iter, double ms) { return thr * iters * flops_per_thread_iter / (ms * 1e-3) / 1e12; };
 
     double ms;
+    if (argc > 1 && std::string(argv[1]) == "--occupancy") {
+        const int smem = (64 * 20 + 16 * 132) * 8;
+        printf("{\"dmma_tflops_by_warps_per_subpartition\": {");
+        const int ws[] = {1, 2, 3, 4, 8};
+        for (int lds = 0; lds < 2; lds++) {
+            printf("%s\"%s\": {", lds ? ", " : "", lds ? "operands_from_shared_memory" : "register_operands");
+            for (int i = 0; i < 5; i++) {
+                const int w = ws[i], threads = 128 * w, it2 = 40000;
+                ms = time_ms([&] {
+                    if (lds) k_occ<true><<<sms, threads, smem>>>(out, it2, 1.0000001, 1e-9);
+                    else k_occ<false><<<sms, threads, smem>>>(out, it2, 1.0000001, 1e-9);
+                }, 5);
+                printf("%s\"%d\": %.3f", i ? ", " : "", w, (double)sms * threads / 32 * it2 * 8 * 2048.0 / (ms * 1e-3) / 1e12);
+            }
+            printf("}");
+        }
+        printf("}}\n");
+        return 0;
+    }
     ms = time_ms([&] { k_dfma<8><<<grid, 256>>>(out, iters, 1.0000001, 1e-9); }, 5);
     double dfma8 = gf(8 * 2, ms);
     ms = time_ms([&] { k_dfma<16><<<grid, 256>>>(out, iters, 1.0000001, 1e-9); }, 5);
