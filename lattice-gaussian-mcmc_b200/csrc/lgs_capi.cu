@@ -1,4 +1,6 @@
 // C ABI of liblgs_b200.so (include/lgs_b200.h): handle management, per-sampler constants, dispatch.
+#include <sched.h>
+
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -614,7 +616,8 @@ static int klein_host_zerocopy(lgs_handle* h, int64_t S, uint64_t seed, uint64_t
                 unsigned spins = 0;
                 while (done[f] != epoch) {
                     __builtin_ia32_pause();
-                    if ((++spins & 0xfffu) == 0 && cudaEventQuery(ev) != cudaErrorNotReady) {
+                    if ((++spins & 0xffu) == 0) sched_yield();   // be polite when the host is oversubscribed
+                    if ((spins & 0xfffu) == 0 && cudaEventQuery(ev) != cudaErrorNotReady) {
                         if (done[f] == epoch) break;  // everything has been issued: the word is out, or the run failed
                         failed.store(1);
                         return;
