@@ -64,3 +64,56 @@ class ChainDiagnostics:
         out["acf"] = acf
         out["gr_sums"] = sums
         return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# D1: total-variation distance between two sample sets / acceptance rate, with the reference's semantics
+# ---------------------------------------------------------------------------------------------------------
+def compute_tvd(samples1, samples2, bins=None) -> float:
+    """Host drop-in for compute_tvd (src/diagnostics/convergence_diag.py:15-72) on numpy arrays: exact-value counting
+    in 1-D (or a shared-range histogram when `bins` is given), the MEAN of the per-coordinate marginal TVDs for
+    [S, n] inputs."""
+    a, b = np.asarray(samples1), np.asarray(samples2)
+    if a.ndim == 1 and b.ndim == 1:
+        if bins is None:
+            values, inv = np.unique(np.concatenate([a, b]), return_inverse=True)
+            p1 = np.bincount(inv[:len(a)], minlength=len(values)) / len(a)
+            p2 = np.bincount(inv[len(a):], minlength=len(values)) / len(b)
+            return float(0.5 * np.abs(p1 - p2).sum())
+        lo, hi = min(a.min(), b.min()), max(a.max(), b.max())
+        h1, _ = np.histogram(a, bins=bins, range=(lo, hi))
+        h2, _ = np.histogram(b, bins=bins, range=(lo, hi))
+        return float(0.5 * np.abs(h1 / h1.sum() - h2 / h2.sum()).sum())
+    return float(np.mean([compute_tvd(a[:, i], b[:, i], bins) for i in range(a.shape[1])]))
+
+
+def compute_acceptance_rate(accepted) -> float:
+    """mcmc_diag.py:107-117: the mean of a boolean array of accept / reject decisions."""
+    return float(np.mean(np.asarray(accepted)))
+
+
+def device_tvd(sampler_or_engine, V1: torch.Tensor, V2: torch.Tensor, dims=None, group=None) -> float:
+    """compute_tvd (bins=None) of two device-resident sets of INTEGER-valued lattice points `[S1, n]`, `[S2, n]` (CUDA
+    float64, e.g. what lgs_klein_sample writes) without moving them to the host: exact-value counting is a histogram
+    with unit bins centred on the integers, accumulated by `lgs_histogram`; with a process group the int64 bins are
+    summed over ranks first (every rank holds its share of both sets).  Returns the mean marginal TVD over `dims`
+    (default: every coordinate), as the reference does for multivariate input."""
+    eng = getattr(sampler_or_engine, "_engine", sampler_or_engine)
+    n = V1.shape[1]
+    dims = np.arange(n, dtype=np.int32) if dims is None else np.ascontiguousarray(dims, dtype=np.int32)
+    ext = torch.stack([torch.minimum(V1.min(), V2.min()), torch.maximum(V1.max(), V2.max())])
+    if group is not None or (dist.is_available() and dist.is_initialized()):
+        ext[0] = -ext[0]
+        dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=group)   # shared binning on every rank
+        ext[0] = -ext[0]
+    lo, hi = (float(x) for x in ext.tolist())
+    nbins = int(round(hi - lo)) + 1
+    hist = torch.zeros((2, len(dims), nbins), dtype=torch.int64, device=V1.device)
+    st = torch.cuda.current_stream().cuda_stream
+    eng.histogram_dev(V1.data_ptr(), V1.shape[0], dims, lo - 0.5, 1.0, nbins, hist[0].data_ptr(), stream=st)
+    eng.histogram_dev(V2.data_ptr(), V2.shape[0], dims, lo - 0.5, 1.0, nbins, hist[1].data_ptr(), stream=st)
+    if group is not None or (dist.is_available() and dist.is_initialized()):
+        dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
+    h = hist.to(torch.float64)
+    p = h / h.sum(dim=-1, keepdim=True)
+    return float((0.5 * (p[0] - p[1]).abs().sum(dim=-1)).mean())

@@ -53,3 +53,30 @@ def gelman_rubin_statistic(chains):
     B = n / (m - 1) * sum((mu - overall) ** 2 for mu in means)
     W = np.mean([np.var(c, ddof=1) for c in chains])
     return float(np.sqrt((((n - 1) / n) * W + B / n) / W))
+
+
+def compute_tvd(samples1, samples2, bins=None):
+    """convergence_diag.py:15-72.  1-D, bins=None: exact-value counting over the union of values,
+    0.5 * sum |n1(v)/N1 - n2(v)/N2|; 1-D with bins: np.histogram of both on the shared [min, max] range, each
+    normalised by its own total; multivariate: MEAN of the per-coordinate TVDs.  Pinned: tests/golden/tvd_d1.npz
+    (minted by tests/golden/make_golden_tvd.py from the reference's function)."""
+    a, b = np.asarray(samples1), np.asarray(samples2)
+    if a.ndim == 1 and b.ndim == 1:
+        if bins is None:
+            values, inv = np.unique(np.concatenate([a, b]), return_inverse=True)
+            c1 = np.bincount(inv[:len(a)], minlength=len(values)) / len(a)
+            c2 = np.bincount(inv[len(a):], minlength=len(values)) / len(b)
+            tvd = 0.0
+            for p1, p2 in zip(c1, c2):      # the reference accumulates value by value, in sorted order
+                tvd += abs(p1 - p2)
+            return 0.5 * tvd
+        lo, hi = min(a.min(), b.min()), max(a.max(), b.max())
+        h1, _ = np.histogram(a, bins=bins, range=(lo, hi))
+        h2, _ = np.histogram(b, bins=bins, range=(lo, hi))
+        return 0.5 * np.abs(h1 / h1.sum() - h2 / h2.sum()).sum()
+    return float(np.mean([compute_tvd(a[:, i], b[:, i], bins) for i in range(a.shape[1])]))
+
+
+def compute_acceptance_rate(accepted):
+    """mcmc_diag.py:107-117."""
+    return np.mean(accepted)

@@ -97,3 +97,33 @@ def test_diagnostics_argument_errors(lgs):
         d.run(V.cpu(), [0])
     with pytest.raises(Exception):
         d.run(torch.zeros((3, 1, 4), dtype=torch.float64, device="cuda"), [0])   # a series needs two points
+
+
+def test_device_tvd_matches_the_reference_golden(lgs):
+    """D1 on device-resident samples: lgs_histogram with unit bins == the reference's exact-value counting
+    (convergence_diag.py:15-72; tests/golden/tvd_d1.npz holds the reference's own outputs)."""
+    import os
+    import torch
+    from lattice_gaussian_mcmc_b200 import diagnostics as D
+    from lattice_gaussian_mcmc_b200.lattices import identity_lattice
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "tvd_d1.npz"))
+    for name in g["names"]:
+        a, b, want = g[f"{name}_a"], g[f"{name}_b"], float(g[f"{name}_tvd"][0])
+        if a.ndim == 1:
+            a, b = a[:, None], b[:, None]
+        smp = lgs.KleinSampler(identity_lattice(a.shape[1]), 5.0, seed=1)
+        A = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        B = torch.from_numpy(np.ascontiguousarray(b)).cuda()
+        assert D.device_tvd(smp, A, B) == pytest.approx(want, rel=0, abs=1e-14)
+    # and on the sampler's own output: two independent native batches of Z^10 are close, a wider sigma is not
+    lat = identity_lattice(10)
+    s5, s7 = lgs.KleinSampler(lat, 5.0, seed=2), lgs.KleinSampler(lat, 7.0, seed=3)
+    S = 40000
+    V = [torch.empty((S, 10), dtype=torch.float64, device="cuda") for _ in range(3)]
+    st = torch.cuda.current_stream().cuda_stream
+    s5._engine.klein_sample_dev(S, 2, 0, "fast", V=V[0].data_ptr(), stream=st)
+    s5._engine.klein_sample_dev(S, 2, S, "fast", V=V[1].data_ptr(), stream=st)
+    s7._engine.klein_sample_dev(S, 3, 0, "fast", V=V[2].data_ptr(), stream=st)
+    same, wider = D.device_tvd(s5, V[0], V[1]), D.device_tvd(s5, V[0], V[2])
+    assert same == pytest.approx(D.compute_tvd(V[0].cpu().numpy(), V[1].cpu().numpy()), abs=1e-14)
+    assert same < 0.03 < 0.1 < wider

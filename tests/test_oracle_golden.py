@@ -106,3 +106,20 @@ def test_diagnostics_oracle_reproduces_reference_golden():
     # multivariate ESS = minimum over coordinates (mcmc_diag.py:98-105)
     xm = np.stack([X[0, 0], X[3, 0]], axis=1)
     assert do.effective_sample_size(xm) == min(do.effective_sample_size(xm[:, 0]), do.effective_sample_size(xm[:, 1]))
+
+
+def test_tvd_and_acceptance_rate_match_the_reference_golden(golden_dir):
+    """D1: compute_tvd / compute_acceptance_rate -- the oracle restatement and the product's host drop-in
+    against outputs of the reference's own functions (tests/golden/tvd_d1.npz, minted by make_golden_tvd.py)."""
+    import os
+    from oracle import diag_oracle
+    from lattice_gaussian_mcmc_b200 import diagnostics as D
+    g = np.load(os.path.join(golden_dir, "tvd_d1.npz"))
+    for name in g["names"]:
+        a, b, want = g[f"{name}_a"], g[f"{name}_b"], g[f"{name}_tvd"]
+        for bins, w in zip((None, 16, 50), want):
+            assert diag_oracle.compute_tvd(a, b, bins) == pytest.approx(w, rel=0, abs=1e-15)
+            assert D.compute_tvd(a, b, bins) == pytest.approx(w, rel=0, abs=1e-14)
+    for acc, w in zip(g["accepted"], g["acceptance_rate"]):
+        assert diag_oracle.compute_acceptance_rate(acc) == w and D.compute_acceptance_rate(acc) == w
+    assert D.compute_acceptance_rate(g["accepted"]) == float(g["acceptance_rate_all"])
