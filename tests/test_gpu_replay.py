@@ -200,3 +200,25 @@ def test_constructor_errors_match_reference(lgs):
         lgs.IMHKSampler(lat, -2.0)
     smp = lgs.KleinSampler(lat, 1.0)
     assert smp.compute_log_density(np.array([0.5, 0.0, 0.0])) == -np.inf  # not a lattice point (klein.py:237-240)
+
+
+@pytest.mark.parametrize("name", ["dd8", "dd24"])
+def test_m6_spectral_gap_and_diagnose_convergence_match_the_reference(lgs, name):
+    """M6 (imhk.py:252-313) in replay mode against values the reference itself produced after np.random.seed
+    (tests/golden/m6_imhk_diag.npz, minted by make_golden_m6.py): same stream consumption order
+    (k Klein samples; then chain init + num steps; then 100 Klein samples), same numbers."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "m6_imhk_diag.npz"))
+    B, sigma = g[f"{name}_basis"], float(g[f"{name}_sigma"])
+    k, num = int(g[f"{name}_k"]), int(g[f"{name}_num"])
+    im = lgs.IMHKSampler(lgs.SimpleLattice(B), sigma, burn_in=5, mode="replay", uniforms=g[f"{name}_uniforms"])
+    assert im.klein_log_partition == pytest.approx(float(g[f"{name}_klein_log_partition"]), rel=1e-13)
+    gap = im.estimate_spectral_gap(k)
+    assert gap == pytest.approx(float(g[f"{name}_gap"]), rel=1e-9)
+    d = im.diagnose_convergence(num)
+    assert d["acceptance_rate"] == float(g[f"{name}_acceptance_rate"])
+    assert d["spectral_gap_estimate"] == pytest.approx(float(g[f"{name}_gap2"]), rel=1e-9)
+    np.testing.assert_allclose(d["empirical_mean"], g[f"{name}_empirical_mean"], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(d["empirical_std"], g[f"{name}_empirical_std"], rtol=1e-13)
+    np.testing.assert_array_equal(d["theoretical_std"], g[f"{name}_theoretical_std"])
+    assert im.proposal_sampler._upos == g[f"{name}_uniforms"].size          # the whole recorded stream, no more
