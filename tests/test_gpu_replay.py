@@ -222,3 +222,53 @@ def test_m6_spectral_gap_and_diagnose_convergence_match_the_reference(lgs, name)
     np.testing.assert_allclose(d["empirical_std"], g[f"{name}_empirical_std"], rtol=1e-13)
     np.testing.assert_array_equal(d["theoretical_std"], g[f"{name}_theoretical_std"])
     assert im.proposal_sampler._upos == g[f"{name}_uniforms"].size          # the whole recorded stream, no more
+
+
+def test_small_api_surface_matches_the_reference(lgs):
+    """B2 / B3 / K6 / K7 / M1 of SURVEY 8a -- the small methods around the hot path -- in replay mode against values the
+    reference itself produced (tests/golden/surface_api.npz, minted by make_golden_surface.py)."""
+    import json
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "surface_api.npz"))
+    B, c, sigma = g["basis"], g["center"], float(g["sigma"])
+    S, k = int(g["S"]), int(g["k"])
+    lat = lgs.SimpleLattice(B, name="dd8-surface")
+    smp = lgs.RefinedKleinSampler(lat, sigma, c, mode="replay", uniforms=g["uniforms"])
+    V = smp.sample(S)
+    assert np.array_equal(V, g["V"])
+    X = smp.sample_coefficients(k)                       # the kernel's coefficients == the reference's lstsq + round
+    assert X.shape == (k, 8) and np.array_equal(X, g["X"])
+    for p, lw, w, ld in zip(g["points"], g["log_gaussian_weight"], g["gaussian_weight"], g["log_density"]):
+        assert smp.log_gaussian_weight(p) == pytest.approx(lw, rel=1e-14)
+        assert smp.gaussian_weight(p) == pytest.approx(w, rel=1e-12)
+        assert smp.compute_log_density(p) == pytest.approx(ld, rel=1e-12)
+    assert smp.compute_log_density(g["off_point"]) == -np.inf and float(g["log_density_off"]) == -np.inf
+    np.testing.assert_allclose(smp.empirical_mean(V), g["empirical_mean"], rtol=0, atol=1e-13)
+    np.testing.assert_allclose(smp.empirical_covariance(V), g["empirical_covariance"], rtol=1e-12, atol=1e-12)
+    np.testing.assert_array_equal(smp.theoretical_covariance(), g["theoretical_covariance"])
+    want = json.loads(str(g["diagnostic_info"]))
+    got = smp.diagnostic_info()
+    assert set(got) >= set(want) - {"cache_size"}
+    for key, val in want.items():
+        if key == "cache_size":
+            continue                                     # the reference's table cache has no counterpart
+        if isinstance(val, (str, bool)):
+            assert got[key] == val
+        else:
+            assert got[key] == pytest.approx(val, rel=1e-12)
+    st = smp.get_stats()
+    assert json.loads(str(g["stats"])) == {"samples_generated": st.samples_generated, "acceptance_rate": st.acceptance_rate}
+    assert repr(smp) == str(g["repr_klein"])
+    smp.reset_stats()
+    assert smp.get_stats().samples_generated == 0
+    # default burn-in estimate (imhk.py:68-91) incl. its 10 000 cap, and klein_log_partition (93-100)
+    for key, val in json.loads(str(g["burn_in"])).items():
+        nn, ratio = key.split(":")
+        im = lgs.IMHKSampler(lgs.SimpleLattice(np.eye(int(nn)) * 10.0), 10.0 * float(ratio))
+        assert im.burn_in == val
+    im = lgs.IMHKSampler(lat, sigma, c, burn_in=17, mode="replay", uniforms=g["imhk_uniforms"])
+    assert im.klein_log_partition == pytest.approx(float(g["imhk_klein_log_partition"]), rel=1e-14)
+    assert isinstance(repr(im), str)                     # the reference raises TypeError here before any sampling
+    assert bool(g["repr_imhk_raises_before_sampling"])
+    im.sample(3)
+    assert repr(im) == str(g["repr_imhk"])
