@@ -213,7 +213,7 @@ struct ChainArgs {
     uint64_t seed, first_id;
     uint32_t tag;
     double inv_two_sigma2;  // 1 / (2 sigma^2)
-    unsigned long long* stats;  // development counters (LGS_CHAIN_STATS=1), 8 per CTA, or nullptr
+    unsigned long long* stats;  // development counters (LGS_CHAIN_STATS=1), 12 per CTA, or nullptr
     // IMHK (imhk.py:126-177): nsteps Metropolis-Hastings steps per chain in this launch, tags tag .. tag + nsteps - 1
     int nsteps;             // Klein: 1
     int first_is_init;      // the first step is _initialize_chain (tag 0): no accept test, no count
@@ -441,9 +441,9 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
         }
     }
     if (rec) {
-        P.stats[blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - t_begin);
-        P.stats[blockIdx.x * 8 + 1] = (unsigned long long)t_wait;
-        P.stats[blockIdx.x * 8 + 2] = it;
+        P.stats[blockIdx.x * 12 + 0] = (unsigned long long)(clock64() - t_begin);
+        P.stats[blockIdx.x * 12 + 1] = (unsigned long long)t_wait;
+        P.stats[blockIdx.x * 12 + 2] = it;
     }
 }
 
@@ -614,8 +614,8 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     }
     push(F_EXIT, 0, 0, -1, nullptr, nullptr);
     if (rec) {
-        P.stats[blockIdx.x * 8 + 3] = (unsigned long long)t_empty;
-        P.stats[blockIdx.x * 8 + 4] = (unsigned long long)t_idle;
+        P.stats[blockIdx.x * 12 + 3] = (unsigned long long)t_empty;
+        P.stats[blockIdx.x * 12 + 4] = (unsigned long long)t_idle;
     }
 }
 
@@ -641,14 +641,18 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     double* __restrict__ xsw = &sm.xs[slot][0][wbase];    // the warp's 32 columns (DMMA fragments)
     uint32_t cr_par = 0, q = 0;
     const bool rec = P.stats && slot == 0 && sl == 0;
-    long long t_cwait = 0;
+    long long t_cwait = 0, t_top = 0, t_cfull = 0, t_bar = 0;
     const long long t_begin = rec ? clock64() : 0;
     // bytes of the constants of the sub-block whose rows-below count is `base` (the rect rows come last)
     auto sub_bytes = [](int base) -> uint32_t {
         return (uint32_t)(offsetof(SubPack, rect) + ((base + 15) / 16 * 16) * kRectLd * sizeof(double));
     };
     for (;;) {
-        mbar_wait(&sm.cready[slot], cr_par);
+        {
+            const long long t0 = rec ? clock64() : 0;
+            mbar_wait(&sm.cready[slot], cr_par);
+            if (rec) t_top += clock64() - t0;
+        }
         cr_par ^= 1;
         const int tile = sm.slot_tile[slot];
         if (tile < 0) break;
@@ -719,7 +723,11 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                 // the sub-block after next (no warpgroup-wide barrier in the coordinate loop)
                 auto release_sub = [&](int b) {
 #if !LGS_CHAIN_NOBAR
-                    named_bar_sync(1 + slot, 128);
+                    {
+                        const long long t0 = rec ? clock64() : 0;
+                        named_bar_sync(1 + slot, 128);
+                        if (rec) t_bar += clock64() - t0;
+                    }
                     if (sl == 0 && isub + 2 < nsub) load_sub(isub + 2, q + 1);
                     isub++;
                     return;
@@ -735,7 +743,11 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     __syncwarp();
                     isub++;
                 };
-                mbar_wait(&sm.cfull[slot][buf], (q >> 1) & 1);
+                {
+                    const long long t0 = rec ? clock64() : 0;
+                    mbar_wait(&sm.cfull[slot][buf], (q >> 1) & 1);
+                    if (rec) t_cfull += clock64() - t0;
+                }
                 q++;
                 const SubPack& sp = sm.sub[slot][buf];
                 double* __restrict__ xp = xt + (size_t)(lo + base + kSubW - 1) * kRowLd;
@@ -912,8 +924,11 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
         }
     }
     if (rec) {
-        P.stats[blockIdx.x * 8 + 5] = (unsigned long long)(clock64() - t_begin);
-        P.stats[blockIdx.x * 8 + 6] = (unsigned long long)t_cwait;
+        P.stats[blockIdx.x * 12 + 5] = (unsigned long long)(clock64() - t_begin);
+        P.stats[blockIdx.x * 12 + 6] = (unsigned long long)t_cwait;
+        P.stats[blockIdx.x * 12 + 7] = (unsigned long long)t_top;
+        P.stats[blockIdx.x * 12 + 8] = (unsigned long long)t_cfull;
+        P.stats[blockIdx.x * 12 + 9] = (unsigned long long)t_bar;
     }
 }
 
@@ -1134,7 +1149,7 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     const int grid = a.ntiles < sms ? a.ntiles : sms;
     static const bool want_stats = getenv("LGS_CHAIN_STATS") != nullptr;
     static unsigned long long* stats_dev = nullptr;
-    if (want_stats && !stats_dev) cudaMalloc(&stats_dev, sizeof(unsigned long long) * 8 * 1024);
+    if (want_stats && !stats_dev) cudaMalloc(&stats_dev, sizeof(unsigned long long) * 12 * 1024);
     a.stats = want_stats ? stats_dev : nullptr;
     {
         ProfScope ps(bc.prof, LGS_PROF_CHAIN, st);
@@ -1144,17 +1159,18 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
         else klein_chain_kernel<false, false, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
     }
     if (want_stats) {  // development only: synchronous read-back, mean over CTAs
-        std::vector<unsigned long long> hs((size_t)grid * 8);
+        std::vector<unsigned long long> hs((size_t)grid * 12);
         cudaStreamSynchronize(st);
         cudaMemcpy(hs.data(), stats_dev, sizeof(unsigned long long) * hs.size(), cudaMemcpyDeviceToHost);
-        double m[8] = {};
+        double m[12] = {};
         for (int b = 0; b < grid; b++)
-            for (int k = 0; k < 8; k++) m[k] += (double)hs[(size_t)b * 8 + k] / grid;
+            for (int k = 0; k < 12; k++) m[k] += (double)hs[(size_t)b * 12 + k] / grid;
         fprintf(stderr,
                 "[chain stats] grid %d tiles %d V=%d steps=%d | dmma total %.0f kcyc, wait-full %.0f (%.1f%%), stages %.0f | "
-                "producer wait-empty %.0f idle %.0f | panel0 total %.0f wait-centers %.0f (%.1f%%)\n",
+                "producer wait-empty %.0f idle %.0f | panel0 total %.0f wait-centers %.0f (%.1f%%) wait-tile %.0f "
+                "wait-constants %.0f sub-block barrier %.0f\n",
                 grid, a.ntiles, a.V ? 1 : 0, a.nsteps, m[0] / 1e3, m[1] / 1e3, 100.0 * m[1] / (m[0] + 1), m[2], m[3] / 1e3,
-                m[4] / 1e3, m[5] / 1e3, m[6] / 1e3, 100.0 * m[6] / (m[5] + 1));
+                m[4] / 1e3, m[5] / 1e3, m[6] / 1e3, 100.0 * m[6] / (m[5] + 1), m[7] / 1e3, m[8] / 1e3, m[9] / 1e3);
     }
     return cudaGetLastError();
 }
