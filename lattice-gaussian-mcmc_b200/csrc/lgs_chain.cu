@@ -227,6 +227,16 @@ struct ChainArgs {
     long long* counts;      // [cap][2] accepted, total
 };
 
+// Development cycle counters (read with LGS_CHAIN_STATS=1 in the environment) exist only in a
+// -DLGS_CHAIN_STATS_BUILD=1 build (tools/build_variant.sh): even predicated-off clock reads cost the panel loop
+// 0.5 % (Klein) to 2.7 % (IMHK).  LGS_CHAIN_STATS_DETAIL=1 adds the tile / constants / sub-block barrier waits.
+#ifndef LGS_CHAIN_STATS_BUILD
+#define LGS_CHAIN_STATS_BUILD 0
+#endif
+constexpr bool kStatsBuild = LGS_CHAIN_STATS_BUILD != 0;
+#ifndef LGS_CHAIN_STATS_DETAIL
+#define LGS_CHAIN_STATS_DETAIL 0
+#endif
 #ifndef LGS_ZC_NOFENCE
 #define LGS_ZC_NOFENCE 0   // development: time the zero-copy epilogue without its system-scope fences (NOT correct)
 #endif
@@ -260,7 +270,7 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
     double acc[2][4][4];
 #endif
     uint32_t it = 0;
-    const bool rec = P.stats && tid == 0;
+    const bool rec = kStatsBuild && P.stats && tid == 0;
     long long t_wait = 0;
     const long long t_begin = rec ? clock64() : 0;
     for (;; it++) {
@@ -456,7 +466,7 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     const int nkt = P.npad / kBK;
     uint32_t it = 0;
     long long t_empty = 0, t_idle = 0;
-    const bool rec = P.stats != nullptr;
+    const bool rec = kStatsBuild && P.stats != nullptr;
     auto push = [&](int flags, int slot, int r0, int tile, const double* asrc, const double* bsrc) {
         const int stage = it % kStages;
         if (rec) {
@@ -640,7 +650,9 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     double* __restrict__ xs = &sm.xs[slot][0][sl];        // this thread's column of the sub-block's draws
     double* __restrict__ xsw = &sm.xs[slot][0][wbase];    // the warp's 32 columns (DMMA fragments)
     uint32_t cr_par = 0, q = 0;
-    const bool rec = P.stats && slot == 0 && sl == 0;
+    const bool rec = kStatsBuild && P.stats && slot == 0 && sl == 0;
+    constexpr bool kDetail = LGS_CHAIN_STATS_DETAIL != 0;
+    const bool rec2 = kDetail && rec;
     long long t_cwait = 0, t_top = 0, t_cfull = 0, t_bar = 0;
     const long long t_begin = rec ? clock64() : 0;
     // bytes of the constants of the sub-block whose rows-below count is `base` (the rect rows come last)
@@ -649,9 +661,9 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     };
     for (;;) {
         {
-            const long long t0 = rec ? clock64() : 0;
+            const long long t0 = rec2 ? clock64() : 0;
             mbar_wait(&sm.cready[slot], cr_par);
-            if (rec) t_top += clock64() - t0;
+            if (rec2) t_top += clock64() - t0;
         }
         cr_par ^= 1;
         const int tile = sm.slot_tile[slot];
@@ -724,9 +736,9 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                 auto release_sub = [&](int b) {
 #if !LGS_CHAIN_NOBAR
                     {
-                        const long long t0 = rec ? clock64() : 0;
+                        const long long t0 = rec2 ? clock64() : 0;
                         named_bar_sync(1 + slot, 128);
-                        if (rec) t_bar += clock64() - t0;
+                        if (rec2) t_bar += clock64() - t0;
                     }
                     if (sl == 0 && isub + 2 < nsub) load_sub(isub + 2, q + 1);
                     isub++;
@@ -744,9 +756,9 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     isub++;
                 };
                 {
-                    const long long t0 = rec ? clock64() : 0;
+                    const long long t0 = rec2 ? clock64() : 0;
                     mbar_wait(&sm.cfull[slot][buf], (q >> 1) & 1);
-                    if (rec) t_cfull += clock64() - t0;
+                    if (rec2) t_cfull += clock64() - t0;
                 }
                 q++;
                 const SubPack& sp = sm.sub[slot][buf];
@@ -1147,7 +1159,7 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     a.want_lz = want_lz ? 1 : 0;
     const int sms = bc.sm_count > 0 ? bc.sm_count : 148;
     const int grid = a.ntiles < sms ? a.ntiles : sms;
-    static const bool want_stats = getenv("LGS_CHAIN_STATS") != nullptr;
+    static const bool want_stats = kStatsBuild && getenv("LGS_CHAIN_STATS") != nullptr;
     static unsigned long long* stats_dev = nullptr;
     if (want_stats && !stats_dev) cudaMalloc(&stats_dev, sizeof(unsigned long long) * 12 * 1024);
     a.stats = want_stats ? stats_dev : nullptr;
