@@ -250,6 +250,10 @@ void lgs_destroy(lgs_handle* h) {
     }
     hostpool_destroy(h->pool);
     for (int i = 0; i < 2; i++) {
+        if (h->bounce[i]) cudaFreeHost(h->bounce[i]);
+        if (h->bounce_ev[i]) cudaEventDestroy(h->bounce_ev[i]);
+    }
+    for (int i = 0; i < 2; i++) {
         if (h->zc_v16[i]) cudaFreeHost(h->zc_v16[i]);
         if (h->zc_done[i]) cudaFreeHost(h->zc_done[i]);
         if (h->zc_ev[i]) cudaEventDestroy(h->zc_ev[i]);
@@ -397,6 +401,63 @@ static int ensure_host_streams(lgs_handle* h) {
     for (int i = 0; i < 2; i++) {
         LGS_CUDA(h, cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
         LGS_CUDA(h, cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
+    }
+    return LGS_OK;
+}
+
+// Device -> host copy on stream ps for results whose destination may be PAGEABLE memory (a fresh numpy array): the
+// driver's own pageable path is a single-threaded bounce; here the bytes land in a two-deep pinned ring at full PCIe
+// rate and the host pool moves each piece on with non-temporal stores (faulting the destination's pages in parallel)
+// while the next piece is in flight.  Pinned / registered destinations and small copies are a plain cudaMemcpyAsync.
+// Returns with the copy either complete (staged) or enqueued on ps (direct): callers synchronise ps before returning.
+static const size_t kBouncePiece = [] {
+    const char* e = std::getenv("LGS_BOUNCE_MB");   // development override of the piece size
+    const int mb = e ? std::atoi(e) : 0;
+    return (size_t)(mb > 0 && mb <= 1024 ? mb : 32) << 20;
+}();
+static constexpr size_t kBounceMin = (size_t)8 << 20;
+
+static bool host_memory_is_pinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
+static bool bounce_enabled() {
+    static const bool on = [] {
+        const char* e = std::getenv("LGS_HOST_BOUNCE");
+        return !(e && e[0] == '0') && hostpool_default_threads() >= 2;
+    }();
+    return on;
+}
+
+static int staged_d2h(lgs_handle* h, void* dst, const void* src_dev, size_t bytes, cudaStream_t ps) {
+    if (!bytes) return LGS_OK;
+    if (bytes < kBounceMin || !bounce_enabled() || host_memory_is_pinned(dst)) {
+        LGS_CUDA(h, cudaMemcpyAsync(dst, src_dev, bytes, cudaMemcpyDeviceToHost, ps));
+        return LGS_OK;
+    }
+    for (int i = 0; i < 2; i++) {
+        if (!h->bounce[i]) LGS_CUDA(h, cudaHostAlloc(&h->bounce[i], kBouncePiece, cudaHostAllocDefault));
+        if (!h->bounce_ev[i]) LGS_CUDA(h, cudaEventCreateWithFlags(&h->bounce_ev[i], cudaEventDisableTiming));
+    }
+    if (!h->pool) h->pool = hostpool_create(0);
+    const size_t pieces = (bytes + kBouncePiece - 1) / kBouncePiece;
+    for (size_t i = 0; i <= pieces; i++) {
+        if (i < pieces) {
+            const size_t off = i * kBouncePiece, len = bytes - off < kBouncePiece ? bytes - off : kBouncePiece;
+            LGS_CUDA(h, cudaMemcpyAsync(h->bounce[i & 1], (const uint8_t*)src_dev + off, len, cudaMemcpyDeviceToHost, ps));
+            LGS_CUDA(h, cudaEventRecord(h->bounce_ev[i & 1], ps));
+        }
+        if (i >= 1) {  // piece i-1 has landed: move it on while piece i crosses PCIe
+            const size_t j = i - 1, off = j * kBouncePiece;
+            const size_t len = bytes - off < kBouncePiece ? bytes - off : kBouncePiece;
+            LGS_CUDA(h, cudaEventSynchronize(h->bounce_ev[j & 1]));
+            hostpool_copy(h->pool, h->bounce[j & 1], (uint8_t*)dst + off, len);
+        }
     }
     return LGS_OK;
 }
@@ -685,33 +746,47 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
     int32_t* dfb = (int32_t*)((uint8_t*)h->stage_dev + 2 * slot);
     cudaStream_t cs = h->host_compute, ps = h->host_copy;
     if (U_host && fb_host) LGS_CUDA(h, cudaMemsetAsync(dfb, 0, sizeof(int32_t), cs));
-    int k = 0;
-    for (int64_t s0 = 0; s0 < S; s0 += chunk, k++) {
-        const int64_t cnt = (S - s0) < chunk ? (S - s0) : chunk;
-        const int b = k & 1;
+    // chunk k is enqueued on the compute stream first, then chunk k-1 leaves for the host: the staged copy of a
+    // pageable destination blocks this thread, and the device works on chunk k meanwhile
+    const int64_t K = (S + chunk - 1) / chunk;
+    auto slot_ptrs = [&](int b, double*& dV, int64_t*& dX, double*& dq, double*& dU) {
         uint8_t* p = (uint8_t*)h->stage_dev + b * slot;
-        double* dV = V_host ? (double*)p : nullptr; p += bV;
-        int64_t* dX = X_host ? (int64_t*)p : nullptr; p += bX;
-        double* dq = logq_host ? (double*)p : nullptr; p += bq;
-        double* dU = U_host ? (double*)p : nullptr;
-        if (k >= 2) LGS_CUDA(h, cudaStreamWaitEvent(cs, h->ev_free[b], 0));  // slot b has left for the host
-        if (U_host) {
-            LGS_CUDA(h, cudaMemcpyAsync(dU, U_host + (size_t)s0 * ups, sizeof(double) * cnt * ups,
-                                        cudaMemcpyHostToDevice, cs));
-            RngSpec rng{dU, ups, 0, 0};
-            // the fallback counter accumulates over chunks (no per-chunk reset)
-            LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, cnt, rng, LGS_SAMPLEZ_TABLE, dV, dX, dq,
-                                             fb_host ? dfb : nullptr, cs));
-        } else {
-            rc = lgs_klein_sample(h, cnt, seed, first_id + (uint64_t)s0, samplez, dV, dX, dq, cs);
-            if (rc) return rc;
+        dV = V_host ? (double*)p : nullptr; p += bV;
+        dX = X_host ? (int64_t*)p : nullptr; p += bX;
+        dq = logq_host ? (double*)p : nullptr; p += bq;
+        dU = U_host ? (double*)p : nullptr;
+    };
+    for (int64_t k = 0; k <= K; k++) {
+        double *dV, *dq, *dU;
+        int64_t* dX;
+        if (k < K) {
+            const int64_t s0 = k * chunk, cnt = (S - s0) < chunk ? (S - s0) : chunk;
+            const int b = (int)(k & 1);
+            slot_ptrs(b, dV, dX, dq, dU);
+            if (k >= 2) LGS_CUDA(h, cudaStreamWaitEvent(cs, h->ev_free[b], 0));  // slot b has left for the host
+            if (U_host) {
+                LGS_CUDA(h, cudaMemcpyAsync(dU, U_host + (size_t)s0 * ups, sizeof(double) * cnt * ups,
+                                            cudaMemcpyHostToDevice, cs));
+                RngSpec rng{dU, ups, 0, 0};
+                // the fallback counter accumulates over chunks (no per-chunk reset)
+                LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, cnt, rng, LGS_SAMPLEZ_TABLE, dV, dX, dq,
+                                                 fb_host ? dfb : nullptr, cs));
+            } else {
+                rc = lgs_klein_sample(h, cnt, seed, first_id + (uint64_t)s0, samplez, dV, dX, dq, cs);
+                if (rc) return rc;
+            }
+            LGS_CUDA(h, cudaEventRecord(h->ev_done[b], cs));
         }
-        LGS_CUDA(h, cudaEventRecord(h->ev_done[b], cs));
-        LGS_CUDA(h, cudaStreamWaitEvent(ps, h->ev_done[b], 0));
-        if (V_host) LGS_CUDA(h, cudaMemcpyAsync(V_host + (size_t)s0 * n, dV, sizeof(double) * cnt * n, cudaMemcpyDeviceToHost, ps));
-        if (X_host) LGS_CUDA(h, cudaMemcpyAsync(X_host + (size_t)s0 * n, dX, sizeof(int64_t) * cnt * n, cudaMemcpyDeviceToHost, ps));
-        if (logq_host) LGS_CUDA(h, cudaMemcpyAsync(logq_host + s0, dq, sizeof(double) * cnt, cudaMemcpyDeviceToHost, ps));
-        LGS_CUDA(h, cudaEventRecord(h->ev_free[b], ps));
+        if (k >= 1) {
+            const int64_t j = k - 1, s0 = j * chunk, cnt = (S - s0) < chunk ? (S - s0) : chunk;
+            const int b = (int)(j & 1);
+            slot_ptrs(b, dV, dX, dq, dU);
+            LGS_CUDA(h, cudaStreamWaitEvent(ps, h->ev_done[b], 0));
+            if (V_host && (rc = staged_d2h(h, V_host + (size_t)s0 * n, dV, sizeof(double) * cnt * n, ps))) return rc;
+            if (X_host && (rc = staged_d2h(h, X_host + (size_t)s0 * n, dX, sizeof(int64_t) * cnt * n, ps))) return rc;
+            if (logq_host) LGS_CUDA(h, cudaMemcpyAsync(logq_host + s0, dq, sizeof(double) * cnt, cudaMemcpyDeviceToHost, ps));
+            LGS_CUDA(h, cudaEventRecord(h->ev_free[b], ps));
+        }
     }
     LGS_CUDA(h, cudaStreamSynchronize(ps));
     if (fb_host && U_host) {
@@ -919,10 +994,18 @@ static int imhk_host_common(lgs_handle* h, int64_t burn_in, int64_t keep, int64_
             rc = ship_points_packed(h, dV, C * keep, V_host);
             if (rc) return rc;
         } else {
-            LGS_CUDA(h, cudaMemcpy(V_host, dV, sizeof(double) * C * keep * n, cudaMemcpyDeviceToHost));
+            LGS_CUDA(h, cudaDeviceSynchronize());
+            if ((rc = ensure_host_streams(h))) return rc;
+            if ((rc = staged_d2h(h, V_host, dV, sizeof(double) * C * keep * n, h->host_copy))) return rc;
+            LGS_CUDA(h, cudaStreamSynchronize(h->host_copy));
         }
     }
-    if (X_host && keep) LGS_CUDA(h, cudaMemcpy(X_host, dX, sizeof(int64_t) * C * keep * n, cudaMemcpyDeviceToHost));
+    if (X_host && keep) {
+        LGS_CUDA(h, cudaDeviceSynchronize());
+        if ((rc = ensure_host_streams(h))) return rc;
+        if ((rc = staged_d2h(h, X_host, dX, sizeof(int64_t) * C * keep * n, h->host_copy))) return rc;
+        LGS_CUDA(h, cudaStreamSynchronize(h->host_copy));
+    }
     if (accept_host && steps) LGS_CUDA(h, cudaMemcpy(accept_host, dA, (size_t)C * steps, cudaMemcpyDeviceToHost));
     if (logw_host) LGS_CUDA(h, cudaMemcpy(logw_host, dW, sizeof(double) * C * (steps + 1), cudaMemcpyDeviceToHost));
     if (fb_host && U_host) LGS_CUDA(h, cudaMemcpy(fb_host, dfb, sizeof(int32_t), cudaMemcpyDeviceToHost));

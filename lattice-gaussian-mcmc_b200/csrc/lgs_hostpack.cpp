@@ -130,4 +130,35 @@ void hostpool_expand_i16(HostPool* p, const int16_t* src, double* dst, size_t co
     });
 }
 
+// dst[0, bytes) = src[0, bytes) on the calling thread; non-temporal stores once the destination is 32-byte aligned
+static void copy_range_nt(const uint8_t* src, uint8_t* dst, size_t bytes) {
+    size_t i = 0;
+    while (i < bytes && ((uintptr_t)(dst + i) & 31)) {
+        dst[i] = src[i];
+        i++;
+    }
+    for (; i + 64 <= bytes; i += 64) {
+        const __m256i a = _mm256_loadu_si256((const __m256i*)(src + i));
+        const __m256i b = _mm256_loadu_si256((const __m256i*)(src + i + 32));
+        _mm256_stream_si256((__m256i*)(dst + i), a);
+        _mm256_stream_si256((__m256i*)(dst + i + 32), b);
+    }
+    for (; i < bytes; i++) dst[i] = src[i];
+    _mm_sfence();
+}
+
+void hostpool_copy(HostPool* p, const void* src, void* dst, size_t bytes) {
+    if (!p || bytes < (size_t)1 << 18) {
+        copy_range_nt((const uint8_t*)src, (uint8_t*)dst, bytes);
+        return;
+    }
+    p->run([=](int tid, int threads) {
+        const size_t per = ((bytes + threads - 1) / threads + 4095) & ~(size_t)4095;
+        const size_t lo = per * (size_t)tid;
+        if (lo >= bytes) return;
+        const size_t hi = lo + per < bytes ? lo + per : bytes;
+        copy_range_nt((const uint8_t*)src + lo, (uint8_t*)dst + lo, hi - lo);
+    });
+}
+
 }  // namespace lgs

@@ -200,6 +200,9 @@ struct lgs_handle {
     void* zs_dev[2] = {};             // device: [batch][n] int16
     unsigned* zs_gcnt = nullptr;      // device: [2][groups]
     cudaEvent_t zs_reset[2] = {}, zs_copied[2] = {};
+    // pinned bounce ring for fp64 / int64 results that go to pageable host memory (staged_d2h in lgs_capi.cu)
+    void* bounce[2] = {};
+    cudaEvent_t bounce_ev[2] = {};
     std::string err;
 };
 

@@ -14,6 +14,9 @@ int hostpool_threads(const HostPool* p);
 // dst[i] = (double)src[i], split over the pool, non-temporal stores
 void hostpool_expand_i16(HostPool* p, const int16_t* src, double* dst, size_t count);
 
+// dst[0, bytes) = src[0, bytes), split over the pool, non-temporal stores (pinned staging -> pageable destination)
+void hostpool_copy(HostPool* p, const void* src, void* dst, size_t bytes);
+
 // run job(thread id, thread count) on every pool thread and wait for all of them
 void hostpool_run(HostPool* p, const std::function<void(int, int)>& job);
 // dst[i] = (double)src[i] on the calling thread, non-temporal stores

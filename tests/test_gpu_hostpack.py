@@ -118,3 +118,39 @@ def test_imhk_kept_states_travel_packed_and_match_the_fp64_copy(lgs):
         assert Va.shape == Vb.shape and Va.dtype == np.float64 and Va.size >= 1 << 22
         assert np.array_equal(Va, Vb)
         assert a.acceptance_rate == b.acceptance_rate
+
+
+def test_pageable_destinations_take_the_pinned_bounce_ring_and_match_the_device_result(lgs):
+    """fp64 points, int64 coefficients and log q of several chunks delivered to pageable numpy arrays (staged through
+    the pinned ring, pieces of 32 MB, ragged last piece) == the same call with page-locked destinations (direct
+    cudaMemcpyAsync) == the device-resident result of the same seed and sample ids."""
+    import torch
+    from lattice_gaussian_mcmc_b200 import _capi
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    n, S = 200, 2 * 65536 + 4321            # 211 MB of points: several pieces per chunk
+    lat = dd_lattice(n, seed=91)
+    smp = _with_pack(0, lambda: lgs.KleinSampler(lat, 1.5 * lat.max_gram_schmidt_norm, seed=8))
+    eng = smp._engine
+    V, X, lq = eng.klein_sample(S, 8, 3, "fast", want_v=True, want_x=True, want_logq=True)
+    Vd = torch.empty((S, n), dtype=torch.float64, device="cuda")
+    Xd = torch.empty((S, n), dtype=torch.int64, device="cuda")
+    qd = torch.empty(S, dtype=torch.float64, device="cuda")
+    eng.klein_sample_dev(S, 8, 3, "fast", V=Vd.data_ptr(), X=Xd.data_ptr(), logq=qd.data_ptr(),
+                         stream=torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(V, Vd.cpu().numpy()) and np.array_equal(X, Xd.cpu().numpy())
+    assert np.array_equal(lq, qd.cpu().numpy())
+    Vp = torch.empty((S, n), dtype=torch.float64).pin_memory()
+    Xp = torch.empty((S, n), dtype=torch.int64).pin_memory()
+    _capi.check(eng._h, _capi.lib().lgs_klein_sample_host(eng._h, S, 8, 3, _capi.SAMPLEZ["fast"],
+                                                          Vp.data_ptr(), Xp.data_ptr(), None))
+    assert np.array_equal(V, Vp.numpy()) and np.array_equal(X, Xp.numpy())
+    # IMHK kept states and coefficients of a real-valued basis (never packed): pageable, above the staging threshold
+    rng = np.random.RandomState(2)
+    B = np.eye(32) * 9 + rng.uniform(-1, 1, (32, 32))
+    im = lgs.IMHKSampler(lgs.SimpleLattice(B), 40.0, burn_in=0, n_chains=4096, seed=5)
+    im._engine.imhk_reset(4096, seed=5)
+    Vk, Xk = im._engine.imhk_run(0, 80, 1, "fast", "reference", want_v=True, want_x=True)
+    assert Vk.nbytes >= 8 << 20 and Xk.nbytes >= 8 << 20
+    np.testing.assert_allclose(Vk, Xk.astype(np.float64) @ B.T, rtol=0, atol=1e-9)
+    assert len(np.unique(Xk[:, -1, 0])) > 3
