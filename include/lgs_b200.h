@@ -135,7 +135,9 @@ LGS_API int lgs_klein_replay(lgs_handle *h, int64_t S, const double *U_dev, doub
  * they exceed 4 Mi values.
  * A batch in which a value does not fit int16 is delivered through the fp64 route instead (same samples).  The array
  * handed back is bit-identical in all three (tests/test_gpu_hostpack.py).  LGS_HOST_THREADS sets the pool size
- * (default: usable CPUs / LOCAL_WORLD_SIZE; with fewer than four threads the fp64 route is used); LGS_HOST_PACK=0 / LGS_HOST_ZEROCOPY=0 select the plainer routes (development A/B). */
+ * (default: usable CPUs / LOCAL_WORLD_SIZE; with fewer than four threads the fp64 route is used); LGS_HOST_PACK=0 / LGS_HOST_ZEROCOPY=0 select the plainer routes (development A/B).
+ * fp64 / int64 results bound for PAGEABLE host memory (>= 8 MB) are staged through a pinned ring and moved on by the
+ * same pool (LGS_HOST_BOUNCE=0: the driver's pageable copy); page-locked destinations are copied directly. */
 enum { LGS_TRANSPORT_FP64 = 0, LGS_TRANSPORT_INT16_COPY = 1, LGS_TRANSPORT_INT16_ZEROCOPY = 2 };
 LGS_API int lgs_host_transport(const lgs_handle *h); /* the route lgs_klein_sample_host(V_host only) takes on this handle */
 /* the host half of the int16 transport on its own (no handle, no CUDA): dst[i] = (double)src[i], non-temporal stores,
