@@ -29,15 +29,22 @@ struct HostPool {
     bool stop = false;
 
     explicit HostPool(int threads) {
-        for (int t = 0; t < threads; t++) workers.emplace_back([this, t, threads] { loop(t, threads); });
+        try {
+            for (int t = 0; t < threads; t++) workers.emplace_back([this, t, threads] { loop(t, threads); });
+        } catch (...) {  // thread limit reached: release the ones that did start, let the caller fall back
+            shutdown();
+            throw;
+        }
     }
-    ~HostPool() {
+    ~HostPool() { shutdown(); }
+    void shutdown() {
         {
             std::lock_guard<std::mutex> lk(mtx);
             stop = true;
         }
         cv_go.notify_all();
         for (auto& w : workers) w.join();
+        workers.clear();
     }
     void loop(int tid, int threads) {
         uint64_t seen = 0;
@@ -88,7 +95,11 @@ int hostpool_default_threads() {
 
 HostPool* hostpool_create(int threads) {
     if (threads <= 0) threads = hostpool_default_threads();
-    return new HostPool(threads);
+    try {
+        return new HostPool(threads);
+    } catch (...) {
+        return nullptr;  // every user below runs the job on the calling thread when there is no pool
+    }
 }
 
 void hostpool_destroy(HostPool* p) { delete p; }
@@ -114,7 +125,12 @@ void expand_i16_range(const int16_t* src, double* dst, size_t count) {
     _mm_sfence();
 }
 
-void hostpool_run(HostPool* p, const std::function<void(int, int)>& job) { p->run(job); }
+void hostpool_run(HostPool* p, const std::function<void(int, int)>& job) {
+    if (p)
+        p->run(job);
+    else
+        job(0, 1);
+}
 
 void hostpool_expand_i16(HostPool* p, const int16_t* src, double* dst, size_t count) {
     if (!p || count < (size_t)1 << 16) {
