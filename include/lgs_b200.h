@@ -39,7 +39,7 @@ enum {
     LGS_OK = 0,
     LGS_E_INVALID = -1, /* bad argument (n <= 0, sigma <= 0, NULL pointer, ...) */
     LGS_E_CUDA = -2,    /* CUDA runtime error; text in lgs_last_error() */
-    LGS_E_NOMEM = -3,   /* device allocation failed */
+    LGS_E_NOMEM = -3,   /* device (or, in the host-side reducer, host) allocation failed */
     LGS_E_STATE = -4,   /* call not valid in the current chain state */
     LGS_E_FALLBACK = -5, /* replay: a draw hit the reference's no-uniform fallback (klein.py:176-179) */
     LGS_E_RANGE = -6,    /* basis reduction: an integer left the exact range (|entry| >= 2^56 or a transform overflow) */

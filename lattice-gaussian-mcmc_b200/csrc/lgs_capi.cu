@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
 #include <vector>
 
 #include "lgs_internal.h"
@@ -102,7 +103,19 @@ int lgs_abi_version(void) { return LGS_ABI_VERSION; }
 
 const char* lgs_last_error(const lgs_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
 
+static int create_impl(const lgs_desc* d, lgs_handle** out);
+
 int lgs_create(const lgs_desc* d, lgs_handle** out) {
+    try {
+        return create_impl(d, out);
+    } catch (const std::bad_alloc&) {  // host-side setup arrays: nothing throws across the ABI
+        return fail(nullptr, LGS_E_NOMEM, "lgs_create: host allocation failed");
+    } catch (...) {
+        return fail(nullptr, LGS_E_INVALID, "lgs_create: unexpected failure in host setup");
+    }
+}
+
+static int create_impl(const lgs_desc* d, lgs_handle** out) {
     if (!d || !out) return fail(nullptr, LGS_E_INVALID, "lgs_create: NULL argument");
     *out = nullptr;
     if (d->n <= 0) return fail(nullptr, LGS_E_INVALID, "lgs_create: n must be positive");

@@ -465,27 +465,39 @@ extern "C" {
 
 int lgs_lll_reduce(int64_t* rows, int32_t n, int32_t m, double delta, double eta, int32_t precision, int64_t* U,
                    int64_t* stats) {
-    return reduce_entry(rows, n, m, delta, eta, 0, 0, 0, precision, U, stats);
+    try {
+        return reduce_entry(rows, n, m, delta, eta, 0, 0, 0, precision, U, stats);
+    } catch (...) {  // std::bad_alloc from the work arrays: nothing throws across the ABI
+        return LGS_E_NOMEM;
+    }
 }
 
 int lgs_bkz_reduce(int64_t* rows, int32_t n, int32_t m, int32_t block_size, double delta, int32_t max_tours,
                    int32_t prune, int32_t precision, int64_t* U, int64_t* stats) {
     if (block_size < 2) return LGS_E_INVALID;
     if (prune < 0) prune = block_size > 32 ? 1 : 0;
-    return reduce_entry(rows, n, m, delta, 0.501, block_size, max_tours, prune, precision, U, stats);
+    try {
+        return reduce_entry(rows, n, m, delta, 0.501, block_size, max_tours, prune, precision, U, stats);
+    } catch (...) {
+        return LGS_E_NOMEM;
+    }
 }
 
 int lgs_gso_norms(const int64_t* rows, int32_t n, int32_t m, double* norms) {
     if (!rows || !norms || n <= 0 || m < n) return LGS_E_INVALID;
-    Reducer<dd> red(rows, n, m, nullptr, 0.99, 0.501);
-    if (red.status) return red.status;
-    for (int k = 0; k < n; k++) {
-        red.gso_row(k);
-        const double d = to_double(red.r[(size_t)k * n + k]);
-        if (!(d > 0)) return LGS_E_INVALID;
-        norms[k] = std::sqrt(d);
+    try {
+        Reducer<dd> red(rows, n, m, nullptr, 0.99, 0.501);
+        if (red.status) return red.status;
+        for (int k = 0; k < n; k++) {
+            red.gso_row(k);
+            const double d = to_double(red.r[(size_t)k * n + k]);
+            if (!(d > 0)) return LGS_E_INVALID;
+            norms[k] = std::sqrt(d);
+        }
+        return LGS_OK;
+    } catch (...) {
+        return LGS_E_NOMEM;
     }
-    return LGS_OK;
 }
 
 }  // extern "C"
