@@ -63,9 +63,16 @@ class Engine:
             pass
 
     # ------------------------------------------------------------------ Klein, host buffers
-    def klein_sample(self, S, seed, first_id, samplez="fast", want_v=True, want_x=False, want_logq=False):
+    def klein_sample(self, S, seed, first_id, samplez="fast", want_v=True, want_x=False, want_logq=False, out=None):
+        """`out`: a caller-owned C-contiguous float64 [S, n] array for the lattice points (reused between calls it
+        saves the page faults of a fresh array: about 2x at n = 1024)."""
         S = int(S)
-        V = np.empty((S, self.n), dtype=np.float64) if want_v else None
+        if out is not None:
+            if not (isinstance(out, np.ndarray) and out.dtype == np.float64 and out.shape == (S, self.n)
+                    and out.flags.c_contiguous and out.flags.writeable):
+                raise ValueError(f"out must be a writeable C-contiguous float64 array of shape ({S}, {self.n})")
+            want_v = True
+        V = out if out is not None else (np.empty((S, self.n), dtype=np.float64) if want_v else None)
         X = np.empty((S, self.n), dtype=np.int64) if want_x else None
         lq = np.empty(S, dtype=np.float64) if want_logq else None
         check(self._h, self._lib.lgs_klein_sample_host(self._h, S, int(seed) & (2**64 - 1), int(first_id),

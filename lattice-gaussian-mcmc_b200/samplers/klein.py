@@ -88,7 +88,9 @@ class RefinedKleinSampler(DiscreteGaussianSampler):
         return u
 
     # ------------------------------------------------------------------ sampling (klein.py:181-220, 304-337)
-    def _draw(self, num_samples: int, want_v=True, want_x=False, want_logq=False):
+    def _draw(self, num_samples: int, want_v=True, want_x=False, want_logq=False, out=None):
+        if out is not None and self.mode == "replay":
+            raise ValueError("out= is a native-mode option")
         if self.mode == "replay":
             U = self._take_uniforms(num_samples * self._engine.ups)
             V, X, lq, fb = self._engine.klein_replay(U, num_samples, want_v, want_x, want_logq)
@@ -97,7 +99,7 @@ class RefinedKleinSampler(DiscreteGaussianSampler):
                                "the replay stream layout after that point is undefined")
         else:
             V, X, lq = self._engine.klein_sample(num_samples, self.seed, self._next_sample_id, self.samplez, want_v,
-                                                 want_x, want_logq)
+                                                 want_x, want_logq, out=out)
             self._next_sample_id += num_samples
         return V, X, lq
 
@@ -108,7 +110,11 @@ class RefinedKleinSampler(DiscreteGaussianSampler):
         # `batch_size` is accepted for signature parity (klein.py:304); the device batches internally
         return self._draw(int(num_samples))[0]
 
-    def sample(self, num_samples: int = 1) -> np.ndarray:
+    def sample(self, num_samples: int = 1, *, out: Optional[np.ndarray] = None) -> np.ndarray:
+        """klein.py:322-337.  `out` (an addition to the reference signature): a float64 [num_samples, n] array to
+        fill and return instead of a fresh one."""
+        if out is not None:
+            return self._draw(int(num_samples), out=out)[0]
         if num_samples == 1:
             return self.sample_single().reshape(1, -1)
         return self.parallel_sample_batch(num_samples)

@@ -154,3 +154,20 @@ def test_pageable_destinations_take_the_pinned_bounce_ring_and_match_the_device_
     assert Vk.nbytes >= 8 << 20 and Xk.nbytes >= 8 << 20
     np.testing.assert_allclose(Vk, Xk.astype(np.float64) @ B.T, rtol=0, atol=1e-9)
     assert len(np.unique(Xk[:, -1, 0])) > 3
+
+
+def test_sample_into_a_caller_owned_array(lgs):
+    """KleinSampler.sample(num, out=...) fills the caller's array with exactly what a fresh call returns"""
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(72, seed=5)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    a = lgs.KleinSampler(lat, sigma, seed=3)
+    b = lgs.KleinSampler(lat, sigma, seed=3)
+    buf = np.full((5000, 72), np.nan)
+    for _ in range(2):                       # the second round continues the sample ids in both
+        got = a.sample(5000, out=buf)
+        assert got is buf
+        assert np.array_equal(buf, b.sample(5000))
+    for bad in (np.empty((5000, 71)), np.empty((5000, 72), np.float32), np.empty((72, 5000)).T):
+        with pytest.raises(ValueError):
+            a.sample(5000, out=bad)
