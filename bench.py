@@ -29,6 +29,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_RING, Q, SIGMA = 512, 12289, 165.74          # NTRU n = 512, q = 12289; sampler sigma = Falcon-512's
+# config.workload of BOTH arms (the reference arm times the CPU implementation of the same path on this workload)
+WORKLOAD = (f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim, exact NTRUSolve, seed 0), sampler sigma={SIGMA}, "
+            "Klein sampling + IMHK")
 DIM = 2 * N_RING
 KLEIN_FLOP = 3 * DIM * DIM - DIM                # back-substitution n(n-1) + lattice point 2n^2   
 NCU_TRAFFIC_BYTES = 37.72e9                     # dram read 33.74 GB + write 3.98 GB per launch of the chain kernel at
@@ -139,8 +142,8 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "klein_samples_per_s", "value": val, "unit": "samples/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim), sigma={SIGMA}, Klein sampling",
-                       "samples_per_step": S},
+            "config": {"workload": WORKLOAD, "samples_per_step": S,
+                       "sample_of": "the same lattice, sigma and sampler as the GPU arm; a bounded sample per step"},
             "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port",
                              "sample": f"{S} samples per step x {args.steps} steps, {cores} OpenMP threads"},
             "imhk": {"value": imhk_val, "unit": "chain-steps/s", "sample": f"{cores} chains x {steps_imhk} steps"},
@@ -341,8 +344,7 @@ def main():
             "metric": "klein_samples_per_s", "value": klein_rate, "unit": "samples/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_klein / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim, exact NTRUSolve, seed 0), "
-                                   f"sampler sigma={SIGMA}, Klein sampling + IMHK",
+            "config": {"workload": WORKLOAD,
                        "samples_per_gpu_per_step": S, "cond_sigma_range": [float(SIGMA / gs.max()), float(SIGMA / gs.min())],
                        "l2_policy": "each step writes S x n fp64 = %.2f GB of fresh output (> 126 MB L2) and streams "
                                     "its %.2f GB tiled coefficient workspace" % (S * n * 8 / 1e9, S * n * 8.25 / 1e9),
