@@ -30,8 +30,8 @@ sys.path.insert(0, ROOT)
 
 N_RING, Q, SIGMA = 512, 12289, 165.74          # NTRU n = 512, q = 12289; sampler sigma = Falcon-512's
 # config.workload of BOTH arms (the reference arm times the CPU implementation of the same path on this workload)
-WORKLOAD = (f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim, exact NTRUSolve, seed 0), sampler sigma={SIGMA}, "
-            "Klein sampling + IMHK")
+WORKLOAD = (f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim, f,g ~ D_Z,4.05 = BASELINE's key-generation sigma, exact "
+            f"NTRUSolve, seed 0), sampler sigma={SIGMA}, Klein sampling + IMHK")
 DIM = 2 * N_RING
 KLEIN_FLOP = 3 * DIM * DIM - DIM                # back-substitution n(n-1) + lattice point 2n^2   
 NCU_TRAFFIC_BYTES = 37.72e9                     # dram read 33.74 GB + write 3.98 GB per launch of the chain kernel at
