@@ -34,8 +34,8 @@ WORKLOAD = (f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim, f,g ~ D_Z,4.05 = B
             f"NTRUSolve, seed 0), sampler sigma={SIGMA}, Klein sampling + IMHK")
 DIM = 2 * N_RING
 KLEIN_FLOP = 3 * DIM * DIM - DIM                # back-substitution n(n-1) + lattice point 2n^2   
-NCU_TRAFFIC_BYTES = 37.72e9                     # dram read 33.74 GB + write 3.98 GB per launch of the chain kernel at
-                                                # S = 170 496 (profiles/r01c_ncu_full_summary.json)
+NCU_TRAFFIC_BYTES = 37.94e9                     # dram read 33.81 GB + write 4.13 GB per launch of the chain kernel at
+                                                # S = 170 496 (profiles/r01j_ncu_full_summary.json; r01c: 37.72 GB)
 
 
 def imhk_flop(thin):                             # proposal back-substitution + two quadratic forms + kept point / thin
