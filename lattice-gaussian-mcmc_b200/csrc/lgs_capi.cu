@@ -161,7 +161,10 @@ static int create_impl(const lgs_desc* d, lgs_handle** out) {
         double half = rf * s;
         bool truncated = 2.0 * half >= (double)(max_range - 1);
         if (truncated) {
-            kind[i] = 2;
+            // wide truncated windows take closed-form masses instead of an O(window) walk (LGS_TRUNC_CLOSED_FORM=0:
+            // the summed form, development A/B)
+            const char* tc = getenv("LGS_TRUNC_CLOSED_FORM");
+            kind[i] = (!(tc && tc[0] == '0') && s >= 50.0 && max_range >= 16) ? 3 : 2;
             dmax[i] = max_range / 2;
         } else {
             dmax[i] = (int)std::ceil(half) + 1;

@@ -33,7 +33,8 @@ struct DeviceCtx {
     const double* fz_sq;      // exp(-1/(2 sigma_i^2))
     const double* fz_znorm;   // sigma_i*sqrt(2 pi)
     const double* fz_eps1;    // 2*exp(-2 pi^2 sigma_i^2)   (first theta-series correction)
-    const int* fz_kind;       // 0 analytic Z, 1 analytic Z + one cosine term, 2 summed Z (small sigma_i or truncated window)
+    const int* fz_kind;       // 0 analytic Z, 1 analytic Z + one cosine term, 2 summed Z (small sigma_i or truncated window),
+                              // 3 wide truncated window (sigma_i >= 50): closed-form masses (window_mass_em)
     const int* fz_dmax;       // walk bound on each side of round(mean)
 };
 
@@ -225,6 +226,23 @@ struct FastZ {
     int kind, dmax;
 };
 
+// sum_{j=-d}^{d} exp(-a (j + delta)^2) in closed form, for the wide truncated windows (kind 3: sigma_i >= 50, where the
+// reference cuts the table to max_range + 1 entries, klein.py:122-126).  Euler-Maclaurin: the integral (two erf), the
+// end-point mean and the B2 / B4 / B6 derivative terms; g^(k) = (-1)^k a^(k/2) H_k(sqrt(a) s) g falls off as a^(k/2),
+// so at a <= 2e-4 the first omitted term is < 1e-16 of the sum.  gu = g(d), gd = g(-d) are passed in (the caller
+// needs them as walk weights anyway).  d = 0 gives g(0) exactly.
+__device__ __forceinline__ double window_mass_em(double a, double sqrt_a, double delta, double d, double gu, double gd) {
+    const double su = d + delta, sd = d - delta;          // |s| at the two ends; every odd derivative is odd in s
+    const double integ = __ddiv_rn(0.88622692545275801365, sqrt_a) * (erf(sqrt_a * su) + erf(sqrt_a * sd));
+    const double a2 = a * a, a3 = a2 * a;
+    const double su2 = su * su, sd2 = sd * sd;
+    const double t1 = -2.0 * a * (su * gu + sd * gd);                                          // 1st derivative, d vs -d
+    const double t3 = (12.0 * a2 - 8.0 * a3 * su2) * su * gu + (12.0 * a2 - 8.0 * a3 * sd2) * sd * gd;   // 3rd
+    const double t5 = -(((32.0 * a3 * a2 * su2 - 160.0 * a2 * a2) * su2 + 120.0 * a3) * su * gu +
+                        ((32.0 * a3 * a2 * sd2 - 160.0 * a2 * a2) * sd2 + 120.0 * a3) * sd * gd);        // 5th
+    return integ + 0.5 * (gu + gd) + t1 * (1.0 / 12.0) - t3 * (1.0 / 720.0) + t5 * (1.0 / 30240.0);
+}
+
 __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, double u, double* zsum) {
     double c0 = rint(mean);
     double delta = c0 - mean;                     // in [-0.5, 0.5]
@@ -237,6 +255,10 @@ __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, d
         Z = c.znorm;
     } else if (c.kind == 1) {
         Z = c.znorm * (1.0 + c.eps1 * (double)cospif(2.0f * (float)delta));
+    } else if (c.kind == 3) {
+        const double D = (double)c.dmax;
+        Z = window_mass_em(c.inv2s2, sqrt(c.inv2s2), delta, D, exp(-c.inv2s2 * (D + delta) * (D + delta)),
+                           exp(-c.inv2s2 * (D - delta) * (D - delta)));
     } else {
         // summed normaliser over the (possibly truncated) window
         double su = w0, wu = w0, wd = w0, a = ru, b = rd;
@@ -254,6 +276,29 @@ __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, d
     if (target < cum) return x;
     double wu = w0, wd = w0;
     int d = 1;
+    if (c.kind == 3) {
+        // jump: an FP32 estimate of the exit distance from the symmetric integral, the exact mass inside distance
+        // ds - 1 in closed form, then the ordinary walk from ds (a few steps).  The estimate only chooses where the walk
+        // starts: if the mass there already exceeds the target (or the estimate is useless) the walk starts at 1.
+        const double sa = sqrt(c.inv2s2);
+        const float y = (float)(target * sa * 0.56418958354775628695);
+        if (y < 0.99999f) {
+            int ds = (int)floorf(erfinvf(y) / (float)sa - 0.5f) - 1;
+            ds = ds > c.dmax ? c.dmax : ds;
+            if (ds >= 3) {
+                const double e = (double)(ds - 1);
+                const double su = e + delta, sd = e - delta;
+                const double gu = exp(-c.inv2s2 * su * su), gd = exp(-c.inv2s2 * sd * sd);
+                const double base = window_mass_em(c.inv2s2, sa, delta, e, gu, gd);
+                if (base <= target) {
+                    cum = base, wu = gu, wd = gd;
+                    ru = exp(-c.inv2s2 * (2.0 * su + 1.0));
+                    rd = exp(-c.inv2s2 * (2.0 * sd + 1.0));
+                    d = ds;
+                }
+            }
+        }
+    }
     for (; d <= c.dmax; d++) {
         wu *= ru; ru *= c.q;
         cum += wu;
