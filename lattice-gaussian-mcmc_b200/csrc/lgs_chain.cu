@@ -632,13 +632,16 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
 // ---------------------------------------------------------------------------------------------------------
 // panel warpgroup: one thread per sample of the slot's tile
 // ---------------------------------------------------------------------------------------------------------
+template <bool WIDE>
 __device__ __noinline__ double chain_samplez_fast_call(double mean, double inv2s2, double q, double sq, double znorm,
                                                        double eps1, int kind, int dmax, double u, double* zsum) {
     FastZ fz{inv2s2, q, sq, znorm, eps1, kind, dmax};
-    return (double)samplez_fast(mean, fz, u, zsum);
+    return (double)samplez_fast<WIDE>(mean, fz, u, zsum);
 }
 
-template <bool WANT_LZ, bool WANT_D2, bool IMHK>
+// WIDE: the lattice has wide truncated windows (kind 3, closed-form masses); a separate instantiation, because the
+// larger callee costs the panel loop spills (+1 % on the NTRU workload, which has none)
+template <bool WANT_LZ, bool WANT_D2, bool IMHK, bool WIDE>
 __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, const int slot) {
     const int sl = (threadIdx.x - kPanelBase) & 127;
     const int lane = threadIdx.x & 31;
@@ -807,7 +810,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                                 if (WANT_LZ) lza += logz;
                             } else {
                                 double zs;
-                                x = chain_samplez_fast_call(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, kind, ci.y, u,
+                                x = chain_samplez_fast_call<WIDE>(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, kind, ci.y, u,
                                                             &zs);
                                 if (WANT_LZ) lza += log(zs);
                             }
@@ -944,7 +947,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     }
 }
 
-template <bool WANT_LZ, bool WANT_D2, bool IMHK>
+template <bool WANT_LZ, bool WANT_D2, bool IMHK, bool WIDE>
 __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_constant__ ChainArgs P) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ChainSmem& sm = *reinterpret_cast<ChainSmem*>(smem_raw);
@@ -972,7 +975,7 @@ __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_c
         if (tid == kProdBase) producer_role(sm, P);
     } else {
         reg_dec<kRegsPanel>();
-        panel_role<WANT_LZ, WANT_D2, IMHK>(sm, P, (tid - kPanelBase) >> 7);
+        panel_role<WANT_LZ, WANT_D2, IMHK, WIDE>(sm, P, (tid - kPanelBase) >> 7);
     }
 }
 
@@ -1110,7 +1113,10 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     if ((e = up((void**)&cc.invr, invr.data(), sizeof(double) * invr.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.subs, subs.data(), sizeof(SubPack) * subs.size())) != cudaSuccess) return e;
 #define LGS_CHAIN_ATTR(LZ, D2, MH)                                                                                 \
-    if ((e = cudaFuncSetAttribute(klein_chain_kernel<LZ, D2, MH>, cudaFuncAttributeMaxDynamicSharedMemorySize,    \
+    if ((e = cudaFuncSetAttribute(klein_chain_kernel<LZ, D2, MH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                  (int)sizeof(ChainSmem))) != cudaSuccess)                                        \
+        return e;                                                                                                  \
+    if ((e = cudaFuncSetAttribute(klein_chain_kernel<LZ, D2, MH, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                   (int)sizeof(ChainSmem))) != cudaSuccess)                                        \
         return e;
     LGS_CHAIN_ATTR(false, false, false)
@@ -1128,6 +1134,8 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
         const int rounds = env ? atoi(env) : by_n;
         cc.batch = (int64_t)(bc.sm_count > 0 ? bc.sm_count : 148) * kTile * kSlots * (rounds > 0 ? rounds : 3);
     }
+    cc.wide = false;
+    for (int i = 0; i < bc.n; i++) cc.wide = cc.wide || hc.kind[i] == 3;
     cc.ready = true;
     return cudaSuccess;
 }
@@ -1165,10 +1173,16 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     a.stats = want_stats ? stats_dev : nullptr;
     {
         ProfScope ps(bc.prof, LGS_PROF_CHAIN, st);
-        if (imhk && want_lz) klein_chain_kernel<true, false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
-        else if (imhk) klein_chain_kernel<false, false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
-        else if (want_d2) klein_chain_kernel<false, true, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
-        else klein_chain_kernel<false, false, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+#define LGS_CHAIN_GO(LZ, D2, MH)                                                                  \
+    do {                                                                                          \
+        if (cc.wide) klein_chain_kernel<LZ, D2, MH, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);   \
+        else klein_chain_kernel<LZ, D2, MH, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);          \
+    } while (0)
+        if (imhk && want_lz) LGS_CHAIN_GO(true, false, true);
+        else if (imhk) LGS_CHAIN_GO(false, false, true);
+        else if (want_d2) LGS_CHAIN_GO(false, true, false);
+        else LGS_CHAIN_GO(false, false, false);
+#undef LGS_CHAIN_GO
     }
     if (want_stats) {  // development only: synchronous read-back, mean over CTAs
         std::vector<unsigned long long> hs((size_t)grid * 12);

@@ -243,6 +243,9 @@ __device__ __forceinline__ double window_mass_em(double a, double sqrt_a, double
     return integ + 0.5 * (gu + gd) + t1 * (1.0 / 12.0) - t3 * (1.0 / 720.0) + t5 * (1.0 / 30240.0);
 }
 
+// WIDE = false compiles the closed-form branch out: the chain kernel instantiates it for lattices without kind-3
+// coordinates, whose register allocation (and speed) must not pay for code they never run.
+template <bool WIDE = true>
 __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, double u, double* zsum) {
     double c0 = rint(mean);
     double delta = c0 - mean;                     // in [-0.5, 0.5]
@@ -255,7 +258,7 @@ __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, d
         Z = c.znorm;
     } else if (c.kind == 1) {
         Z = c.znorm * (1.0 + c.eps1 * (double)cospif(2.0f * (float)delta));
-    } else if (c.kind == 3) {
+    } else if (WIDE && c.kind == 3) {
         const double D = (double)c.dmax;
         Z = window_mass_em(c.inv2s2, sqrt(c.inv2s2), delta, D, exp(-c.inv2s2 * (D + delta) * (D + delta)),
                            exp(-c.inv2s2 * (D - delta) * (D - delta)));
@@ -276,7 +279,7 @@ __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, d
     if (target < cum) return x;
     double wu = w0, wd = w0;
     int d = 1;
-    if (c.kind == 3) {
+    if (WIDE && c.kind == 3) {
         // jump: an FP32 estimate of the exit distance from the symmetric integral, the exact mass inside distance
         // ds - 1 in closed form, then the ordinary walk from ds (a few steps).  The estimate only chooses where the walk
         // starts: if the mass there already exceeds the target (or the estimate is useless) the walk starts at 1.
