@@ -49,7 +49,9 @@ enum {
 /* 1-D sampler used for each coordinate */
 enum {
     LGS_SAMPLEZ_TABLE = 0, /* the reference's normalised table + inverse CDF (klein.py:101-179), same arithmetic order */
-    LGS_SAMPLEZ_FAST = 1   /* same distribution, recurrence-built weights walked outward from round(mean) */
+    LGS_SAMPLEZ_FAST = 1   /* same distribution, recurrence-built weights walked outward from round(mean); wide truncated
+                            * windows (sigma_i >= 50: the reference's max_range + 1 entry tables, klein.py:122-126) use
+                            * closed-form window masses (LGS_TRUNC_CLOSED_FORM=0 at lgs_create: the summed form, A/B) */
 };
 
 /* importance weight used by the IMHK accept step */
