@@ -118,10 +118,19 @@ LGS_API int lgs_klein_sample(lgs_handle *h, int64_t S, uint64_t seed, uint64_t f
  * U_dev[s*ups .. (s+1)*ups), ups = lgs_uniforms_per_sample(), in coordinate order i = n-1 .. 0 -- i.e.
  * np.random.RandomState(seed).random_sample(S*ups) reproduces np.random.seed(seed); sampler.sample(S).
  * Always uses LGS_SAMPLEZ_TABLE.  fallback_count_dev (int32[1], may be NULL) counts draws that took the
- * reference's no-uniform fallback.
+ * reference's no-uniform fallback.  Runs on the kernel lgs_replay_path() names.
  */
 LGS_API int lgs_klein_replay(lgs_handle *h, int64_t S, const double *U_dev, double *V_dev, int64_t *X_dev,
                      double *logq_dev, int32_t *fallback_count_dev, void *stream);
+
+/*
+ * Which kernel the replay entry points of this handle run on: LGS_PATH_ORDERED (one thread per sample, the reference's
+ * summation order: klein_ordered_kernel / imhk_ordered_kernel) or LGS_PATH_BLOCKED (the throughput kernel itself --
+ * klein_chain_kernel's REPLAY instantiation: the conditional means of klein.py:189-195 come from the FP64 DMMA
+ * contraction, the draw is the reference's table SampleZ on the recorded uniform).  A handle created with
+ * lgs_desc.path = LGS_PATH_BLOCKED replays on the chain kernel whenever that kernel serves the lattice.
+ */
+LGS_API int lgs_replay_path(const lgs_handle *h);
 
 /* Host-buffer forms (pageable or pinned host memory; copies inside; synchronous).
  *

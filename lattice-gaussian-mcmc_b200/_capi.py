@@ -56,6 +56,7 @@ PROTOTYPES = {
     "lgs_preferred_batch": (ctypes.c_int64, [vp]),
     "lgs_klein_sample": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, vp, vp, vp, vp]),
     "lgs_klein_replay": (ctypes.c_int, [vp, ctypes.c_int64, vp, vp, vp, vp, vp, vp]),
+    "lgs_replay_path": (ctypes.c_int, [vp]),
     "lgs_host_transport": (ctypes.c_int, [vp]),
     "lgs_host_widen_i16": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int32]),
     "lgs_klein_sample_host": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, vp, vp, vp]),

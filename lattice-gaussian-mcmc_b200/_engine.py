@@ -51,6 +51,11 @@ class Engine:
         self.preferred_batch = int(self._lib.lgs_preferred_batch(self._h))
         self.chains = 0
 
+    @property
+    def replay_on_chain(self) -> bool:
+        """True when the replay entry points of this handle run on the throughput (chain) kernel (lgs_replay_path)"""
+        return int(self._lib.lgs_replay_path(self._h)) == PATH["blocked"]
+
     def close(self):
         if getattr(self, "_h", None) is not None:
             self._lib.lgs_destroy(self._h)

@@ -56,7 +56,7 @@ int ensure_stage(lgs_handle* h, size_t nbytes) {
 
 void free_chains(ChainSet& cs) {
     cudaFree(cs.Xbuf); cudaFree(cs.Vbuf); cudaFree(cs.logw); cudaFree(cs.cur); cudaFree(cs.init);
-    cudaFree(cs.counts); cudaFree(cs.step_no); cudaFree(cs.Xcur); cudaFree(cs.flags);
+    cudaFree(cs.counts); cudaFree(cs.step_no); cudaFree(cs.upos); cudaFree(cs.Xcur); cudaFree(cs.flags);
     cs = ChainSet{};
 }
 
@@ -320,16 +320,39 @@ int lgs_klein_sample(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_sam
     return LGS_OK;
 }
 
+// replay calls of a handle created with LGS_PATH_BLOCKED run on the chain kernel (when it serves this lattice)
+static bool replay_on_chain(const lgs_handle* h) {
+    return h->path == LGS_PATH_BLOCKED && h->blocked.ready && h->blocked.use_chain && h->blocked.chain.ready;
+}
+
+int lgs_replay_path(const lgs_handle* h) {
+    if (!h) return LGS_E_INVALID;
+    return replay_on_chain(h) ? LGS_PATH_BLOCKED : LGS_PATH_ORDERED;
+}
+
+// one replay launch sequence; the fallback counter is accumulated into, not reset
+static int klein_replay_impl(lgs_handle* h, int64_t S, const double* U_dev, double* V_dev, int64_t* X_dev,
+                             double* logq_dev, int32_t* fallback_count_dev, cudaStream_t stream) {
+    if (replay_on_chain(h)) {
+        // LGS_PATH_BLOCKED: the recorded stream goes through the throughput kernel itself (klein_chain_kernel, REPLAY
+        // instantiation: DMMA-contracted conditional means + the reference's table SampleZ)
+        const ChainReplay rp{U_dev, h->ctx.ups, fallback_count_dev, nullptr, nullptr};
+        LGS_CUDA(h, launch_klein_chain(h->blocked, S, 0, 0, V_dev, X_dev, logq_dev, stream, &rp));
+        return LGS_OK;
+    }
+    RngSpec rng{U_dev, h->ctx.ups, 0, 0};
+    LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, S, rng, LGS_SAMPLEZ_TABLE, V_dev, X_dev, logq_dev,
+                                     fallback_count_dev, stream));
+    return LGS_OK;
+}
+
 int lgs_klein_replay(lgs_handle* h, int64_t S, const double* U_dev, double* V_dev, int64_t* X_dev, double* logq_dev,
                      int32_t* fallback_count_dev, void* stream) {
     if (!h) return LGS_E_INVALID;
     if (S < 0 || (S > 0 && !U_dev)) return fail(h, LGS_E_INVALID, "lgs_klein_replay: bad arguments");
     LGS_CUDA(h, cudaSetDevice(h->device));
     if (fallback_count_dev) LGS_CUDA(h, cudaMemsetAsync(fallback_count_dev, 0, sizeof(int32_t), (cudaStream_t)stream));
-    RngSpec rng{U_dev, h->ctx.ups, 0, 0};
-    LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, S, rng, LGS_SAMPLEZ_TABLE, V_dev, X_dev, logq_dev,
-                                     fallback_count_dev, (cudaStream_t)stream));
-    return LGS_OK;
+    return klein_replay_impl(h, S, U_dev, V_dev, X_dev, logq_dev, fallback_count_dev, (cudaStream_t)stream);
 }
 
 // Host-buffer Klein call for an integer basis, lattice points only: chunk k is sampled and packed to int16 on the
@@ -783,10 +806,9 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
             if (U_host) {
                 LGS_CUDA(h, cudaMemcpyAsync(dU, U_host + (size_t)s0 * ups, sizeof(double) * cnt * ups,
                                             cudaMemcpyHostToDevice, cs));
-                RngSpec rng{dU, ups, 0, 0};
                 // the fallback counter accumulates over chunks (no per-chunk reset)
-                LGS_CUDA(h, launch_klein_ordered(h->ctx, h->scratch, cnt, rng, LGS_SAMPLEZ_TABLE, dV, dX, dq,
-                                                 fb_host ? dfb : nullptr, cs));
+                rc = klein_replay_impl(h, cnt, dU, dV, dX, dq, fb_host ? dfb : nullptr, cs);
+                if (rc) return rc;
             } else {
                 rc = lgs_klein_sample(h, cnt, seed, first_id + (uint64_t)s0, samplez, dV, dX, dq, cs);
                 if (rc) return rc;
@@ -880,6 +902,7 @@ int lgs_imhk_reset(lgs_handle* h, int64_t chains, uint64_t seed, uint64_t first_
         LGS_CUDA(h, cudaMalloc(&cs.init, sizeof(int32_t) * chains));
         LGS_CUDA(h, cudaMalloc(&cs.counts, sizeof(int64_t) * 2 * chains));
         LGS_CUDA(h, cudaMalloc(&cs.step_no, sizeof(int64_t) * chains));
+        LGS_CUDA(h, cudaMalloc(&cs.upos, sizeof(int64_t) * chains));
         cs.chains = chains;
     }
     cs.seed = seed;
@@ -892,6 +915,7 @@ int lgs_imhk_reset(lgs_handle* h, int64_t chains, uint64_t seed, uint64_t first_
     LGS_CUDA(h, cudaMemset(cs.init, 0, sizeof(int32_t) * chains));
     LGS_CUDA(h, cudaMemset(cs.counts, 0, sizeof(int64_t) * 2 * chains));
     LGS_CUDA(h, cudaMemset(cs.step_no, 0, sizeof(int64_t) * chains));
+    LGS_CUDA(h, cudaMemset(cs.upos, 0, sizeof(int64_t) * chains));
     return LGS_OK;
 }
 
@@ -948,9 +972,16 @@ int lgs_imhk_replay(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, 
     if (rc) return rc;
     if (!U_dev) return fail(h, LGS_E_INVALID, "lgs_imhk_replay: NULL uniform stream");
     LGS_CUDA(h, cudaSetDevice(h->device));
+    if (fallback_count_dev) LGS_CUDA(h, cudaMemsetAsync(fallback_count_dev, 0, sizeof(int32_t), (cudaStream_t)stream));
+    if (replay_on_chain(h) && h->chains.state_path != 1) {
+        h->chains.state_path = 2;
+        const ChainReplay rp{U_dev, stride, fallback_count_dev, accept_dev, logw_dev};
+        LGS_CUDA(h, launch_imhk_chain(h->blocked, h->chains, burn_in, keep, thin, weight_mode, V_dev, X_dev,
+                                      (cudaStream_t)stream, &rp));
+        return LGS_OK;
+    }
     rc = ensure_ordered_chains(h);
     if (rc) return rc;
-    if (fallback_count_dev) LGS_CUDA(h, cudaMemsetAsync(fallback_count_dev, 0, sizeof(int32_t), (cudaStream_t)stream));
     RngSpec rng{U_dev, stride, 0, 0};
     LGS_CUDA(h, launch_imhk_ordered(h->ctx, h->chains, burn_in, keep, thin, rng, LGS_SAMPLEZ_TABLE, weight_mode, V_dev,
                                     X_dev, accept_dev, logw_dev, fallback_count_dev, (cudaStream_t)stream));

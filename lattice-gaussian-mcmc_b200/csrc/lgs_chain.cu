@@ -225,6 +225,23 @@ struct ChainArgs {
     uint8_t* loc;           // [cap] where a chain's current state lives: 0 = Xcur, 1 / 2 = Xbuf[0] / Xbuf[1]
     double* lw_cur;         // [cap] current log importance weight
     long long* counts;      // [cap][2] accepted, total
+    // Replay (the REPLAY instantiations; lgs_klein_replay / lgs_imhk_replay on LGS_PATH_BLOCKED): the panel threads take
+    // their uniforms from the reference's recorded stream instead of Philox -- unit s reads U[s * u_stride + position],
+    // one uniform per drawn coordinate in the order i = n-1 .. 0 (klein.py:181-220), then one for the accept test of a
+    // Metropolis-Hastings step (imhk.py:167) -- and draw with the reference's table arithmetic (samplez_table:
+    // klein.py:101-179 + numpy choice), so the integers are the reference's except where the DMMA summation order of
+    // the conditional mean moves a CDF comparison (counted by the tests, ~1e-15 per draw).
+    const double* U;
+    int64_t u_stride;
+    long long* upos;        // IMHK: [cap] position of every chain inside its stream, carried over the launches of one
+                            // call; Klein: nullptr (every sample starts at 0)
+    const double* sig;      // [npad] sigma_i = sigma / |R_ii|
+    int precision, max_range;
+    int32_t* fallback;      // counts draws that took the reference's no-uniform fallback (klein.py:176-179), or nullptr
+    uint8_t* accept_out;    // IMHK: [S][call_steps] accept bit of every step of the call, or nullptr
+    double* logw_out;       // IMHK: [S][call_steps + 1] log weight at entry and of every proposal, or nullptr
+    int64_t call_steps;     // Metropolis-Hastings steps of the whole call (row length of accept_out)
+    int64_t step_off;       // steps of the call performed by earlier launches
 };
 
 // Development cycle counters (read with LGS_CHAIN_STATS=1 in the environment) exist only in a
@@ -639,9 +656,27 @@ __device__ __noinline__ double chain_samplez_fast_call(double mean, double inv2s
     return (double)samplez_fast<WIDE>(mean, fz, u, zsum);
 }
 
+// Replay draw: the reference's table SampleZ (klein.py:101-179) on the recorded uniform; *lse (exact weights) is the
+// table's log-sum-exp, the log of the window mass (imhk: Wang-Ling weight).  Returns false when the reference's
+// no-uniform fallback was taken (klein.py:176-179): the uniform is then not consumed.
+template <bool WANT_LZ>
+__device__ __noinline__ bool chain_samplez_table_call(double mean, double sig, int precision, int max_range, double u,
+                                                      double* x, double* lse) {
+    long long xi;
+    const bool ok = samplez_table(mean, sig, precision, max_range, u, &xi);
+    *x = (double)xi;
+    if (WANT_LZ) {
+        const TableWindow tw = table_window(mean, sig, precision, max_range);
+        const LogpGen lpg{(double)tw.lower, mean, sig};
+        *lse = table_lse(lpg, tw.len);
+    }
+    return ok;
+}
+
 // WIDE: the lattice has wide truncated windows (kind 3, closed-form masses); a separate instantiation, because the
 // larger callee costs the panel loop spills (+1 % on the NTRU workload, which has none)
-template <bool WANT_LZ, bool WANT_D2, bool IMHK, bool WIDE>
+// REPLAY: uniforms from the recorded stream + the reference's table SampleZ (see ChainArgs::U)
+template <bool WANT_LZ, bool WANT_D2, bool IMHK, bool WIDE, bool REPLAY>
 __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, const int slot) {
     const int sl = (threadIdx.x - kPanelBase) & 127;
     const int lane = threadIdx.x & 31;
@@ -682,10 +717,15 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
         // IMHK chain state of this thread's chain (imhk.py:126-177)
         double lw = 0.0;
         int loc = 0, acc_n = 0, tot_n = 0;
+        long long upos = 0;   // replay: position inside this unit's recorded stream
         if (IMHK && s < P.S) {
             lw = P.lw_cur[s];
             loc = P.loc[s];
+            if (REPLAY && P.upos) upos = P.upos[s];
+            // the state a call starts from (launches of initialised chains): entry 0 of the log-weight row
+            if (REPLAY && P.logw_out && P.step_off == 0 && !P.first_is_init) P.logw_out[s * (P.call_steps + 1)] = lw;
         }
+        const double* __restrict__ urow = REPLAY ? P.U + (size_t)(s < P.S ? s : 0) * P.u_stride : nullptr;
         // column copy of one chain's coefficients between tiled matrices (predicated per lane, coalesced per row)
         auto copy_column = [&](const double* __restrict__ src, double* __restrict__ dst) {
             const size_t o = (size_t)tile * P.npad * kRowLd + sl;
@@ -777,6 +817,14 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     const double rmean = rint(mean);
                     if (ci.w) {
                         x = rmean;
+                    } else if constexpr (REPLAY) {
+                        const double u = s < P.S ? __ldg(urow + upos) : 0.5;
+                        double lse = 0.0;
+                        const bool ok = chain_samplez_table_call<WANT_LZ>(mean, __ldg(P.sig + lo + base + j), P.precision,
+                                                                          P.max_range, u, &x, &lse);
+                        if (ok) upos++;
+                        else if (P.fallback && s < P.S) atomicAdd(P.fallback, 1);
+                        if (WANT_LZ) lza += lse;
                     } else {
                         if ((ci.z >> 1) != wpair) {
                             wpair = ci.z >> 1;
@@ -893,9 +941,20 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                 if (P.first_is_init && step == 0) {
                     lw = lw_prop;
                     loc = buf;
+                    if (REPLAY && P.logw_out && s < P.S) P.logw_out[s * (P.call_steps + 1)] = lw;
                 } else {
                     bool acc = true;
-                    if (P.exact) {
+                    if (REPLAY) {  // imhk.py:156-174 on the recorded uniform (always drawn, imhk.py:167)
+                        const double ua = s < P.S ? __ldg(urow + upos) : 0.0;
+                        upos++;
+                        const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
+                        acc = ua < ratio;
+                        const int64_t k = P.step_off + step - (P.first_is_init ? 1 : 0);
+                        if (s < P.S) {
+                            if (P.accept_out) P.accept_out[s * P.call_steps + k] = acc ? 1 : 0;
+                            if (P.logw_out) P.logw_out[s * (P.call_steps + 1) + k + 1] = lw_prop;
+                        }
+                    } else if (P.exact) {
                         const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
                         acc = philox_uniform(gen, id, kAcceptDraw, tagv) < ratio;
                     }
@@ -932,6 +991,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
         if (IMHK && s < P.S) {
             P.lw_cur[s] = lw;
             P.loc[s] = (uint8_t)loc;
+            if (REPLAY && P.upos) P.upos[s] = upos;
             if (tot_n) {
                 P.counts[2 * s] += acc_n;
                 P.counts[2 * s + 1] += tot_n;
@@ -947,7 +1007,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     }
 }
 
-template <bool WANT_LZ, bool WANT_D2, bool IMHK, bool WIDE>
+template <bool WANT_LZ, bool WANT_D2, bool IMHK, bool WIDE, bool REPLAY = false>
 __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_constant__ ChainArgs P) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ChainSmem& sm = *reinterpret_cast<ChainSmem*>(smem_raw);
@@ -975,7 +1035,7 @@ __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_c
         if (tid == kProdBase) producer_role(sm, P);
     } else {
         reg_dec<kRegsPanel>();
-        panel_role<WANT_LZ, WANT_D2, IMHK, WIDE>(sm, P, (tid - kPanelBase) >> 7);
+        panel_role<WANT_LZ, WANT_D2, IMHK, WIDE, REPLAY>(sm, P, (tid - kPanelBase) >> 7);
     }
 }
 
@@ -1017,6 +1077,7 @@ void chain_free(BlockedCtx& bc) {
     cudaFree(cc.Bpk);
     cudaFree(cc.tp);
     cudaFree(cc.invr);
+    cudaFree(cc.sig);
     cudaFree(cc.subs);
     for (auto& w : cc.work) {
         cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
@@ -1111,6 +1172,13 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     if ((e = up((void**)&cc.Bpk, Bpk.data(), sizeof(double) * Bpk.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.tp, tp.data(), sizeof(double) * tp.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.invr, invr.data(), sizeof(double) * invr.size())) != cudaSuccess) return e;
+    {
+        std::vector<double> sigp(npad, 1.0);
+        for (int i = 0; i < n; i++) sigp[i] = hc.sig[i];
+        if ((e = up((void**)&cc.sig, sigp.data(), sizeof(double) * sigp.size())) != cudaSuccess) return e;
+    }
+    cc.precision = d.precision > 0 ? d.precision : 10;
+    cc.max_range = d.max_range > 0 ? d.max_range : 1000;
     if ((e = up((void**)&cc.subs, subs.data(), sizeof(SubPack) * subs.size())) != cudaSuccess) return e;
 #define LGS_CHAIN_ATTR(LZ, D2, MH)                                                                                 \
     if ((e = cudaFuncSetAttribute(klein_chain_kernel<LZ, D2, MH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
@@ -1124,6 +1192,14 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     LGS_CHAIN_ATTR(false, false, true)
     LGS_CHAIN_ATTR(true, false, true)
 #undef LGS_CHAIN_ATTR
+#define LGS_CHAIN_ATTR_REPLAY(LZ, D2, MH)                                                                            \
+    if ((e = cudaFuncSetAttribute(klein_chain_kernel<LZ, D2, MH, false, true>,                                       \
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ChainSmem))) != cudaSuccess) \
+        return e;
+    LGS_CHAIN_ATTR_REPLAY(false, true, false)
+    LGS_CHAIN_ATTR_REPLAY(false, false, true)
+    LGS_CHAIN_ATTR_REPLAY(true, false, true)
+#undef LGS_CHAIN_ATTR_REPLAY
     {
         // a full batch gives every SM the same whole number of rounds of its kSlots tiles
         // ... and more rounds per launch for small dimensions, where a tile is short and the ramps at both ends of a
@@ -1178,7 +1254,12 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
         if (cc.wide) klein_chain_kernel<LZ, D2, MH, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);   \
         else klein_chain_kernel<LZ, D2, MH, false><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);          \
     } while (0)
-        if (imhk && want_lz) LGS_CHAIN_GO(true, false, true);
+        if (a.U) {  // replay instantiations (the table sampler covers every kind of window: no WIDE split)
+            a.sig = cc.sig; a.precision = cc.precision; a.max_range = cc.max_range;
+            if (imhk && want_lz) klein_chain_kernel<true, false, true, false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+            else if (imhk) klein_chain_kernel<false, false, true, false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+            else klein_chain_kernel<false, true, false, false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
+        } else if (imhk && want_lz) LGS_CHAIN_GO(true, false, true);
         else if (imhk) LGS_CHAIN_GO(false, false, true);
         else if (want_d2) LGS_CHAIN_GO(false, true, false);
         else LGS_CHAIN_GO(false, false, false);
@@ -1204,14 +1285,19 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
 // one batch of S <= w.cap samples: coefficients into w.X (tiled), accumulators into w.lp / d2, lattice points into V
 // (may be nullptr)
 static cudaError_t chain_batch(BlockedCtx& bc, BlockedWork& w, int64_t S, uint64_t seed, uint64_t first_id,
-                               bool want_d2, double* V, int64_t ldv, cudaStream_t st) {
+                               bool want_d2, double* V, int64_t ldv, const ChainReplay* rp, int64_t s0, cudaStream_t st) {
     ChainArgs a{};
     a.Xbuf[0] = a.Xbuf[1] = w.X;
     a.lp = w.lp; a.d2 = w.d2; a.lz = w.lz;
     a.V = V; a.ldv = ldv; a.S = S;
     a.seed = seed; a.first_id = first_id; a.tag = 0u;
     a.nsteps = 1;
-    return chain_launch(bc, a, false, false, want_d2, st);
+    if (rp) {
+        a.U = rp->U + (size_t)s0 * rp->stride;
+        a.u_stride = rp->stride;
+        a.fallback = rp->fallback;
+    }
+    return chain_launch(bc, a, false, false, want_d2 || rp != nullptr, st);
 }
 
 // one batch (S <= chain.batch) with the packed zero-copy output described at ChainArgs::V16
@@ -1238,7 +1324,7 @@ cudaError_t launch_klein_chain_zc(BlockedCtx& bc, int64_t S, uint64_t seed, uint
 }
 
 cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
-                               double* logq, cudaStream_t st) {
+                               double* logq, cudaStream_t st, const ChainReplay* rp) {
     if (S <= 0) return cudaSuccess;
     ChainCtx& cc = bc.chain;
     cudaError_t e;
@@ -1249,7 +1335,7 @@ cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_
     for (int64_t s0 = 0; s0 < S; s0 += w.cap) {
         const int64_t cnt = (S - s0) < w.cap ? (S - s0) : w.cap;
         if ((e = chain_batch(bc, w, cnt, seed, first_id + (uint64_t)s0, logq != nullptr, V ? V + (size_t)s0 * n : nullptr, n,
-                             st)) != cudaSuccess) return e;
+                             rp, s0, st)) != cudaSuccess) return e;
         if (X) {
             ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
             dim3 grid((unsigned)((cnt + 31) / 32), (unsigned)((n + 31) / 32));
@@ -1312,9 +1398,14 @@ static void chain_imhk_args(BlockedCtx& bc, ChainSet& cs, ChainArgs& a, int weig
 }
 
 cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
-                              double* V, int64_t* X, cudaStream_t st) {
+                              double* V, int64_t* X, cudaStream_t st, const ChainReplay* rp) {
     cudaError_t e;
     if ((e = chain_ensure_chains(bc, cs)) != cudaSuccess) return e;
+    int64_t call_done = 0;   // replay: steps of this call performed by earlier launches
+    if (rp) {  // stream positions are per call: chain k reads U[k * stride ...) from its start
+        if (!cs.upos) return cudaErrorInvalidValue;
+        if ((e = cudaMemsetAsync(cs.upos, 0, sizeof(int64_t) * (size_t)cs.chains, st)) != cudaSuccess) return e;
+    }
     const bool exact = weight_mode == LGS_WEIGHT_EXACT;
     const int64_t C = cs.chains;
     const int n = bc.n;
@@ -1333,9 +1424,17 @@ cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int
             a.nsteps = (int)now;
             a.flush = (flush && last) ? 1 : 0;
             if (a.flush && V) { a.V = V + (size_t)kidx * n; a.ldv = keep * (int64_t)n; }
+            if (rp) {
+                a.U = rp->U; a.u_stride = rp->stride; a.fallback = rp->fallback;
+                a.upos = reinterpret_cast<long long*>(cs.upos);
+                a.accept_out = rp->accept; a.logw_out = rp->logw;
+                a.call_steps = burn_in + keep * thin;
+                a.step_off = call_done;
+            }
             cudaError_t er = chain_launch(bc, a, true, exact, false, st);
             if (er != cudaSuccess) return er;
             const int64_t done = now - (init ? 1 : 0);
+            call_done += done;
             cs.bl_steps += done;
             cs.bl_init = true;
             cnt -= done;

@@ -125,6 +125,8 @@ struct ChainCtx {
     double* Bpk = nullptr;        // same for the basis
     double* tp = nullptr;         // [npad]
     double* invr = nullptr;       // [npad] 1 / R_ii
+    double* sig = nullptr;        // [npad] sigma_i (the replay instantiations' table sampler takes sigma_i itself)
+    int precision = 10, max_range = 1000;
     SubPack* subs = nullptr;      // [npad/8]
     BlockedWork work[3];          // tiled: X = [cap/128][npad][132]; [0] Klein, [1]/[2] IMHK proposals
     int64_t batch = 0;            // samples per full batch: sm_count x 128 x 9
@@ -253,12 +255,21 @@ cudaError_t launch_chain_diagnostics(const double* V, int64_t chains, int64_t ke
 cudaError_t launch_gelman_rubin_sums(const double* stats, int64_t chains, int n_dims, double* sums, cudaStream_t st);
 
 // lgs_chain.cu  (persistent warp-specialised kernel)
+// Replay through the chain kernel: the recorded uniform stream (device), `stride` doubles per sample / chain, and the
+// optional per-step outputs of lgs_imhk_replay.  nullptr = native Philox.
+struct ChainReplay {
+    const double* U;
+    int64_t stride;
+    int32_t* fallback;   // or nullptr
+    uint8_t* accept;     // IMHK: [chains][steps] or nullptr
+    double* logw;        // IMHK: [chains][steps + 1] or nullptr
+};
 cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc);
 void chain_free(BlockedCtx& bc);
 cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_t first_id, double* V, int64_t* X,
-                               double* logq, cudaStream_t st);
+                               double* logq, cudaStream_t st, const ChainReplay* rp = nullptr);
 cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
-                              double* V, int64_t* X, cudaStream_t st);
+                              double* V, int64_t* X, cudaStream_t st, const ChainReplay* rp = nullptr);
 cudaError_t launch_imhk_chain_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
                                         double* logw, cudaStream_t st);
 

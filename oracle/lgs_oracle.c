@@ -335,6 +335,100 @@ static double log_target(const ctx_t *cx, const double *v) {
 }
 
 /*
+ * Conditional-law check of sampler OUTPUT (no uniforms involved; checker for native-RNG samples).
+ * For every sample x (integer coefficients, as returned by the sampler under test) and every coordinate i the
+ * reference's conditional mean m_i is recomputed in the reference's order (klein.py:189-195) and the reference's own
+ * table for (m_i, sigma_i) is built (klein.py:101-141, 160-170: probs = exp(log_p); probs /= probs.sum()).  Under the
+ * reference's law the offset x_i - round(m_i) given m_i is distributed by that table, whatever the other coordinates
+ * did.  Per coordinate i, per bin f of frac(m_i) = m_i - floor(m_i) (FB equal bins) and per clipped offset
+ * k in [-K, K] (|offset| >= K pooled into the end bins) this accumulates
+ *     obs[i][f][k + K]  += 1
+ *     expc[i][f][k + K] += table probability of the offsets that clip to k
+ * so that the caller can form sum (obs - expc)^2 / expc per coordinate (a sum of independent, non-identically
+ * distributed multinomial draws: Var(obs) <= expc, i.e. the chi-square reference distribution is conservative).
+ * Coordinates with sigma_i < 1e-10 (deterministic, klein.py:201-204) are skipped.  `width` (int32[n] or NULL = all 1)
+ * coarsens the offsets of coordinate i into bins of width[i] integers (offset -> nearest multiple) before the clip, for
+ * the wide truncated windows (sigma_i >= 50: offsets spread over +-500).
+ */
+static int64_t bin_offset(int64_t off, int64_t w, int K) {
+    int64_t k = off >= 0 ? (off + w / 2) / w : -((-off + w / 2) / w);
+    if (k > K) k = K;
+    if (k < -K) k = -K;
+    return k;
+}
+
+int lgs_oracle_conditional_counts(int n, const double *R, const double *B, const double *t, const double *center,
+                                  double sigma, int precision, int64_t S, const int64_t *X, int K, int FB,
+                                  const int32_t *width, int64_t *obs, double *expc, int threads) {
+    ctx_t cx = {n, R, B, t, center, sigma, precision};
+    const int W = 2 * K + 1;
+    const size_t cells = (size_t)n * FB * W;
+    memset(obs, 0, sizeof(int64_t) * cells);
+    for (size_t c = 0; c < cells; c++) expc[c] = 0.0;
+    int err = 0;
+#ifdef _OPENMP
+    if (threads > 0) omp_set_num_threads(threads);
+#pragma omp parallel
+#endif
+    {
+        table_t *tb = (table_t *)malloc(sizeof(table_t));
+        int64_t *lo = (int64_t *)calloc(cells, sizeof(int64_t));
+        double *le = (double *)calloc(cells, sizeof(double));
+        if (!tb || !lo || !le) {
+#ifdef _OPENMP
+#pragma omp atomic write
+#endif
+            err = 1;
+        } else {
+#ifdef _OPENMP
+#pragma omp for schedule(dynamic, 16)
+#endif
+            for (int64_t s = 0; s < S; s++) {
+                const int64_t *x = X + (size_t)s * n;
+                for (int i = n - 1; i >= 0; i--) {
+                    const double *Ri = cx.R + (size_t)i * n;
+                    double csum = 0.0;
+                    for (int j = i + 1; j < n; j++) csum += Ri[j] * (double)x[j];
+                    double rii = Ri[i];
+                    double mean = (cx.t[i] - csum) / rii;
+                    double sg = cx.sigma / fabs(rii);
+                    if (sg < 1e-10) continue;
+                    if (sg > 1e10) sg = fmin(sg, 1e6);
+                    table_build(tb, mean, sg, cx.precision);
+                    int len = tb->len;
+                    double *p = tb->work;
+                    for (int k = 0; k < len; k++) p[k] = exp(tb->logp[k]);
+                    double tot = np_pairwise_sum(p, len);
+                    int64_t c0 = (int64_t)nearbyint(mean);
+                    double fr = mean - floor(mean);
+                    int f = (int)(fr * FB);
+                    if (f >= FB) f = FB - 1;
+                    if (f < 0) f = 0;
+                    size_t base = ((size_t)i * FB + f) * W;
+                    const int64_t w = width && width[i] > 1 ? width[i] : 1;
+                    lo[base + (size_t)(bin_offset(x[i] - c0, w, K) + K)] += 1;
+                    for (int k = 0; k < len; k++)
+                        le[base + (size_t)(bin_offset(tb->lower + k - c0, w, K) + K)] += p[k] / tot;
+                }
+            }
+#ifdef _OPENMP
+#pragma omp critical
+#endif
+            {
+                for (size_t c = 0; c < cells; c++) {
+                    obs[c] += lo[c];
+                    expc[c] += le[c];
+                }
+            }
+        }
+        free(tb);
+        free(lo);
+        free(le);
+    }
+    return err ? -1 : 0;
+}
+
+/*
  * Replay of KleinSampler.sample(S): sample s consumes U[s*ups .. (s+1)*ups) with ups = uniforms per sample.
  * X int64[S*n], V double[S*n] or NULL, logq double[S] or NULL (Klein log-density, klein.py:222-271).
  * Returns 0, or -1 if a draw fell into the no-uniform fallback (stream layout then undefined).

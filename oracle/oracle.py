@@ -8,6 +8,7 @@ Each function names the reference code it restates (paths relative to the refere
   klein_replay       src/samplers/klein.py:181-220 (sample_single) x S, 222-271 (compute_log_density)
   imhk_replay        src/samplers/imhk.py:126-177  (_initialize_chain, step), 196-229 (sample)
   uniform_stream     numpy legacy RandomState(seed).random_sample(N) -- the "recorded uniform stream"
+  conditional_counts src/samplers/klein.py:189-195 (conditional means) + 101-170 (the table) applied to sampler OUTPUT
 """
 from __future__ import annotations
 
@@ -121,6 +122,26 @@ def klein_replay(prob: Problem, U: np.ndarray, S: int, want_v=True, want_logq=Tr
     if rc != 0:
         raise RuntimeError("oracle: a draw took the no-uniform fallback; stream layout undefined")
     return X, V, logq
+
+
+def conditional_counts(prob: Problem, X: np.ndarray, K: int = 6, FB: int = 4, threads=0, width=None):
+    """Per coordinate, per bin of frac(m_i) and per clipped offset x_i - round(m_i): observed counts in the sampler
+    output X [S, n] and the counts the reference's own table (klein.py:101-170) expects at the recomputed conditional
+    means (klein.py:189-195).  `width` (int32 [n], optional) coarsens the offsets of a coordinate into bins of that many
+    integers.  Returns (obs int64 [n, FB, 2K+1], exp float64 [n, FB, 2K+1])."""
+    X = np.ascontiguousarray(X, dtype=np.int64)
+    if width is not None:
+        width = np.ascontiguousarray(width, dtype=np.int32)
+        assert width.shape == (prob.n,)
+    S = X.shape[0]
+    obs = np.zeros((prob.n, FB, 2 * K + 1), dtype=np.int64)
+    exp = np.zeros((prob.n, FB, 2 * K + 1), dtype=np.float64)
+    rc = lib().lgs_oracle_conditional_counts(*prob._args(), ctypes.c_int64(S), _p(X, _i64p), ctypes.c_int(K),
+                                             ctypes.c_int(FB), _p(width, ctypes.POINTER(ctypes.c_int32)), _p(obs, _i64p),
+                                             _p(exp, _f64p), ctypes.c_int(threads))
+    if rc != 0:
+        raise MemoryError("oracle: conditional_counts could not allocate its accumulators")
+    return obs, exp
 
 
 def klein_seeded(prob: Problem, S: int, seed: int, chains: int = 1, want_v=True, threads=0):
