@@ -111,14 +111,14 @@ def test_chain_kernel_imhk_replay_stepwise_and_split_calls(lgs, oracle):
     and restarts per call; exact weights use the table normalisers"""
     from lattice_gaussian_mcmc_b200.lattices import dd_lattice
     lat = dd_lattice(24, seed=7)
-    sigma = 40.0
     center = np.random.RandomState(3).uniform(-5, 5, 24)
-    prob = oracle.Problem(lat.basis, sigma, center)
     chains, burn, keep, thin = 200, 5, 4, 3
     steps = burn + keep * thin
-    per = oracle.imhk_stream_len(prob, steps)
-    U = oracle.uniform_stream(99, chains * per)
     for exact in (False, True):
+        sigma = 18.0 if exact else 40.0    # sigma_i ~ 0.4: the normalisers vary with the means => real rejections
+        prob = oracle.Problem(lat.basis, sigma, center)
+        per = oracle.imhk_stream_len(prob, steps)
+        U = oracle.uniform_stream(99, chains * per)
         ref = oracle.imhk_replay(prob, U, chains, steps, thin=1, exact_logz=exact)
         im = lgs.IMHKSampler(lat, sigma, center, burn_in=0, n_chains=chains, mode="replay", uniforms=U,
                              path="blocked", weight_mode="exact" if exact else "reference")
@@ -135,7 +135,7 @@ def test_chain_kernel_imhk_replay_stepwise_and_split_calls(lgs, oracle):
             Vo = io.sample(n_samples=keep, burn_in=burn, thin=thin)
             assert np.array_equal(V, Vo)
             assert np.array_equal(im._last_accept, io._last_accept)
-            assert 0.2 < im._last_accept.mean() < 1.0
+            assert 0.1 < im._last_accept.mean() < 0.999, im._last_accept.mean()
             assert _rel(im._last_logw, io._last_logw) <= 1e-11
         assert im.total_proposals == chains * steps
 
