@@ -34,8 +34,31 @@ WORKLOAD = (f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim, f,g ~ D_Z,4.05 = B
             f"NTRUSolve, seed 0), sampler sigma={SIGMA}, Klein sampling + IMHK")
 DIM = 2 * N_RING
 KLEIN_FLOP = 3 * DIM * DIM - DIM                # back-substitution n(n-1) + lattice point 2n^2   
-NCU_TRAFFIC_BYTES = 37.94e9                     # dram read 33.81 GB + write 4.13 GB per launch of the chain kernel at
-                                                # S = 170 496 (profiles/r01j_ncu_full_summary.json; r01c: 37.72 GB)
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the Klein chain kernel, from the NEWEST committed
+    `ncu --set full` summary of this command (profiles/*ncu_full_summary.json, written by tools/ncu_summary.py).
+    Returns (bytes or None, source file)."""
+    import glob
+    import re
+    def val(txt):
+        m = re.match(r"([0-9.eE+-]+)\s*([KMGT]?)byte", txt.strip())
+        return float(m.group(1)) * {"": 1, "K": 1e3, "M": 1e6, "G": 1e9, "T": 1e12}[m.group(2)] if m else None
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_summary.json")),
+                   key=lambda f: (re.sub(r"^r(\d+)([a-z]*)_.*", lambda m: f"{int(m.group(1)):04d}{m.group(2):>3}",
+                                         os.path.basename(f))))
+    for f in reversed(files):
+        try:
+            for k in json.load(open(f)).get("kernels", []):
+                name = k.get("Kernel Name", "")
+                if "klein_chain_kernel<0, 0, 0, 0" in name and k.get("launch__grid_size") == "148":
+                    r, w = val(k["dram__bytes_read.sum"]), val(k["dram__bytes_write.sum"])
+                    if r is not None and w is not None:
+                        return r + w, os.path.relpath(f, ROOT)
+        except Exception:
+            continue
+    return None, None
 
 
 def imhk_flop(thin):                             # proposal back-substitution + two quadratic forms + kept point / thin
@@ -113,15 +136,57 @@ def cpu_baseline(lat, seconds=12.0):
     dt = time.perf_counter() - t0
     return {"value": S / dt, "unit": "samples/s", "cores": cores, "kind": "port",
             "sample": f"{S} Klein samples of the same NTRU-512 lattice, {cores} OpenMP threads, {dt:.1f} s; "
-                      "C restatement of klein.py:101-220 (the Python reference itself measured 2.7 samples/s/core at "
-                      "n=1024 in the survey container, BASELINE.md section 2)"}
+                      "C restatement of klein.py:101-220 (value); the reference's own numpy code timed beside it in "
+                      "reference_python",
+            "reference_python": reference_python_leg(lat)}
+
+
+def reference_python_leg(lat, samples_per_proc=24, imhk_steps_per_proc=8):
+    """The reference's OWN src/samplers/klein.py + imhk.py (staged into oracle/_ref by build(), see
+    oracle/ref_python.py) on this box's host cores, the way its scaling experiment runs them: one independently seeded
+    process per core (experiments/dimension_scaling.py:841-845, 877-884), warm-up sample excluded.  About 0.35 s per
+    1024-dim sample per core => ~10 s for the Klein leg."""
+    from oracle import ref_python
+    if not ref_python.available():
+        return {"unavailable": "oracle/_ref not staged (build() stages it where /root/reference is mounted)"}
+    procs = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    k = ref_python.time_klein(lat.basis, SIGMA, procs=procs, samples_per_proc=samples_per_proc, seed=0)
+    m = ref_python.time_imhk(lat.basis, SIGMA, procs=procs, steps_per_proc=imhk_steps_per_proc, thin=1, seed=0)
+    return {"value": k["value"], "unit": "samples/s", "cores": procs, "procs": procs, "per_core": k["per_core"],
+            "sample": f"RefinedKleinSampler.sample({samples_per_proc}) in each of {procs} processes "
+                      f"(np.random.seed(0 + 1000 i)), {k['sampling_s']:.1f} s; same lattice and sigma",
+            "imhk": {"value": m["value"], "unit": "chain-steps/s", "per_core": m["per_core"],
+                     "sample": f"IMHKSampler.sample({imhk_steps_per_proc}) per process, {m['sampling_s']:.1f} s"},
+            "versions": k["versions"]}
+
+
+def host_info():
+    """what the host offers the ranks: CPUs, NUMA nodes, this process' affinity"""
+    info = {"nproc": os.cpu_count(), "affinity": sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else None}
+    try:
+        nodes = sorted(d for d in os.listdir("/sys/devices/system/node") if d.startswith("node"))
+        info["numa_nodes"] = {d: open(f"/sys/devices/system/node/{d}/cpulist").read().strip() for d in nodes}
+    except Exception:
+        info["numa_nodes"] = None
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                info["cpu_model"] = line.split(":", 1)[1].strip()
+                break
+        info["thp"] = open("/sys/kernel/mm/transparent_hugepage/enabled").read().strip()
+    except Exception:
+        pass
+    a = info["affinity"]
+    if a is not None:
+        info["affinity"] = f"{len(a)} cpus: {a[0]}-{a[-1]}" if a == list(range(a[0], a[-1] + 1)) else a
+    return info
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
     import __graft_entry__ as g
-    g.build()
+    g.build_oracle()               # the checker only: this arm never loads the product library
     from oracle import oracle
     lat = build_lattice()
     cores = os.cpu_count() or 1
@@ -145,7 +210,9 @@ def run_reference(args, rank, world):
             "config": {"workload": WORKLOAD, "samples_per_step": S,
                        "sample_of": "the same lattice, sigma and sampler as the GPU arm; a bounded sample per step"},
             "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port",
-                             "sample": f"{S} samples per step x {args.steps} steps, {cores} OpenMP threads"},
+                             "sample": f"{S} samples per step x {args.steps} steps, {cores} OpenMP threads",
+                             "reference_python": reference_python_leg(lat)},
+            "host": host_info(),
             "imhk": {"value": imhk_val, "unit": "chain-steps/s", "sample": f"{cores} chains x {steps_imhk} steps"},
             "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -164,6 +231,8 @@ def main():
     ap.add_argument("--skip-imhk", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--check-invariance", action="store_true",
+                    help="(always on) every rank hashes the samples of ids [0, 4096); see `invariance` in the line")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -241,6 +310,11 @@ def main():
     eng.profile_enable(False)
     launches_per_step = sum(c for _, c in prof.values()) // K
     peak, peak_src = fp64_peak()
+    traffic, traffic_src = ncu_traffic()
+    try:
+        hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        hbm_peak = None
     if prof["chain"][1] > 0:        # the persistent chain kernel does the whole sample: (3 n^2 - n) flop per sample
         pt_ms, pt_cnt = prof["chain"]
         pt_flop = float(KLEIN_FLOP) * S
@@ -256,82 +330,173 @@ def main():
     # ---------------------------------------------------------------- e2e: the C ABI with HOST buffers
     e2e = None
     if not args.skip_e2e:
-        S2 = S
-        Vh = torch.empty((S2, n), dtype=torch.float64).pin_memory()
         import ctypes
         from lattice_gaussian_mcmc_b200._capi import check
+        BATCHES = 4                                       # batches per host call: the streamed int16 route
+        S2 = BATCHES * S
+        Vh = torch.empty((S2, n), dtype=torch.float64).pin_memory()
+
         def host_step(k, base=30_000):
             gid = ((base + k) * world + rank) * S2
             check(eng._h, eng._lib.lgs_klein_sample_host(eng._h, S2, smp.seed, gid, 1, Vh.data_ptr(), None, None))
+
+        def wall(fn, steps):
+            sync_all()
+            t0 = time.perf_counter()
+            for k in range(steps):
+                fn(k)
+            torch.cuda.synchronize()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+            windows.append((t0, time.perf_counter()))
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            return float(dt.item())
+
         for w in range(2):
             host_step(w, base=40_000)
-        sync_all()
-        t0 = time.perf_counter()
-        for k in range(K):
-            host_step(k)
-        torch.cuda.synchronize()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-        windows.append((t0, time.perf_counter()))
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        Ke = max(2, (K + BATCHES - 1) // BATCHES)         # the same number of batches as K single-batch steps
+        dt = wall(host_step, Ke)
         transport = int(eng._lib.lgs_host_transport(eng._h))
         tname = {0: "fp64 copies", 1: "int16 pack kernel + chunked copies, widened to float64 by the host pool",
-                 2: "int16 written by the chain kernel into mapped pinned memory (zero-copy), widened to float64 by "
-                    "the host pool tile by tile while the kernel runs"}[transport]
-        d2h = S2 * n * 8 if transport == 0 else S2 * n * 2 + 4 * ((S2 + 127) // 128)
-        e2e = {"value": world * S2 * K / float(dt.item()), "unit": "samples/s", "h2d_bytes_per_step": 16,
-               "d2h_bytes_per_step": d2h, "host_bytes_delivered_per_step": S2 * n * 8, "transport": tname,
-               "host_threads_per_rank": int(os.environ.get("LGS_HOST_THREADS", 0)) or max(
-                   1, len(os.sched_getaffinity(0)) // int(os.environ.get("LOCAL_WORLD_SIZE", "1"))),
-               "note": "lgs_klein_sample_host: the sampler's only inputs are (seed, first id) scalars; every step "
-                       "delivers its S x n float64 lattice points (the reference's return array) into a pinned host "
-                       "buffer; for this integer basis they cross PCIe as int16, bit-identical after widening"}
-        del Vh
+                 2: "int16 written by the chain kernel's lattice-point epilogue (HBM), shipped group by group by the "
+                    "copy engine behind cuStreamWaitValue32 while the kernel runs, widened to float64 by the host pool"
+                 }[transport]
+        threads = int(os.environ.get("LGS_HOST_THREADS", 0)) or max(
+            1, len(os.sched_getaffinity(0)) // int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+        # the host's own ceiling for this delivery: the pool widening a RESIDENT int16 buffer into the same float64
+        # array with non-temporal stores, every rank at once (what the transport does minus the GPU and PCIe)
+        src16 = np.zeros((S, n), dtype=np.int16)
+        dst64 = Vh.numpy()[:S]
+        best = 1e9
+        for r in range(4):
+            sync_all()
+            t0 = time.perf_counter()
+            check(None, eng._lib.lgs_host_widen_i16(src16.ctypes.data, dst64.ctypes.data, S * n, threads))
+            best = min(best, time.perf_counter() - t0)
+        tb = torch.tensor([best], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+        store_gbs = world * S * n * 8 / float(tb.item()) / 1e9
+        e2e_rate = world * S2 * Ke / dt
+        d2h = S * n * 8 if transport == 0 else S * n * 2 + 4 * ((S + 127) // 128)
+        e2e = {"value": e2e_rate, "unit": "samples/s", "h2d_bytes_per_step": 16,
+               "d2h_bytes_per_step": d2h, "host_bytes_delivered_per_step": S * n * 8,
+               "call_shape": f"lgs_klein_sample_host into a pinned, reused float64 [{S2}, {n}] buffer, {BATCHES} batches "
+                             f"of {S} per call (a 'step' of this leg = one batch), {Ke} calls timed",
+               "transport": tname, "host_threads_per_rank": threads,
+               "host_store_gbs_peak": store_gbs,
+               "host_store_peak_how": "lgs_host_widen_i16 on a resident int16 buffer into the same pinned float64 "
+                                      "array, all ranks at once with their pool threads, best of 4",
+               "frac_of_host_peak": e2e_rate * n * 8 / 1e9 / store_gbs,
+               "note": "the sampler's only inputs are (seed, first id) scalars; every step delivers its S x n float64 "
+                       "lattice points (the reference's return array) into host memory; for this integer basis they "
+                       "cross PCIe as int16, bit-identical after widening"}
+        del Vh, src16, dst64
+        # the reference-shaped call: KleinSampler.sample(S) returns a FRESH float64 array every time (klein.py:322)
+        def fresh_step(k):
+            smp._next_sample_id = ((50_000 + k) * world + rank) * S
+            out = smp.sample(S)
+            assert out.shape == (S, n)
+        for w in range(2):
+            fresh_step(w)
+        Kf = max(2, min(K, 6))
+        dtf = wall(fresh_step, Kf)
+        e2e["fresh_array"] = {"value": world * S * Kf / dtf, "unit": "samples/s",
+                              "call_shape": f"KleinSampler.sample({S}) -> a fresh float64 array per call (the reference's "
+                                            "return contract; 2 MB-aligned anonymous mapping + MADV_HUGEPAGE, first "
+                                            "touched by the widening pool)", "calls": Kf}
+        e2e["host"] = host_info()
 
     # ---------------------------------------------------------------- IMHK leg
-    imhk = None
+    imhk = imhk_exact = None
     if not args.skip_imhk:
+        from lattice_gaussian_mcmc_b200 import distributed as D
         thin = args.thin
-        eng.imhk_reset(C, seed=77, first_chain_id=rank * C)
         Vk = torch.empty((C, 1, n), dtype=torch.float64, device="cuda")
-        counts = torch.zeros((C, 2), dtype=torch.int64, device="cuda")
-        hist = torch.zeros((4, 64), dtype=torch.int64, device="cuda")
         dims = np.array([0, 1, n // 2, n - 1], dtype=np.int32)
 
-        def imhk_step(k):
-            eng.imhk_run_dev(0, 1, thin, "fast", "reference", V=Vk.data_ptr(), stream=stream)
-            # statistics of src/diagnostics (acceptance mean, marginal histograms): accumulate per rank ...
-            eng.histogram_dev(Vk.data_ptr(), C, dims, -8 * SIGMA, SIGMA / 4, 64, hist.data_ptr(), stream=stream)
+        def imhk_leg(weight, steps):
+            eng.imhk_reset(C, seed=77, first_chain_id=rank * C)
+            counts = torch.zeros((C, 2), dtype=torch.int64, device="cuda")
+            hist = torch.zeros((4, 64), dtype=torch.int64, device="cuda")
+            res = {}
 
-        for w in range(2):
-            imhk_step(w)
-        hist.zero_()
+            def imhk_step(k):
+                eng.imhk_run_dev(0, 1, thin, "fast", weight, V=Vk.data_ptr(), stream=stream)
+                # statistics of src/diagnostics (acceptance mean, marginal histograms): accumulate per rank ...
+                eng.histogram_dev(Vk.data_ptr(), C, dims, -8 * SIGMA, SIGMA / 4, 64, hist.data_ptr(), stream=stream)
 
-        from lattice_gaussian_mcmc_b200 import distributed as D
+            for w in range(2):
+                imhk_step(w)
+            hist.zero_()
 
-        def imhk_all(k):
-            imhk_step(k)
-            if k == K - 1:                                # ... and all-reduce once at the end of the run (NCCL)
-                eng.imhk_state_dev(counts=counts.data_ptr(), stream=stream)
-                imhk_all.tot, imhk_all.hist = D.allreduce_stats(counts, hist)
-        ms_imhk = timed(imhk_all, K)
-        tot = imhk_all.tot.cpu().numpy()
-        rate = world * C * thin * K / (ms_imhk * 1e-3)
-        # per-class device time of the same work (separate pass, events around every launch)
-        eng.profile_enable(True)
-        for k in range(2):
-            imhk_step(k)
-        iprof = eng.profile_read()
-        eng.profile_enable(False)
-        itot = max(sum(v[0] for v in iprof.values()), 1e-9)
-        imhk = {"value": rate, "unit": "chain-steps/s", "chains_per_gpu": C, "thin": thin, "ms_per_step": ms_imhk / K,
-                "acceptance_rate": D.acceptance_rate(imhk_all.tot.cpu()),
-                "flop_per_chain_step": imhk_flop(thin),
-                "fp64_tflops_per_gpu": rate / world * imhk_flop(thin) * 1e-12,
-                "fp64_frac_of_peak": rate / world * imhk_flop(thin) * 1e-12 / peak,
-                "share_of_step": {k: round(v[0] / itot, 4) for k, v in iprof.items()},
-                "gpu_launches_per_step": sum(v[1] for v in iprof.values()) // 2,
-                "hist_total": int(imhk_all.hist.sum().item())}
+            def imhk_all(k):
+                imhk_step(k)
+                if k == steps - 1:                            # ... and all-reduce once at the end of the run (NCCL)
+                    eng.imhk_state_dev(counts=counts.data_ptr(), stream=stream)
+                    res["tot"], res["hist"] = D.allreduce_stats(counts, hist)
+            ms = timed(imhk_all, steps)
+            rate = world * C * thin * steps / (ms * 1e-3)
+            # per-class device time of the same work (separate pass, events around every launch)
+            eng.profile_enable(True)
+            for k in range(2):
+                imhk_step(k)
+            iprof = eng.profile_read()
+            eng.profile_enable(False)
+            itot = max(sum(v[0] for v in iprof.values()), 1e-9)
+            return {"value": rate, "unit": "chain-steps/s", "weight_mode": weight, "chains_per_gpu": C, "thin": thin,
+                    "ms_per_step": ms / steps, "acceptance_rate": D.acceptance_rate(res["tot"].cpu()),
+                    "flop_per_chain_step": imhk_flop(thin),
+                    "fp64_tflops_per_gpu": rate / world * imhk_flop(thin) * 1e-12,
+                    "fp64_frac_of_peak": rate / world * imhk_flop(thin) * 1e-12 / peak,
+                    "share_of_step": {k: round(v[0] / itot, 4) for k, v in iprof.items()},
+                    "gpu_launches_per_step": sum(v[1] for v in iprof.values()) // 2,
+                    "hist_total": int(res["hist"].sum().item())}
+
+        imhk = imhk_leg("reference", K)
+        # the Wang-Ling weights (LGS_WEIGHT_EXACT): normalisers accumulated, exp + accept draw per step.  At this
+        # lattice's sigma_i >= 1.29 the normalisers are constant to ~1e-13, so the acceptance rate stays 1 - O(1e-13);
+        # tools/quick_imhk.py runs the same mode where it rejects (sigma = 60: sigma_i ~ 0.5)
+        imhk_exact = imhk_leg("exact", max(3, K // 2))
+
+    # ---------------------------------------------------------------- replay through the same kernel (parity mode)
+    replay = None
+    if not args.skip_imhk:
+        Sr = S // 3                                           # one round of tiles: the table sampler is ~40x slower
+        U = torch.rand((Sr, eng.ups), dtype=torch.float64, device="cuda")
+        if eng.replay_on_chain:
+            eng.klein_replay_dev(Sr, U.data_ptr(), V=V.data_ptr(), stream=stream)
+            ms_r = timed(lambda k: eng.klein_replay_dev(Sr, U.data_ptr(), V=V.data_ptr(), stream=stream), 2)
+            replay = {"value": world * Sr * 2 / (ms_r * 1e-3), "unit": "samples/s", "samples_per_gpu_per_step": Sr,
+                      "kernel": "klein_chain_kernel<0,1,0,0,REPLAY> (recorded uniforms + the reference's table SampleZ "
+                                "on DMMA-contracted means; lgs_klein_replay on a LGS_PATH_BLOCKED handle)"}
+        del U
+
+    # ---------------------------------------------------------------- rank-count invariance (SURVEY 8e "test this")
+    # Every rank samples ids [0, 4096) in full AND its own 1/world slice of them; a 64-bit hash of the integer
+    # coefficients, additive over samples, must (a) be the same on every rank and (b) equal the all-reduced sum of the
+    # slice hashes.  The N = 1, 2, 4, 8 lines of a scaling run therefore carry the same `hash`.
+    def coeff_hash(first, count):
+        Xi = torch.empty((count, n), dtype=torch.int64, device="cuda")
+        eng.klein_sample_dev(count, 424242, first, "fast", X=Xi.data_ptr(), stream=stream)
+        gid = torch.arange(first, first + count, dtype=torch.int64, device="cuda")[:, None] * n + \
+            torch.arange(n, dtype=torch.int64, device="cuda")[None, :]
+        wgt = gid * -7046029254386353131 + 0x2545F4914F6CDD1D        # odd multiplier: int64 arithmetic wraps
+        return (Xi * wgt).sum()
+    NI = 4096
+    h_full = coeff_hash(0, NI)
+    part = NI // world
+    h_part = coeff_hash(rank * part, part if rank < world - 1 else NI - rank * part)
+    h_sum, h_min, h_max = h_part.clone(), h_full.clone(), h_full.clone()
+    if world > 1:
+        dist.all_reduce(h_sum, op=dist.ReduceOp.SUM)
+        dist.all_reduce(h_min, op=dist.ReduceOp.MIN)
+        dist.all_reduce(h_max, op=dist.ReduceOp.MAX)
+    invariance = {"ids": f"[0, {NI}) under seed 424242", "hash": f"{int(h_full.item()) & (2**64 - 1):016x}",
+                  "all_ranks_equal": bool(h_min.item() == h_max.item() == h_full.item()),
+                  "sum_of_rank_slices_equals_full": bool(h_sum.item() == h_full.item())}
+    if not (invariance["all_ranks_equal"] and invariance["sum_of_rank_slices_equals_full"]):
+        raise SystemExit(f"rank-count invariance violated: {invariance}")
 
     clk = clocks.stop(windows) if rank == 0 else None
     cpu = None
@@ -354,13 +519,17 @@ def main():
             "roofline": {"bound": "tensor", "kernel": kernel_name,
                          "achieved": pt_tf, "peak": peak, "unit": "TFLOP/s", "frac": pt_tf / peak,
                          "peak_source": peak_src,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel per launch from the ncu
-                         # --set full capture of this command (profiles/r01c_ncu_full_summary.json)
-                         "traffic": NCU_TRAFFIC_BYTES if (S == 170496 and n == 1024 and prof["chain"][1] > 0) else None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel per launch from the newest
+                         # committed ncu --set full capture of this command
+                         "traffic": traffic if (S == 170496 and n == 1024 and prof["chain"][1] > 0) else None,
+                         "traffic_source": traffic_src,
+                         "traffic_frac_of_hbm_peak": (traffic / (pt_ms / pt_cnt * 1e-3) / 1e9 / hbm_peak
+                                                      if traffic and hbm_peak else None),
                          "algorithmic_flop_per_launch": pt_flop, "avg_launch_ms": pt_ms / pt_cnt,
                          "share_of_step": share},
             "gpu_launches": int(launches_per_step * K),
-            "e2e": e2e, "imhk": imhk, "cpu_baseline": cpu, "clocks": clk,
+            "e2e": e2e, "imhk": imhk, "imhk_exact": imhk_exact, "replay": replay, "invariance": invariance,
+            "cpu_baseline": cpu, "clocks": clk,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -9,6 +9,8 @@
  *   - every function returns 0 on success or a negative LGS_E_* code; nothing throws across the ABI;
  *     lgs_last_error() gives the text of the last failure on a handle (or of the last lgs_create()).
  *   - one handle per CUDA device; calls on one handle are serialised by the caller; handles are independent.
+ *     A handle owns scratch buffers (coefficient workspaces, diagnostics scratch) that its calls write in stream
+ *     order: issue the calls of one handle on ONE stream at a time, or order the streams with events yourself.
  *   - `*_dev` pointers are device memory on the handle's device (e.g. a torch tensor's data_ptr());
  *     `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Calls are asynchronous
  *     with respect to the host unless the name ends in `_host`.
@@ -205,6 +207,21 @@ LGS_API int lgs_imhk_replay(lgs_handle *h, int64_t burn_in, int64_t keep, int64_
  */
 LGS_API int lgs_imhk_get_state(lgs_handle *h, int64_t *counts_dev, int64_t *X_dev, double *V_dev, double *logw_dev,
                        void *stream);
+/*
+ * Checkpoint / resume.  The reference's chain state is three plain attributes a caller can assign
+ * (IMHKSampler.current_state / current_coeffs / current_log_weight, imhk.py:59-61) plus two counters (imhk.py:54-55).
+ * lgs_imhk_set_state installs, after lgs_imhk_reset(chains, seed, first_chain_id), for every chain: its integer
+ * coefficient vector X_dev [chains*n] (the lattice point is B x), its log importance weight logw_dev [chains], its
+ * counters counts_dev [chains*2] (NULL: zeros), and `steps_done`, the number of Metropolis-Hastings steps the chain had
+ * performed when the state was taken (lgs_imhk_steps_done) -- the index of its Philox stream, so a resumed native-mode
+ * run continues the uninterrupted run draw for draw.  `samplez` names the kernels that will continue the chains
+ * (as in lgs_imhk_run: LGS_SAMPLEZ_FAST on a non-ordered handle = the chain kernel, else the ordered kernels).
+ */
+LGS_API int lgs_imhk_set_state(lgs_handle *h, int samplez, const int64_t *X_dev, const double *logw_dev,
+                       const int64_t *counts_dev, int64_t steps_done, void *stream);
+LGS_API int lgs_imhk_set_state_host(lgs_handle *h, int samplez, const int64_t *X_host, const double *logw_host,
+                            const int64_t *counts_host, int64_t steps_done);
+LGS_API int64_t lgs_imhk_steps_done(const lgs_handle *h);
 /* sum over chains of (accepted, total), copied to the host: the two numbers acceptance_rate is made of */
 LGS_API int lgs_imhk_counts_host(lgs_handle *h, int64_t *accepted, int64_t *total);
 
@@ -221,7 +238,9 @@ LGS_API int lgs_imhk_get_state_host(lgs_handle *h, int64_t *counts_host, int64_t
  * Marginal histograms for src/diagnostics/convergence_diag.py:15-72 (compute_tvd) on device-resident samples:
  * for each tracked coordinate d in dims[], counts of floor((V[s, d] - lo) / width) over [0, nbins), values
  * outside are dropped into the first / last bin.  hist_dev is int64[n_dims*nbins] and is ACCUMULATED into, so
- * per-rank results can be all-reduced (sum) afterwards.
+ * per-rank results can be all-reduced (sum) afterwards.  Any n_dims and nbins: coordinates are processed 256 per launch,
+ * with block-private shared-memory bins while 256 * nbins * 4 bytes fit 160 KB and global (L2) atomics beyond that
+ * (e.g. all 1024 marginals of the NTRU lattice over +-1500).  Touches no per-handle scratch.
  */
 LGS_API int lgs_histogram(lgs_handle *h, const double *V_dev, int64_t S, const int32_t *dims_host, int32_t n_dims,
                   double lo, double width, int32_t nbins, int64_t *hist_dev, void *stream);

@@ -70,6 +70,9 @@ PROTOTYPES = {
     "lgs_imhk_run_host": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp, vp]),
     "lgs_imhk_replay_host": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, vp, ctypes.c_int64, vp, vp, vp, vp, vp]),
     "lgs_imhk_get_state_host": (ctypes.c_int, [vp, vp, vp, vp, vp]),
+    "lgs_imhk_set_state": (ctypes.c_int, [vp, ctypes.c_int, vp, vp, vp, ctypes.c_int64, vp]),
+    "lgs_imhk_set_state_host": (ctypes.c_int, [vp, ctypes.c_int, vp, vp, vp, ctypes.c_int64]),
+    "lgs_imhk_steps_done": (ctypes.c_int64, [vp]),
     "lgs_imhk_counts_host": (ctypes.c_int, [vp, c_i64p, c_i64p]),
     "lgs_chain_diagnostics": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int64, c_i32p, ctypes.c_int32, ctypes.c_double,
                                              ctypes.c_int32, vp, vp, ctypes.c_int32, vp]),

@@ -7,6 +7,10 @@ GPU (bench.py, the multi-GPU driver).  No sampling happens in Python and nothing
 from __future__ import annotations
 
 import ctypes
+import mmap
+import os
+import threading
+import weakref
 
 import numpy as np
 
@@ -25,6 +29,79 @@ def precompute_qr(basis: np.ndarray, center: np.ndarray):
             Q[:, i] *= -1
     t = Q.T @ center
     return Q, R, t
+
+
+_HUGE = 2 << 20
+
+
+class _Block:
+    """Owner of one result buffer: exports the mapping through the buffer protocol (PEP 688), so that every numpy
+    array and view made from it keeps it alive; when the last one dies the mapping goes back to the cache."""
+    __slots__ = ("mm", "off", "nbytes", "__weakref__")
+
+    def __init__(self, mm, off, nbytes):
+        self.mm, self.off, self.nbytes = mm, off, nbytes
+
+    def __buffer__(self, flags):
+        return memoryview(self.mm)[self.off:self.off + self.nbytes]
+
+
+class _HostArrayCache:
+    """Recycles the host memory of large result arrays.  The reference returns a NEW array per call (klein.py:322);
+    a new 1.4 GB array means 350 k page faults (half the cost of KleinSampler.sample(170496) in round 1).  Arrays
+    handed out here are new objects over 2 MB-aligned anonymous mappings (MADV_HUGEPAGE); when the caller drops an
+    array -- and every view of it -- its mapping is kept (up to LGS_HOST_CACHE_MB, default 4096) and backs a later
+    result of the same size, already faulted in.  LGS_HOST_CACHE_MB=0 disables the cache (np.empty)."""
+
+    def __init__(self):
+        self.free = {}      # nbytes -> [(mm, off)]
+        self.cached = 0
+        self.lock = threading.Lock()
+        self.limit = int(os.environ.get("LGS_HOST_CACHE_MB", "4096")) << 20
+
+    def _release(self, mm, off, nbytes):
+        with self.lock:
+            if self.cached + nbytes <= self.limit:
+                self.free.setdefault(nbytes, []).append((mm, off))
+                self.cached += nbytes
+                return
+        try:
+            mm.close()
+        except BufferError:
+            pass
+
+    def empty(self, shape, dtype=np.float64):
+        count = int(np.prod(shape))
+        nbytes = count * np.dtype(dtype).itemsize
+        if nbytes < (64 << 20) or self.limit <= 0:
+            return np.empty(shape, dtype=dtype)
+        with self.lock:
+            lst = self.free.get(nbytes)
+            hit = lst.pop() if lst else None
+            if hit:
+                self.cached -= nbytes
+        try:
+            if hit:
+                mm, off = hit
+            else:
+                mm = mmap.mmap(-1, nbytes + _HUGE)
+                addr = ctypes.addressof(ctypes.c_char.from_buffer(mm))
+                off = (-addr) % _HUGE
+                if hasattr(mmap, "MADV_HUGEPAGE") and os.environ.get("LGS_FRESH_HUGEPAGE", "1") != "0":
+                    mm.madvise(mmap.MADV_HUGEPAGE)
+            blk = _Block(mm, off, nbytes)
+            weakref.finalize(blk, self._release, mm, off, nbytes)
+            return np.frombuffer(blk, dtype=dtype, count=count).reshape(shape)
+        except (OSError, ValueError, BufferError, TypeError):
+            return np.empty(shape, dtype=dtype)
+
+
+_host_cache = _HostArrayCache()
+
+
+def fresh_array(shape, dtype=np.float64):
+    """A new writeable C-contiguous array for a result the device pipeline fills (see _HostArrayCache)."""
+    return _host_cache.empty(shape, dtype)
 
 
 def _ptr(a, typ=ctypes.c_void_p):
@@ -77,7 +154,7 @@ class Engine:
                     and out.flags.c_contiguous and out.flags.writeable):
                 raise ValueError(f"out must be a writeable C-contiguous float64 array of shape ({S}, {self.n})")
             want_v = True
-        V = out if out is not None else (np.empty((S, self.n), dtype=np.float64) if want_v else None)
+        V = out if out is not None else (fresh_array((S, self.n)) if want_v else None)
         X = np.empty((S, self.n), dtype=np.int64) if want_x else None
         lq = np.empty(S, dtype=np.float64) if want_logq else None
         check(self._h, self._lib.lgs_klein_sample_host(self._h, S, int(seed) & (2**64 - 1), int(first_id),
@@ -139,6 +216,19 @@ class Engine:
         lw = np.empty(C, dtype=np.float64)
         check(self._h, self._lib.lgs_imhk_get_state_host(self._h, _ptr(counts), _ptr(X), _ptr(V), _ptr(lw)))
         return counts, X, V, lw
+
+    def imhk_steps_done(self) -> int:
+        return int(self._lib.lgs_imhk_steps_done(self._h))
+
+    def imhk_set_state(self, X, logw, counts=None, steps_done=0, samplez="fast"):
+        """lgs_imhk_set_state_host: install a chain state taken with imhk_state() / imhk_steps_done()"""
+        C = self.chains
+        X = np.ascontiguousarray(X, dtype=np.int64).reshape(C, self.n)
+        logw = np.ascontiguousarray(logw, dtype=np.float64).reshape(C)
+        if counts is not None:
+            counts = np.ascontiguousarray(counts, dtype=np.int64).reshape(C, 2)
+        check(self._h, self._lib.lgs_imhk_set_state_host(self._h, SAMPLEZ[samplez], _ptr(X), _ptr(logw), _ptr(counts),
+                                                         int(steps_done)))
 
     def imhk_counts(self):
         a, t = ctypes.c_int64(0), ctypes.c_int64(0)

@@ -9,6 +9,8 @@
 #include <new>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "lgs_internal.h"
 
 using namespace lgs;
@@ -33,6 +35,16 @@ int cuda_fail(lgs_handle* h, cudaError_t e, const char* where) {
         cudaError_t e__ = (call);                                \
         if (e__ != cudaSuccess) return cuda_fail(h, e__, #call); \
     } while (0)
+
+// NVTX range around a C-ABI call (tracing): visible to nsys / ncu --nvtx, free when no tool is
+// attached (the header-only NVTX v3 stub resolves to no-ops)
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
+#define LGS_TRACE() NvtxRange nvtx_range__(__func__)
 
 struct ArenaBuilder {
     std::vector<uint8_t> bytes;
@@ -116,6 +128,7 @@ int lgs_create(const lgs_desc* d, lgs_handle** out) {
 }
 
 static int create_impl(const lgs_desc* d, lgs_handle** out) {
+    NvtxRange nvtx_range__("lgs_create");
     if (!d || !out) return fail(nullptr, LGS_E_INVALID, "lgs_create: NULL argument");
     *out = nullptr;
     if (d->n <= 0) return fail(nullptr, LGS_E_INVALID, "lgs_create: n must be positive");
@@ -244,6 +257,7 @@ static int create_impl(const lgs_desc* d, lgs_handle** out) {
     for (size_t i = 0; i < (size_t)n * n && h->pack_ok; i++)
         h->pack_ok = d->B[i] == std::nearbyint(d->B[i]) && std::fabs(d->B[i]) < 9007199254740992.0;
     if (const char* e = getenv("LGS_HOST_PACK")) h->pack_ok = h->pack_ok && atoi(e) != 0;
+    h->pack_ok = h->pack_ok && host_simd_ok();   // the widening loops are AVX2: without it, the fp64 route
     *out = h;
     return LGS_OK;
 }
@@ -302,6 +316,7 @@ int64_t lgs_preferred_batch(const lgs_handle* h) {
 
 int lgs_klein_sample(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez, double* V_dev,
                      int64_t* X_dev, double* logq_dev, void* stream) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (S < 0) return fail(h, LGS_E_INVALID, "lgs_klein_sample: S < 0");
     if (samplez != LGS_SAMPLEZ_TABLE && samplez != LGS_SAMPLEZ_FAST)
@@ -348,6 +363,7 @@ static int klein_replay_impl(lgs_handle* h, int64_t S, const double* U_dev, doub
 
 int lgs_klein_replay(lgs_handle* h, int64_t S, const double* U_dev, double* V_dev, int64_t* X_dev, double* logq_dev,
                      int32_t* fallback_count_dev, void* stream) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (S < 0 || (S > 0 && !U_dev)) return fail(h, LGS_E_INVALID, "lgs_klein_replay: bad arguments");
     LGS_CUDA(h, cudaSetDevice(h->device));
@@ -468,7 +484,7 @@ static bool host_memory_is_pinned(const void* p) {
 static bool bounce_enabled() {
     static const bool on = [] {
         const char* e = std::getenv("LGS_HOST_BOUNCE");
-        return !(e && e[0] == '0') && hostpool_default_threads() >= 2;
+        return !(e && e[0] == '0') && hostpool_default_threads() >= 2 && host_simd_ok();
     }();
     return on;
 }
@@ -733,7 +749,11 @@ static int klein_host_zerocopy(lgs_handle* h, int64_t S, uint64_t seed, uint64_t
         if (failed.load()) return fail(h, LGS_E_CUDA, "lgs_klein_sample_host: the chain kernel ended without publishing every tile");
         int ovf = 0;
         LGS_CUDA(h, cudaMemcpy(&ovf, h->zc_ovf + b, sizeof(int), cudaMemcpyDeviceToHost));
-        if (ovf) {  // a value outside int16: this batch again, as fp64 (cudaMemcpy above has drained the stream)
+        if (ovf) {
+            // A value outside int16: this batch again, as fp64.  host_compute / host_copy are cudaStreamNonBlocking, so the
+            // legacy-stream cudaMemcpy above has NOT drained them: batch k + 1's kernel and its gated copies may still be
+            // in flight.  The re-run is ordered after them because it is enqueued on the same two streams (and shares
+            // chain.work[0] with batch k + 1 in stream order); its output buffers are this batch's alone.
             rc = klein_host_common(h, cnt, nullptr, seed, first_id + (uint64_t)s0, LGS_SAMPLEZ_FAST, V_host + (size_t)s0 * n,
                                    nullptr, nullptr, nullptr, false);
             if (rc) return rc;
@@ -748,9 +768,31 @@ static int klein_host_zerocopy(lgs_handle* h, int64_t S, uint64_t seed, uint64_t
 // staging slots while chunk k-1 travels to the host on the copy stream, so the PCIe transfer (the larger cost:
 // 8n bytes per sample) hides the sampling.  Works with pageable host memory too (the copy then blocks the host, not
 // the device).
+static int klein_host_common_impl(lgs_handle* h, int64_t S, const double* U_host, uint64_t seed, uint64_t first_id,
+                                  int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host,
+                                  bool allow_pack);
+
+// Every early error return below can leave work in flight on the handle's two streams that reads or writes
+// handle-owned buffers: drain them before the error reaches the caller, so that a later call or lgs_destroy cannot
+// free or reuse a buffer under a running kernel.
 static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uint64_t seed, uint64_t first_id,
                              int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host,
                              bool allow_pack) {
+    const int rc = klein_host_common_impl(h, S, U_host, seed, first_id, samplez, V_host, X_host, logq_host, fb_host,
+                                          allow_pack);
+    if (rc != LGS_OK && h && h->host_compute) {
+        const std::string keep = h->err;
+        cudaStreamSynchronize(h->host_compute);
+        cudaStreamSynchronize(h->host_copy);
+        cudaGetLastError();
+        h->err = keep;
+    }
+    return rc;
+}
+
+static int klein_host_common_impl(lgs_handle* h, int64_t S, const double* U_host, uint64_t seed, uint64_t first_id,
+                                  int samplez, double* V_host, int64_t* X_host, double* logq_host, int32_t* fb_host,
+                                  bool allow_pack) {
     if (!h) return LGS_E_INVALID;
     if (S < 0) return fail(h, LGS_E_INVALID, "S < 0");
     if (S == 0) return LGS_OK;
@@ -836,6 +878,10 @@ static int klein_host_common(lgs_handle* h, int64_t S, const double* U_host, uin
 
 int lgs_host_widen_i16(const int16_t* src, double* dst, int64_t count, int32_t threads) {
     if (count < 0 || (count > 0 && (!src || !dst)) || threads < 0) return LGS_E_INVALID;
+    if (!host_simd_ok()) {  // no AVX2 on this host: plain loop
+        for (int64_t i = 0; i < count; i++) dst[i] = (double)src[i];
+        return LGS_OK;
+    }
     if (threads <= 1) {
         expand_i16_range(src, dst, (size_t)count);
         return LGS_OK;
@@ -856,16 +902,19 @@ int lgs_host_transport(const lgs_handle* h) {
 
 int lgs_klein_sample_host(lgs_handle* h, int64_t S, uint64_t seed, uint64_t first_sample_id, int samplez,
                           double* V_host, int64_t* X_host, double* logq_host) {
+    LGS_TRACE();
     return klein_host_common(h, S, nullptr, seed, first_sample_id, samplez, V_host, X_host, logq_host, nullptr, true);
 }
 
 int lgs_klein_replay_host(lgs_handle* h, int64_t S, const double* U_host, double* V_host, int64_t* X_host,
                           double* logq_host, int32_t* fallback_count_host) {
+    LGS_TRACE();
     if (S > 0 && !U_host) return fail(h, LGS_E_INVALID, "lgs_klein_replay_host: NULL uniform stream");
     return klein_host_common(h, S, U_host, 0, 0, LGS_SAMPLEZ_TABLE, V_host, X_host, logq_host, fallback_count_host, true);
 }
 
 int lgs_klein_logdensity(lgs_handle* h, int64_t S, const int64_t* X_dev, double* logq_dev, void* stream) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (S < 0 || (S > 0 && (!X_dev || !logq_dev))) return fail(h, LGS_E_INVALID, "lgs_klein_logdensity: bad arguments");
     LGS_CUDA(h, cudaSetDevice(h->device));
@@ -891,6 +940,7 @@ int lgs_klein_logdensity_host(lgs_handle* h, int64_t S, const int64_t* X_host, d
 }
 
 int lgs_imhk_reset(lgs_handle* h, int64_t chains, uint64_t seed, uint64_t first_chain_id) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (chains <= 0) return fail(h, LGS_E_INVALID, "lgs_imhk_reset: chains must be positive");
     LGS_CUDA(h, cudaSetDevice(h->device));
@@ -905,11 +955,15 @@ int lgs_imhk_reset(lgs_handle* h, int64_t chains, uint64_t seed, uint64_t first_
         LGS_CUDA(h, cudaMalloc(&cs.upos, sizeof(int64_t) * chains));
         cs.chains = chains;
     }
-    cs.seed = seed;
+    // IMHK chains draw from their own Philox key: with the plain seed, chain c would start exactly at sample c of a
+    // Klein sampler (and of its own proposal_sampler) created with the same seed, correlating the two arms of the
+    // reference's IMHK-vs-Klein convergence studies at step 0
+    cs.seed = seed ^ 0x494D484B5F4C4753ull;
     cs.first_id = first_chain_id;
     cs.state_path = 0;
     cs.bl_init = false;
     cs.bl_steps = 0;
+    cs.steps_total = 0;
     LGS_CUDA(h, cudaMemset(cs.logw, 0, sizeof(double) * chains));
     LGS_CUDA(h, cudaMemset(cs.cur, 0, sizeof(int32_t) * chains));
     LGS_CUDA(h, cudaMemset(cs.init, 0, sizeof(int32_t) * chains));
@@ -943,6 +997,7 @@ static int imhk_check(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin
 
 int lgs_imhk_run(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int samplez, int weight_mode,
                  double* V_dev, int64_t* X_dev, void* stream) {
+    LGS_TRACE();
     int rc = imhk_check(h, burn_in, keep, thin);
     if (rc) return rc;
     LGS_CUDA(h, cudaSetDevice(h->device));
@@ -955,6 +1010,7 @@ int lgs_imhk_run(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int
         cs.state_path = 2;
         LGS_CUDA(h, launch_imhk_blocked(h->blocked, cs, burn_in, keep, thin, weight_mode, V_dev, X_dev,
                                         (cudaStream_t)stream));
+        cs.steps_total += burn_in + keep * thin;
         return LGS_OK;
     }
     rc = ensure_ordered_chains(h);
@@ -962,12 +1018,14 @@ int lgs_imhk_run(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int
     RngSpec rng{nullptr, 0, h->chains.seed, h->chains.first_id};
     LGS_CUDA(h, launch_imhk_ordered(h->ctx, h->chains, burn_in, keep, thin, rng, samplez, weight_mode, V_dev, X_dev,
                                     nullptr, nullptr, nullptr, (cudaStream_t)stream));
+    cs.steps_total += burn_in + keep * thin;
     return LGS_OK;
 }
 
 int lgs_imhk_replay(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode, const double* U_dev,
                     int64_t stride, double* V_dev, int64_t* X_dev, uint8_t* accept_dev, double* logw_dev,
                     int32_t* fallback_count_dev, void* stream) {
+    LGS_TRACE();
     int rc = imhk_check(h, burn_in, keep, thin);
     if (rc) return rc;
     if (!U_dev) return fail(h, LGS_E_INVALID, "lgs_imhk_replay: NULL uniform stream");
@@ -978,6 +1036,7 @@ int lgs_imhk_replay(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, 
         const ChainReplay rp{U_dev, stride, fallback_count_dev, accept_dev, logw_dev};
         LGS_CUDA(h, launch_imhk_chain(h->blocked, h->chains, burn_in, keep, thin, weight_mode, V_dev, X_dev,
                                       (cudaStream_t)stream, &rp));
+        h->chains.steps_total += burn_in + keep * thin;
         return LGS_OK;
     }
     rc = ensure_ordered_chains(h);
@@ -985,11 +1044,13 @@ int lgs_imhk_replay(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, 
     RngSpec rng{U_dev, stride, 0, 0};
     LGS_CUDA(h, launch_imhk_ordered(h->ctx, h->chains, burn_in, keep, thin, rng, LGS_SAMPLEZ_TABLE, weight_mode, V_dev,
                                     X_dev, accept_dev, logw_dev, fallback_count_dev, (cudaStream_t)stream));
+    h->chains.steps_total += burn_in + keep * thin;
     return LGS_OK;
 }
 
 int lgs_imhk_get_state(lgs_handle* h, int64_t* counts_dev, int64_t* X_dev, double* V_dev, double* logw_dev,
                        void* stream) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
     LGS_CUDA(h, cudaSetDevice(h->device));
@@ -1000,6 +1061,57 @@ int lgs_imhk_get_state(lgs_handle* h, int64_t* counts_dev, int64_t* X_dev, doubl
         return LGS_OK;
     }
     LGS_CUDA(h, launch_imhk_get_state(h->ctx, h->chains, counts_dev, X_dev, V_dev, logw_dev, (cudaStream_t)stream));
+    return LGS_OK;
+}
+
+int64_t lgs_imhk_steps_done(const lgs_handle* h) { return h ? h->chains.steps_total : (int64_t)LGS_E_INVALID; }
+
+int lgs_imhk_set_state(lgs_handle* h, int samplez, const int64_t* X_dev, const double* logw_dev,
+                       const int64_t* counts_dev, int64_t steps_done, void* stream) {
+    LGS_TRACE();
+    if (!h) return LGS_E_INVALID;
+    if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
+    if (!X_dev || !logw_dev || steps_done < 0) return fail(h, LGS_E_INVALID, "lgs_imhk_set_state: bad arguments");
+    if (samplez != LGS_SAMPLEZ_TABLE && samplez != LGS_SAMPLEZ_FAST) return fail(h, LGS_E_INVALID, "imhk: unknown samplez");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    ChainSet& cs = h->chains;
+    const bool want_blocked = samplez == LGS_SAMPLEZ_FAST && h->path != LGS_PATH_ORDERED && h->blocked.ready;
+    if (want_blocked) {
+        if (cs.state_path == 1) return fail(h, LGS_E_STATE, "imhk: this chain set is owned by the ordered kernels; call lgs_imhk_reset()");
+        if (!(h->blocked.use_chain && h->blocked.chain.ready))
+            return fail(h, LGS_E_STATE, "lgs_imhk_set_state: not offered by the LGS_CHAIN=0 development path");
+        LGS_CUDA(h, launch_imhk_chain_set_state(h->blocked, cs, X_dev, logw_dev, counts_dev, steps_done, (cudaStream_t)stream));
+        cs.state_path = 2;
+    } else {
+        int rc = ensure_ordered_chains(h);
+        if (rc) return rc;
+        LGS_CUDA(h, launch_imhk_set_state(h->ctx, cs, X_dev, logw_dev, counts_dev, steps_done, (cudaStream_t)stream));
+    }
+    cs.steps_total = steps_done;
+    return LGS_OK;
+}
+
+int lgs_imhk_set_state_host(lgs_handle* h, int samplez, const int64_t* X_host, const double* logw_host,
+                            const int64_t* counts_host, int64_t steps_done) {
+    if (!h) return LGS_E_INVALID;
+    if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
+    if (!X_host || !logw_host) return fail(h, LGS_E_INVALID, "lgs_imhk_set_state_host: NULL argument");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    const size_t n = h->n;
+    const int64_t C = h->chains.chains;
+    const size_t bX = align256(sizeof(int64_t) * C * n), bw = align256(sizeof(double) * C), bc = align256(sizeof(int64_t) * 2 * C);
+    int rc = ensure_stage(h, bX + bw + bc);
+    if (rc) return rc;
+    uint8_t* p = (uint8_t*)h->stage_dev;
+    int64_t* dX = (int64_t*)p; p += bX;
+    double* dw = (double*)p; p += bw;
+    int64_t* dc = (int64_t*)p;
+    LGS_CUDA(h, cudaMemcpy(dX, X_host, sizeof(int64_t) * C * n, cudaMemcpyHostToDevice));
+    LGS_CUDA(h, cudaMemcpy(dw, logw_host, sizeof(double) * C, cudaMemcpyHostToDevice));
+    if (counts_host) LGS_CUDA(h, cudaMemcpy(dc, counts_host, sizeof(int64_t) * 2 * C, cudaMemcpyHostToDevice));
+    rc = lgs_imhk_set_state(h, samplez, dX, dw, counts_host ? dc : nullptr, steps_done, nullptr);
+    if (rc) return rc;
+    LGS_CUDA(h, cudaDeviceSynchronize());
     return LGS_OK;
 }
 
@@ -1062,6 +1174,7 @@ static int imhk_host_common(lgs_handle* h, int64_t burn_in, int64_t keep, int64_
 
 int lgs_imhk_run_host(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int samplez, int weight_mode,
                       double* V_host, int64_t* X_host) {
+    LGS_TRACE();
     return imhk_host_common(h, burn_in, keep, thin, samplez, weight_mode, nullptr, 0, V_host, X_host, nullptr, nullptr,
                             nullptr);
 }
@@ -1069,12 +1182,14 @@ int lgs_imhk_run_host(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin
 int lgs_imhk_replay_host(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
                          const double* U_host, int64_t stride, double* V_host, int64_t* X_host, uint8_t* accept_host,
                          double* logw_host, int32_t* fallback_count_host) {
+    LGS_TRACE();
     if (!U_host) return h ? fail(h, LGS_E_INVALID, "lgs_imhk_replay_host: NULL uniform stream") : LGS_E_INVALID;
     return imhk_host_common(h, burn_in, keep, thin, LGS_SAMPLEZ_TABLE, weight_mode, U_host, stride, V_host, X_host,
                             accept_host, logw_host, fallback_count_host);
 }
 
 int lgs_imhk_get_state_host(lgs_handle* h, int64_t* counts_host, int64_t* X_host, double* V_host, double* logw_host) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
     LGS_CUDA(h, cudaSetDevice(h->device));
@@ -1099,6 +1214,7 @@ int lgs_imhk_get_state_host(lgs_handle* h, int64_t* counts_host, int64_t* X_host
 }
 
 int lgs_imhk_counts_host(lgs_handle* h, int64_t* accepted, int64_t* total) {
+    LGS_TRACE();
     if (!h || !accepted || !total) return LGS_E_INVALID;
     if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
     LGS_CUDA(h, cudaSetDevice(h->device));
@@ -1127,25 +1243,22 @@ int lgs_profile_read(lgs_handle* h, double* ms_by_class, int64_t* launches_by_cl
 
 int lgs_histogram(lgs_handle* h, const double* V_dev, int64_t S, const int32_t* dims_host, int32_t n_dims, double lo,
                   double width, int32_t nbins, int64_t* hist_dev, void* stream) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (!V_dev || !dims_host || !hist_dev || n_dims <= 0 || nbins <= 0 || !(width > 0.0))
         return fail(h, LGS_E_INVALID, "lgs_histogram: bad arguments");
     for (int i = 0; i < n_dims; i++)
         if (dims_host[i] < 0 || dims_host[i] >= h->n) return fail(h, LGS_E_INVALID, "lgs_histogram: dim out of range");
-    if (n_dims > 256) return fail(h, LGS_E_INVALID, "lgs_histogram: at most 256 tracked coordinates");
     LGS_CUDA(h, cudaSetDevice(h->device));
-    if (!h->hist_dims) LGS_CUDA(h, cudaMalloc(&h->hist_dims, sizeof(int32_t) * 256));
-    // stream-ordered, no host synchronisation: the tiny pageable copy is staged by the driver before it returns
-    LGS_CUDA(h, cudaMemcpyAsync(h->hist_dims, dims_host, sizeof(int32_t) * n_dims, cudaMemcpyHostToDevice,
-                                (cudaStream_t)stream));
-    LGS_CUDA(h, launch_histogram(h->ctx, V_dev, S, h->hist_dims, n_dims, lo, width, nbins, hist_dev,
-                                 (cudaStream_t)stream));
+    // the tracked coordinates go to the kernels by value (256 per launch): nothing per-handle is written here
+    LGS_CUDA(h, launch_histogram(h->ctx, V_dev, S, dims_host, n_dims, lo, width, nbins, hist_dev, (cudaStream_t)stream));
     return LGS_OK;
 }
 
 int lgs_chain_diagnostics(lgs_handle* h, const double* V_dev, int64_t chains, int64_t keep, const int32_t* dims_host,
                           int32_t n_dims, double c_window, int32_t max_lag, double* stats_dev, double* acf_dev,
                           int32_t acf_len, void* stream) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (!V_dev || !dims_host || !stats_dev || chains <= 0 || keep < 2 || n_dims <= 0 || n_dims > 256 || !(c_window > 0.0))
         return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics: bad arguments (need keep >= 2, 1 <= n_dims <= 256)");
@@ -1175,6 +1288,7 @@ int lgs_chain_diagnostics(lgs_handle* h, const double* V_dev, int64_t chains, in
 
 int lgs_gelman_rubin_sums(lgs_handle* h, const double* stats_dev, int64_t chains, int32_t n_dims, double* sums_dev,
                           void* stream) {
+    LGS_TRACE();
     if (!h) return LGS_E_INVALID;
     if (!stats_dev || !sums_dev || chains <= 0 || n_dims <= 0) return fail(h, LGS_E_INVALID, "lgs_gelman_rubin_sums: bad arguments");
     LGS_CUDA(h, cudaSetDevice(h->device));

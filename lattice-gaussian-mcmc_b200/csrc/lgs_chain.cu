@@ -1060,6 +1060,26 @@ export_coeffs_tiled_kernel(const double* __restrict__ Xt, int npad, int n, int64
     }
 }
 
+// int64 [S][n] row-major -> tiled workspace (the inverse of export_coeffs_tiled_kernel); padding coordinates untouched
+__global__ void __launch_bounds__(256)
+import_coeffs_tiled_kernel(const int64_t* __restrict__ in, int64_t ldi, int npad, int n, int64_t S, double* __restrict__ Xt) {
+    __shared__ double tile[32][33];
+    const int64_t s0 = (int64_t)blockIdx.x * 32;
+    const int i0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) {
+        const int64_t s = s0 + r;
+        const int i = i0 + tx;
+        tile[tx][r] = (s < S && i < n) ? (double)in[(size_t)s * ldi + i] : 0.0;
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int i = i0 + r;
+        const int64_t s = s0 + tx;
+        if (i < n && s < S) Xt[((size_t)(s >> 7) * npad + i) * kRowLd + (s & 127)] = tile[r][tx];
+    }
+}
+
 __global__ void chain_finish_logq_kernel(const double* __restrict__ lp, double sum_lognorm, int64_t S,
                                          double* __restrict__ logq) {
     int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1488,6 +1508,27 @@ cudaError_t launch_imhk_chain_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* c
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
     }
+    return cudaSuccess;
+}
+
+// lgs_imhk_set_state on the chain kernel's state: coefficients into the tiled current-state matrix, every chain's
+// location = Xcur, log-weights and counters as given, `steps_done` = the Philox stream index the run continues from
+cudaError_t launch_imhk_chain_set_state(BlockedCtx& bc, ChainSet& cs, const int64_t* X, const double* logw,
+                                        const int64_t* counts, int64_t steps_done, cudaStream_t st) {
+    cudaError_t e;
+    if ((e = chain_ensure_chains(bc, cs)) != cudaSuccess) return e;
+    const int64_t C = cs.chains;
+    const int n = bc.n;
+    dim3 grid((unsigned)((C + 31) / 32), (unsigned)((n + 31) / 32));
+    import_coeffs_tiled_kernel<<<grid, 256, 0, st>>>(X, n, bc.chain.npad, n, C, cs.Xcur);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(cs.flags, 0, (size_t)cs.bl_cap, st)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyAsync(cs.logw, logw, sizeof(double) * C, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
+    if (counts) e = cudaMemcpyAsync(cs.counts, counts, sizeof(int64_t) * 2 * C, cudaMemcpyDeviceToDevice, st);
+    else e = cudaMemsetAsync(cs.counts, 0, sizeof(int64_t) * 2 * C, st);
+    if (e != cudaSuccess) return e;
+    cs.bl_steps = steps_done;
+    cs.bl_init = true;
     return cudaSuccess;
 }
 

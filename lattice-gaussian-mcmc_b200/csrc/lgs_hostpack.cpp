@@ -74,6 +74,11 @@ struct HostPool {
     }
 };
 
+bool host_simd_ok() {
+    static const bool ok = __builtin_cpu_supports("avx2");
+    return ok;
+}
+
 // LGS_HOST_THREADS, else the CPUs this process may run on divided by the ranks sharing the host (LOCAL_WORLD_SIZE of
 // torchrun): every rank of a multi-GPU job brings its own pool, and the pool threads spin on completion words
 int hostpool_default_threads() {

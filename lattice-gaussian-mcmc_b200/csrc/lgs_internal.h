@@ -40,6 +40,7 @@ struct ChainSet {
     int64_t bl_cap = 0;
     int64_t bl_steps = 0;         // steps performed so far by every chain (Philox stream index)
     bool bl_init = false;
+    int64_t steps_total = 0;      // host mirror, both paths: Metropolis-Hastings steps every chain has performed
 };
 
 // ---- blocked (DMMA) path -------------------------------------------------------------------------------
@@ -220,7 +221,10 @@ cudaError_t launch_imhk_ordered(const DeviceCtx& ctx, ChainSet& cs, int64_t burn
                                 uint8_t* accept, double* logw_out, int32_t* fallback, cudaStream_t st);
 cudaError_t launch_imhk_get_state(const DeviceCtx& ctx, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
                                   double* logw, cudaStream_t st);
-cudaError_t launch_histogram(const DeviceCtx& ctx, const double* V, int64_t S, const int32_t* dims_dev, int n_dims,
+cudaError_t launch_imhk_set_state(const DeviceCtx& ctx, ChainSet& cs, const int64_t* X, const double* logw,
+                                  const int64_t* counts, int64_t steps_done, cudaStream_t st);
+constexpr int kHistChunk = 256;  // tracked coordinates per histogram launch (passed by value as a kernel parameter)
+cudaError_t launch_histogram(const DeviceCtx& ctx, const double* V, int64_t S, const int32_t* dims_host, int n_dims,
                              double lo, double width, int nbins, int64_t* hist, cudaStream_t st);
 cudaError_t launch_reduce_counts(const ChainSet& cs, int64_t* out2, cudaStream_t st);
 
@@ -272,5 +276,7 @@ cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int
                               double* V, int64_t* X, cudaStream_t st, const ChainReplay* rp = nullptr);
 cudaError_t launch_imhk_chain_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
                                         double* logw, cudaStream_t st);
+cudaError_t launch_imhk_chain_set_state(BlockedCtx& bc, ChainSet& cs, const int64_t* X, const double* logw,
+                                        const int64_t* counts, int64_t steps_done, cudaStream_t st);
 
 }  // namespace lgs

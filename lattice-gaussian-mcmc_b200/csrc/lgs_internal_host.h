@@ -6,6 +6,7 @@
 
 namespace lgs {
 
+bool host_simd_ok();                     // the CPU has AVX2 (the widening / non-temporal copy loops use it)
 struct HostPool;
 int hostpool_default_threads();          // LGS_HOST_THREADS, else usable CPUs / LOCAL_WORLD_SIZE
 HostPool* hostpool_create(int threads);  // threads <= 0: hostpool_default_threads()

@@ -214,6 +214,24 @@ __global__ void imhk_get_state_kernel(DeviceCtx ctx, ChainSet cs, int64_t* __res
     if (V) for (int i = 0; i < n; i++) V[ch * n + i] = cs.Vbuf[cur * bufsz + (size_t)i * cs.chains + ch];
 }
 
+// lgs_imhk_set_state for the ordered kernels' state: coefficients into buffer 0, its lattice point recomputed
+// (klein.py:218), log-weight / counters / step index as given
+__global__ void imhk_set_state_kernel(DeviceCtx ctx, ChainSet cs, const int64_t* __restrict__ X,
+                                      const double* __restrict__ logw, const int64_t* __restrict__ counts,
+                                      int64_t steps_done) {
+    int64_t ch = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (ch >= cs.chains) return;
+    const int n = ctx.n;
+    for (int i = 0; i < n; i++) cs.Xbuf[(size_t)i * cs.chains + ch] = (double)X[ch * n + i];
+    lattice_point(ctx, cs.Xbuf, cs.Vbuf, cs.chains, ch);
+    cs.cur[ch] = 0;
+    cs.init[ch] = 1;
+    cs.logw[ch] = logw[ch];
+    cs.counts[ch * 2] = counts ? counts[ch * 2] : 0;
+    cs.counts[ch * 2 + 1] = counts ? counts[ch * 2 + 1] : 0;
+    cs.step_no[ch] = steps_done;
+}
+
 __global__ void reduce_counts_kernel(const int64_t* __restrict__ counts, int64_t chains, unsigned long long* out2) {
     unsigned long long a = 0, t = 0;
     for (int64_t ch = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; ch < chains; ch += (int64_t)gridDim.x * blockDim.x) {
@@ -230,9 +248,16 @@ __global__ void reduce_counts_kernel(const int64_t* __restrict__ counts, int64_t
     }
 }
 
-// compute_tvd's per-coordinate histograms (convergence_diag.py:15-72) on device-resident samples:
-// block-private shared-memory bins, one global atomic per bin per block.
-__global__ void histogram_kernel(const double* __restrict__ V, int64_t S, int n, const int32_t* __restrict__ dims,
+// compute_tvd's per-coordinate histograms (convergence_diag.py:15-72) on device-resident samples.  The tracked
+// coordinates travel BY VALUE as a kernel parameter (up to 256 per launch): no per-handle device buffer, so calls on
+// different streams cannot race on it.  Two variants: block-private shared-memory bins with one global atomic per bin
+// and block (n_dims * nbins * 4 <= 160 KB), or global atomics straight into the int64 bins (any size; the bins of a
+// 1024-dim marginal histogram over +-1500 are 25 MB and live in L2).
+struct HistDims {
+    int32_t d[kHistChunk];
+};
+
+__global__ void histogram_kernel(const double* __restrict__ V, int64_t S, int n, const __grid_constant__ HistDims dims,
                                  int n_dims, double lo, double inv_width, int nbins, unsigned long long* hist) {
     extern __shared__ unsigned int sbins[];
     const int total = n_dims * nbins;
@@ -241,7 +266,7 @@ __global__ void histogram_kernel(const double* __restrict__ V, int64_t S, int n,
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < S * n_dims; e += (int64_t)gridDim.x * blockDim.x) {
         int64_t s = e / n_dims;
         int d = (int)(e - s * n_dims);
-        double v = V[s * n + dims[d]];
+        double v = V[s * n + dims.d[d]];
         double b = floor((v - lo) * inv_width);
         int bi = b < 0.0 ? 0 : (b >= (double)nbins ? nbins - 1 : (int)b);
         atomicAdd(&sbins[d * nbins + bi], 1u);
@@ -249,6 +274,19 @@ __global__ void histogram_kernel(const double* __restrict__ V, int64_t S, int n,
     __syncthreads();
     for (int i = threadIdx.x; i < total; i += blockDim.x)
         if (sbins[i]) atomicAdd(&hist[i], (unsigned long long)sbins[i]);
+}
+
+__global__ void histogram_global_kernel(const double* __restrict__ V, int64_t S, int n,
+                                        const __grid_constant__ HistDims dims, int n_dims, double lo, double inv_width,
+                                        int nbins, unsigned long long* hist) {
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < S * n_dims; e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t s = e / n_dims;
+        int d = (int)(e - s * n_dims);
+        double v = V[s * n + dims.d[d]];
+        double b = floor((v - lo) * inv_width);
+        int bi = b < 0.0 ? 0 : (b >= (double)nbins ? nbins - 1 : (int)b);
+        atomicAdd(&hist[(size_t)d * nbins + bi], 1ull);
+    }
 }
 
 }  // namespace
@@ -298,6 +336,14 @@ cudaError_t launch_imhk_get_state(const DeviceCtx& ctx, ChainSet& cs, int64_t* c
     return cudaGetLastError();
 }
 
+cudaError_t launch_imhk_set_state(const DeviceCtx& ctx, ChainSet& cs, const int64_t* X, const double* logw,
+                                  const int64_t* counts, int64_t steps_done, cudaStream_t st) {
+    if (cs.chains <= 0) return cudaSuccess;
+    int blocks = (int)((cs.chains + 127) / 128);
+    imhk_set_state_kernel<<<blocks, 128, 0, st>>>(ctx, cs, X, logw, counts, steps_done);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_reduce_counts(const ChainSet& cs, int64_t* out2, cudaStream_t st) {
     cudaError_t e = cudaMemsetAsync(out2, 0, 2 * sizeof(int64_t), st);
     if (e != cudaSuccess) return e;
@@ -308,21 +354,31 @@ cudaError_t launch_reduce_counts(const ChainSet& cs, int64_t* out2, cudaStream_t
     return cudaGetLastError();
 }
 
-cudaError_t launch_histogram(const DeviceCtx& ctx, const double* V, int64_t S, const int32_t* dims_dev, int n_dims,
+cudaError_t launch_histogram(const DeviceCtx& ctx, const double* V, int64_t S, const int32_t* dims_host, int n_dims,
                              double lo, double width, int nbins, int64_t* hist, cudaStream_t st) {
     if (S <= 0 || n_dims <= 0) return cudaSuccess;
-    size_t smem = sizeof(unsigned int) * (size_t)n_dims * nbins;
-    if (smem > 160 * 1024) return cudaErrorInvalidValue;
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(histogram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    for (int d0 = 0; d0 < n_dims; d0 += kHistChunk) {
+        const int nd = n_dims - d0 < kHistChunk ? n_dims - d0 : kHistChunk;
+        HistDims hd{};
+        for (int i = 0; i < nd; i++) hd.d[i] = dims_host[d0 + i];
+        unsigned long long* out = (unsigned long long*)hist + (size_t)d0 * nbins;
+        const size_t smem = sizeof(unsigned int) * (size_t)nd * nbins;
+        const int64_t work = S * nd;
+        int blocks = (int)((work + 255) / 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        if (smem <= 160 * 1024) {
+            if (smem > 48 * 1024) {
+                cudaError_t e = cudaFuncSetAttribute(histogram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return e;
+            }
+            histogram_kernel<<<blocks, 256, smem, st>>>(V, S, ctx.n, hd, nd, lo, 1.0 / width, nbins, out);
+        } else {
+            histogram_global_kernel<<<blocks * 2, 256, 0, st>>>(V, S, ctx.n, hd, nd, lo, 1.0 / width, nbins, out);
+        }
+        cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
-    int64_t work = S * n_dims;
-    int blocks = (int)((work + 255) / 256);
-    if (blocks > 148 * 8) blocks = 148 * 8;
-    histogram_kernel<<<blocks, 256, smem, st>>>(V, S, ctx.n, dims_dev, n_dims, lo, 1.0 / width, nbins,
-                                                (unsigned long long*)hist);
-    return cudaGetLastError();
+    return cudaSuccess;
 }
 
 }  // namespace lgs

@@ -461,10 +461,18 @@ int reduce_entry(i64* rows, int n, int m, double delta, double eta, int beta, in
 
 }  // namespace
 
+// this file is compiled with -mfma (std::fma must be the single-rounding hardware instruction for the exact products
+// and the double-double arithmetic): refuse to run, instead of dying with SIGILL, on a host without it
+static bool host_has_fma() {
+    static const bool ok = __builtin_cpu_supports("fma");
+    return ok;
+}
+
 extern "C" {
 
 int lgs_lll_reduce(int64_t* rows, int32_t n, int32_t m, double delta, double eta, int32_t precision, int64_t* U,
                    int64_t* stats) {
+    if (!host_has_fma()) return LGS_E_PRECISION;
     try {
         return reduce_entry(rows, n, m, delta, eta, 0, 0, 0, precision, U, stats);
     } catch (...) {  // std::bad_alloc from the work arrays: nothing throws across the ABI
@@ -475,6 +483,7 @@ int lgs_lll_reduce(int64_t* rows, int32_t n, int32_t m, double delta, double eta
 int lgs_bkz_reduce(int64_t* rows, int32_t n, int32_t m, int32_t block_size, double delta, int32_t max_tours,
                    int32_t prune, int32_t precision, int64_t* U, int64_t* stats) {
     if (block_size < 2) return LGS_E_INVALID;
+    if (!host_has_fma()) return LGS_E_PRECISION;
     if (prune < 0) prune = block_size > 32 ? 1 : 0;
     try {
         return reduce_entry(rows, n, m, delta, 0.501, block_size, max_tours, prune, precision, U, stats);
@@ -485,6 +494,7 @@ int lgs_bkz_reduce(int64_t* rows, int32_t n, int32_t m, int32_t block_size, doub
 
 int lgs_gso_norms(const int64_t* rows, int32_t n, int32_t m, double* norms) {
     if (!rows || !norms || n <= 0 || m < n) return LGS_E_INVALID;
+    if (!host_has_fma()) return LGS_E_PRECISION;
     try {
         Reducer<dd> red(rows, n, m, nullptr, 0.99, 0.501);
         if (red.status) return red.status;

@@ -184,6 +184,24 @@ class IMHKSampler(DiscreteGaussianSampler):
         s = self._state(3)
         return None if s is None else (float(s) if self.n_chains == 1 else s)
 
+    def get_state(self) -> dict:
+        """Checkpoint: everything a new IMHKSampler on the same lattice / sigma needs to continue these chains
+        (the reference's current_coeffs / current_log_weight / counters, imhk.py:54-61, for every chain, plus the
+        Philox stream position)."""
+        if not self._initialized:
+            raise RuntimeError("the chains have no state yet")
+        counts, X, _, lw = self._engine.imhk_state()
+        return {"coeffs": X, "log_weight": lw, "counts": counts, "steps_done": self._engine.imhk_steps_done(),
+                "n_chains": self.n_chains}
+
+    def set_state(self, state: dict) -> None:
+        """Resume from get_state(): with the same seed and first_chain_id the run continues the uninterrupted one."""
+        if int(state["n_chains"]) != self.n_chains:
+            raise ValueError("state was taken from a different number of chains")
+        self._engine.imhk_set_state(state["coeffs"], state["log_weight"], state["counts"], state["steps_done"],
+                                    self.proposal_sampler.samplez)
+        self._initialized = True
+
     # ------------------------------------------------------------------ imhk.py:252-313
     def estimate_spectral_gap(self, num_samples: int = 1000) -> float:
         V, X, lq = self.proposal_sampler.sample_with_coefficients(num_samples)

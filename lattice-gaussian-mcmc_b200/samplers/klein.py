@@ -48,8 +48,10 @@ class RefinedKleinSampler(DiscreteGaussianSampler):
         self._validate_klein_parameters()
         self._log_2pi = np.log(2 * np.pi)
         self._log_sigma = np.log(self.sigma)
+        self._engine_kwargs = dict(max_range=max_range, device=device, path=path)
+        self._alt_engines = {}           # precision -> Engine, for adaptive_precision_sample
         self._engine = Engine(self.R, self._basis, self.center_transformed, self.center, self.sigma,
-                              precision=precision, max_range=max_range, device=device, path=path)
+                              precision=precision, **self._engine_kwargs)
         self._next_sample_id = 0
         self._uniforms = None if uniforms is None else np.ascontiguousarray(uniforms, dtype=np.float64).ravel()
         self._upos = 0
@@ -128,9 +130,28 @@ class RefinedKleinSampler(DiscreteGaussianSampler):
         return self._draw(int(num_samples), True, True, True)
 
     def adaptive_precision_sample(self, target_distance: Optional[float] = None) -> np.ndarray:
-        # klein.py:273-302 changes the table window for one draw; the window only matters beyond 10 sigma_i,
-        # so the device sampler keeps the constructor's precision
-        return self.sample_single()
+        """klein.py:273-302: one draw with the table window (`precision`, in conditional sigmas) doubled (>= 20) for
+        a target closer than sigma, halved (>= 5) for one further than 5 sigma.  The window is a per-handle constant on
+        the device, so the draw comes from a second handle built for that precision (created on first use, kept)."""
+        if target_distance is None:
+            return self.sample_single()
+        relative_distance = target_distance / self.sigma
+        precision = self.precision
+        if relative_distance < 1:
+            precision = max(20, 2 * self.precision)
+        elif relative_distance > 5:
+            precision = max(5, self.precision // 2)
+        if precision == self.precision:
+            return self.sample_single()
+        main = self._engine
+        if precision not in self._alt_engines:
+            self._alt_engines[precision] = Engine(self.R, self._basis, self.center_transformed, self.center, self.sigma,
+                                                  precision=precision, **self._engine_kwargs)
+        try:
+            self._engine = self._alt_engines[precision]
+            return self.sample_single()
+        finally:
+            self._engine = main
 
     # ------------------------------------------------------------------ density (klein.py:222-271)
     def compute_log_density(self, point: np.ndarray) -> float:

@@ -112,8 +112,10 @@ def _run(kind, basis, sigma, procs, count, seed, thin=1):
     if procs == 1:
         res = [_worker(jobs[0])]
     else:
-        ctx = mp.get_context("fork")
-        with ctx.Pool(procs) as pool:                      # dimension_scaling.py:841-845
+        # dimension_scaling.py:841-845 uses Pool(n) (fork); here the parent may hold CUDA / OpenMP threads, so the
+        # workers are spawned: same processes, same seeding, and the timed region lies inside the worker
+        ctx = mp.get_context("spawn")
+        with ctx.Pool(procs) as pool:
             res = pool.map(_worker, jobs)
     wall = time.perf_counter() - t0
     units = sum(r[0] for r in res)

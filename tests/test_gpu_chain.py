@@ -125,3 +125,54 @@ def test_chain_imhk_equals_v1_at_full_dimension(lgs):
     assert np.array_equal(Va, Vb)
     assert np.array_equal(a.current_coeffs, b.current_coeffs)
     assert a.total_proposals == b.total_proposals == 300 * 6
+
+
+def test_imhk_checkpoint_resume_reproduces_the_uninterrupted_run(lgs):
+    """get_state -> destroy -> create -> set_state -> continue == one uninterrupted run (imhk.py:59-61: the reference's
+    chain state is three assignable attributes; with counter-based Philox the resume point is (x, log w, counts, step))"""
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(96, seed=3)
+    for weight, sigma in (("reference", 1.5 * lat.max_gram_schmidt_norm), ("exact", 0.45 * lat.max_gram_schmidt_norm)):
+        chains = 300
+        whole = lgs.IMHKSampler(lat, sigma, burn_in=0, n_chains=chains, seed=9, weight_mode=weight, first_chain_id=1000)
+        Xw = whole.sample_coefficients(6, thin=3, burn_in=4)                  # 22 steps
+        first = lgs.IMHKSampler(lat, sigma, burn_in=0, n_chains=chains, seed=9, weight_mode=weight, first_chain_id=1000)
+        Xa = first.sample_coefficients(2, thin=3, burn_in=4)                  # 10 steps
+        state = first.get_state()
+        assert state["steps_done"] == 10
+        del first
+        second = lgs.IMHKSampler(lat, sigma, burn_in=0, n_chains=chains, seed=9, weight_mode=weight, first_chain_id=1000)
+        second.set_state(state)
+        assert np.array_equal(second.current_coeffs, state["coeffs"])
+        Xb = second.sample_coefficients(4, thin=3)                           # 12 more
+        assert np.array_equal(np.concatenate([Xa, Xb], axis=1), Xw)
+        assert second.total_proposals == whole.total_proposals == chains * 22
+        assert second.accepted_proposals == whole.accepted_proposals
+        if weight == "exact":
+            assert 0.05 < whole.acceptance_rate < 0.999
+        assert np.allclose(second.current_log_weight, whole.current_log_weight, rtol=0, atol=0)
+    # the ordered kernels take a state too (table SampleZ, native RNG)
+    lat = dd_lattice(12, seed=1)
+    kw = dict(burn_in=0, n_chains=40, seed=4, samplez="table", path="ordered")
+    whole = lgs.IMHKSampler(lat, 30.0, **kw)
+    Xw = whole.sample_coefficients(5, thin=2)
+    first = lgs.IMHKSampler(lat, 30.0, **kw)
+    Xa = first.sample_coefficients(2, thin=2)
+    st = first.get_state()
+    second = lgs.IMHKSampler(lat, 30.0, **kw)
+    second.set_state(st)
+    Xb = second.sample_coefficients(3, thin=2)
+    assert np.array_equal(np.concatenate([Xa, Xb], axis=1), Xw)
+
+
+def test_adaptive_precision_sample_uses_the_requested_window(lgs):
+    """klein.py:273-302: a target further than 5 sigma halves the window (precision 10 -> 5): draws beyond 5 sigma_i
+    can no longer occur; without a target the constructor's window is used"""
+    lat = lgs.SimpleLattice(np.eye(1))
+    smp = lgs.KleinSampler(lat, 1.0, seed=3, samplez="table", path="ordered")
+    assert smp.adaptive_precision_sample().shape == (1,)
+    x = np.array([smp.adaptive_precision_sample(target_distance=100.0)[0] for _ in range(50)])
+    assert np.all(np.abs(x) <= 5)
+    assert 5 in smp._alt_engines and smp._engine is not smp._alt_engines[5]
+    y = smp.adaptive_precision_sample(target_distance=0.5)
+    assert 20 in smp._alt_engines and y.shape == (1,)

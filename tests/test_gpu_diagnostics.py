@@ -127,3 +127,35 @@ def test_device_tvd_matches_the_reference_golden(lgs):
     same, wider = D.device_tvd(s5, V[0], V[1]), D.device_tvd(s5, V[0], V[2])
     assert same == pytest.approx(D.compute_tvd(V[0].cpu().numpy(), V[1].cpu().numpy()), abs=1e-14)
     assert same < 0.03 < 0.1 < wider
+
+
+def test_device_tvd_default_call_at_the_headline_dimension(lgs):
+    """compute_tvd's default -- every coordinate, exact-value counting (convergence_diag.py:15-72) -- on device-resident
+    NTRU-512 samples: 1024 marginals over a range of ~3000 integers (the shared-memory histogram alone
+    could hold 13 of them).  Must equal the host function on the same arrays."""
+    import torch
+    from lattice_gaussian_mcmc_b200.diagnostics import compute_tvd, device_tvd
+    from lattice_gaussian_mcmc_b200.ntru import ntru_lattice
+    lat = ntru_lattice(512, 12289, seed=0)
+    smp = lgs.KleinSampler(lat, 165.74, seed=1, path="blocked")
+    S = 3000
+    Va = torch.empty((S, 1024), dtype=torch.float64, device="cuda")
+    Vb = torch.empty((S, 1024), dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    smp._engine.klein_sample_dev(S, 1, 0, "fast", V=Va.data_ptr(), stream=st)
+    smp._engine.klein_sample_dev(S, 2, 0, "fast", V=Vb.data_ptr(), stream=st)
+    got = device_tvd(smp, Va, Vb)
+    want = compute_tvd(Va.cpu().numpy(), Vb.cpu().numpy())
+    assert abs(got - want) < 1e-12, (got, want)
+    assert 0.3 < got < 1.0          # 3000 samples over ~1000 occupied values per marginal: mostly sampling noise
+    # a subset of coordinates through the shared-memory variant, more than 256 through the chunked one
+    dims = np.arange(0, 1024, 3)
+    got2 = device_tvd(smp, Va, Vb, dims=dims)
+    want2 = compute_tvd(Va.cpu().numpy()[:, dims], Vb.cpu().numpy()[:, dims])
+    assert abs(got2 - want2) < 1e-12
+    # histogram accumulation with few bins and many coordinates: 300 tracked dims x 16 bins
+    from lattice_gaussian_mcmc_b200.distributed import host_histogram
+    dims3 = np.arange(300, dtype=np.int32)
+    hist = torch.zeros((300, 16), dtype=torch.int64, device="cuda")
+    smp._engine.histogram_dev(Va.data_ptr(), S, dims3, -800.0, 100.0, 16, hist.data_ptr(), stream=st)
+    assert torch.equal(hist.cpu(), host_histogram(Va.cpu(), dims3, -800.0, 100.0, 16))

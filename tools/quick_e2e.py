@@ -38,13 +38,17 @@ print(f"n={n} S={S} host call {dt*1e3:.2f} ms = {S/dt/1e6:.2f} M samples/s | cha
       f" | env pack={os.environ.get('LGS_HOST_PACK')} zc={os.environ.get('LGS_HOST_ZEROCOPY')} threads={os.environ.get('LGS_HOST_THREADS')}")
 
 # the user-facing call: KleinSampler.sample(S) returns a FRESH pageable float64 array (klein.py:322)
-for _ in range(2):
-    smp.sample(S)
-t0 = time.perf_counter()
-for r in range(3):
-    out = smp.sample(S)
-dt = (time.perf_counter() - t0) / 3
-print(f"KleinSampler.sample({S}) -> {out.shape} {out.dtype}: {dt*1e3:.2f} ms = {S/dt/1e6:.2f} M samples/s (fresh pageable array per call)")
+for huge in ("1", "0"):
+    os.environ["LGS_FRESH_HUGEPAGE"] = huge
+    for _ in range(2):
+        smp.sample(S)
+    t0 = time.perf_counter()
+    for r in range(3):
+        out = smp.sample(S)
+    dt = (time.perf_counter() - t0) / 3
+    print(f"KleinSampler.sample({S}) -> {out.shape} {out.dtype}: {dt*1e3:.2f} ms = {S/dt/1e6:.2f} M samples/s "
+          f"(fresh pageable array per call, MADV_HUGEPAGE mapping = {huge})")
+    del out
 buf = np.empty((S, n))
 for _ in range(2):
     smp.sample(S, out=buf)
