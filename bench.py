@@ -61,6 +61,15 @@ def ncu_traffic():
     return None, None
 
 
+_T0 = time.perf_counter()
+
+
+def phase(name):
+    """wall-clock trace of the run on stderr (the JSON line on stdout stays alone)"""
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(f"[bench +{time.perf_counter() - _T0:7.1f} s] {name}", file=sys.stderr, flush=True)
+
+
 def imhk_flop(thin):                             # proposal back-substitution + two quadratic forms + kept point / thin
     return DIM * (DIM - 1) + 6 * DIM + 2 * DIM * DIM / thin
 
@@ -188,7 +197,9 @@ def run_reference(args, rank, world):
     import __graft_entry__ as g
     g.build_oracle()               # the checker only: this arm never loads the product library
     from oracle import oracle
+    phase("oracle built")
     lat = build_lattice()
+    phase("lattice (NTRUSolve)")
     cores = os.cpu_count() or 1
     prob = oracle.Problem(lat.basis, SIGMA)
     S = 2048 * cores                                                   # bounded sample per step (~3 s on 16 cores)
@@ -199,11 +210,15 @@ def run_reference(args, rank, world):
         oracle.klein_seeded(prob, S, seed=200 + k, chains=cores, want_v=True, threads=cores)
     dt = time.perf_counter() - t0
     val = S * args.steps / dt
+    phase("port: klein steps")
     steps_imhk = 4
     t1 = time.perf_counter()
     oracle.imhk_seeded(prob, cores, steps_imhk, seed=5, threads=cores)
     dti = time.perf_counter() - t1
     imhk_val = cores * (steps_imhk + 1) / dti
+    phase("port: imhk")
+    refpy = reference_python_leg(lat)
+    phase("reference python legs")
     line = {"impl": "reference", "metric": "klein_samples_per_s", "value": val, "unit": "samples/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -211,7 +226,7 @@ def run_reference(args, rank, world):
                        "sample_of": "the same lattice, sigma and sampler as the GPU arm; a bounded sample per step"},
             "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port",
                              "sample": f"{S} samples per step x {args.steps} steps, {cores} OpenMP threads",
-                             "reference_python": reference_python_leg(lat)},
+                             "reference_python": refpy},
             "host": host_info(),
             "imhk": {"value": imhk_val, "unit": "chain-steps/s", "sample": f"{cores} chains x {steps_imhk} steps"},
             "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -257,7 +272,9 @@ def main():
     W = max(args.warmup, 3)
     K = args.steps
     n = DIM
+    phase("built / loaded the library")
     lat = build_lattice()
+    phase("lattice (NTRUSolve)")
     smp = lgs.KleinSampler(lat, SIGMA, seed=2026, device=local, path="blocked")
     eng = smp._engine
     S = args.samples or eng.preferred_batch
@@ -296,9 +313,11 @@ def main():
         gid = ((base + k) * world + rank) * S           # global sample ids: disjoint per (step, rank)
         eng.klein_sample_dev(S, smp.seed, gid, "fast", V=V.data_ptr(), stream=stream)
 
+    phase("sampler created")
     for w in range(W):
         klein_step(w, base=10_000)
     ms_klein = timed(klein_step, K)
+    phase("klein leg")
     klein_rate = world * S * K / (ms_klein * 1e-3)
 
     # per-kernel-class device time of the same K steps (events around every launch; separate pass so that the
@@ -352,10 +371,12 @@ def main():
                 dist.all_reduce(dt, op=dist.ReduceOp.MAX)
             return float(dt.item())
 
+        phase("pinned host buffer")
         for w in range(2):
             host_step(w, base=40_000)
         Ke = max(2, (K + BATCHES - 1) // BATCHES)         # the same number of batches as K single-batch steps
         dt = wall(host_step, Ke)
+        phase("e2e leg")
         transport = int(eng._lib.lgs_host_transport(eng._h))
         tname = {0: "fp64 copies", 1: "int16 pack kernel + chunked copies, widened to float64 by the host pool",
                  2: "int16 written by the chain kernel's lattice-point epilogue (HBM), shipped group by group by the "
@@ -391,6 +412,7 @@ def main():
                "note": "the sampler's only inputs are (seed, first id) scalars; every step delivers its S x n float64 "
                        "lattice points (the reference's return array) into host memory; for this integer basis they "
                        "cross PCIe as int16, bit-identical after widening"}
+        phase("host store peak")
         del Vh, src16, dst64
         # the reference-shaped call: KleinSampler.sample(S) returns a FRESH float64 array every time (klein.py:322)
         def fresh_step(k):
@@ -406,6 +428,7 @@ def main():
                                             "return contract; 2 MB-aligned anonymous mapping + MADV_HUGEPAGE, first "
                                             "touched by the widening pool)", "calls": Kf}
         e2e["host"] = host_info()
+        phase("e2e fresh-array leg")
 
     # ---------------------------------------------------------------- IMHK leg
     imhk = imhk_exact = None
@@ -454,10 +477,12 @@ def main():
                     "hist_total": int(res["hist"].sum().item())}
 
         imhk = imhk_leg("reference", K)
+        phase("imhk leg")
         # the Wang-Ling weights (LGS_WEIGHT_EXACT): normalisers accumulated, exp + accept draw per step.  At this
         # lattice's sigma_i >= 1.29 the normalisers are constant to ~1e-13, so the acceptance rate stays 1 - O(1e-13);
         # tools/quick_imhk.py runs the same mode where it rejects (sigma = 60: sigma_i ~ 0.5)
         imhk_exact = imhk_leg("exact", max(3, K // 2))
+        phase("imhk exact leg")
 
     # ---------------------------------------------------------------- replay through the same kernel (parity mode)
     replay = None
@@ -498,10 +523,12 @@ def main():
     if not (invariance["all_ranks_equal"] and invariance["sum_of_rank_slices_equals_full"]):
         raise SystemExit(f"rank-count invariance violated: {invariance}")
 
+    phase("replay + invariance")
     clk = clocks.stop(windows) if rank == 0 else None
     cpu = None
     if rank == 0 and world == 1 and not args.skip_cpu:
         cpu = cpu_baseline(lat)
+        phase("cpu baseline (port + reference python)")
 
     if rank == 0:
         gs = np.abs(np.diag(smp.R))

@@ -69,6 +69,7 @@ int ensure_stage(lgs_handle* h, size_t nbytes) {
 void free_chains(ChainSet& cs) {
     cudaFree(cs.Xbuf); cudaFree(cs.Vbuf); cudaFree(cs.logw); cudaFree(cs.cur); cudaFree(cs.init);
     cudaFree(cs.counts); cudaFree(cs.step_no); cudaFree(cs.upos); cudaFree(cs.Xcur); cudaFree(cs.flags);
+    cudaFree(cs.sp_src); cudaFree(cs.sp_keep);
     cs = ChainSet{};
 }
 
@@ -964,6 +965,7 @@ int lgs_imhk_reset(lgs_handle* h, int64_t chains, uint64_t seed, uint64_t first_
     cs.bl_init = false;
     cs.bl_steps = 0;
     cs.steps_total = 0;
+    cs.bl_loc_dirty = false;
     LGS_CUDA(h, cudaMemset(cs.logw, 0, sizeof(double) * chains));
     LGS_CUDA(h, cudaMemset(cs.cur, 0, sizeof(int32_t) * chains));
     LGS_CUDA(h, cudaMemset(cs.init, 0, sizeof(int32_t) * chains));

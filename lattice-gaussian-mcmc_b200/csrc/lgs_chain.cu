@@ -225,6 +225,13 @@ struct ChainArgs {
     uint8_t* loc;           // [cap] where a chain's current state lives: 0 = Xcur, 1 / 2 = Xbuf[0] / Xbuf[1]
     double* lw_cur;         // [cap] current log importance weight
     long long* counts;      // [cap][2] accepted, total
+    // Step-parallel IMHK (launch_imhk_chain, few chains): the proposals of an independent Metropolis-Hastings chain do
+    // not depend on its state (imhk.py:150 draws y from the Klein sampler alone), so the proposals of MANY steps of
+    // the same chains are drawn as one Klein-mode batch -- tile t holds chains [(t % tiles_per_step) * 128, +128) at step
+    // t / tiles_per_step, Philox key (chain id, tag + step) exactly as the step-by-step launch -- and the accept /
+    // reject recursion runs afterwards over the per-proposal log-weights (imhk_scan_kernel).  0 = off.
+    int tiles_per_step;
+    int64_t v_slot_stride;  // lattice points of a step-parallel points launch: slot (= tile / tiles_per_step) stride in V
     // Replay (the REPLAY instantiations; lgs_klein_replay / lgs_imhk_replay on LGS_PATH_BLOCKED): the panel threads take
     // their uniforms from the reference's recorded stream instead of Philox -- unit s reads U[s * u_stride + position],
     // one uniform per drawn coordinate in the order i = n-1 .. 0 (klein.py:181-220), then one for the accept test of a
@@ -425,7 +432,10 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
                     }
                 }
             } else if (h.flags & F_POINT) {
-                const int64_t s0 = (int64_t)h.tile * kTile;
+                // step-parallel points launch: tile -> (kept slot, chain tile)
+                const int tps = P.tiles_per_step;
+                const int64_t s0 = (int64_t)(tps ? h.tile % tps : h.tile) * kTile;
+                double* __restrict__ Vb = P.V + (tps ? (size_t)(h.tile / tps) * P.v_slot_stride : 0);
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++)
 #pragma unroll
@@ -435,8 +445,8 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
 #pragma unroll
                         for (int nt = 0; nt < 4; nt++) {
                             const int64_t col = s0 + wn * 32 + nt * 8 + t * 2;
-                            if (col < P.S) P.V[(size_t)col * P.ldv + row] = LGS_ACC(mt, hh, nt, 0);
-                            if (col + 1 < P.S) P.V[(size_t)(col + 1) * P.ldv + row] = LGS_ACC(mt, hh, nt, 1);
+                            if (col < P.S) Vb[(size_t)col * P.ldv + row] = LGS_ACC(mt, hh, nt, 0);
+                            if (col + 1 < P.S) Vb[(size_t)(col + 1) * P.ldv + row] = LGS_ACC(mt, hh, nt, 1);
                         }
                     }
             } else {
@@ -713,7 +723,10 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
             bulk_g2s(&sm.sub[slot][qq & 1], &P.subs[nsub - 1 - i], nb, &sm.cfull[slot][qq & 1]);
         };
         const int64_t s = (int64_t)tile * kTile + sl;
-        const uint64_t id = P.first_id + (uint64_t)s;
+        // step-parallel proposals: the tile's chains and its step (see ChainArgs::tiles_per_step)
+        const int tps = IMHK ? 0 : P.tiles_per_step;
+        const uint32_t tile_step = tps ? (uint32_t)(tile / tps) : 0u;
+        const uint64_t id = P.first_id + (uint64_t)(tps ? (int64_t)(tile % tps) * kTile + sl : s);
         // IMHK chain state of this thread's chain (imhk.py:126-177)
         double lw = 0.0;
         int loc = 0, acc_n = 0, tot_n = 0;
@@ -750,7 +763,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
             load_sub(1, q + 1);
         }
         int isub = 0;
-        const uint32_t tagv = P.tag + (uint32_t)step;
+        const uint32_t tagv = P.tag + (uint32_t)step + tile_step;
         double* __restrict__ xtile = P.Xbuf[tagv & 1] + (size_t)tile * P.npad * kRowLd;
         double* __restrict__ xt = xtile + sl;
         double d2a = 0.0, lza = 0.0;
@@ -1080,6 +1093,86 @@ import_coeffs_tiled_kernel(const int64_t* __restrict__ in, int64_t ldi, int npad
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// step-parallel IMHK (ChainArgs::tiles_per_step): the accept / reject recursion over the proposals of one launch
+// ---------------------------------------------------------------------------------------------------------
+struct ScanArgs {
+    int64_t C, cpad;            // chains, chains padded to whole tiles
+    int nsteps;                 // proposals per chain in this launch (the first one may be _initialize_chain)
+    int first_is_init, exact;
+    uint64_t seed, first_id;
+    uint32_t tag;               // Philox tag of proposal 0
+    double sum_lognorm;
+    const double* lz;           // [nsteps][cpad] log-weights of the proposals (exact weights)
+    double* lw_cur;             // [C]
+    long long* counts;          // [C][2]
+    int keep_first, thin, nkeep;   // kept states: after proposals keep_first, keep_first + thin, ...  (nkeep of them)
+    int* keep_src;              // [nkeep][cpad] which proposal holds the state kept in slot m (-1: the state at entry)
+    int* final_src;             // [cpad] the state after the last proposal
+};
+
+// imhk.py:141-177 for one chain per thread, given every proposal's log-weight: the same expressions, in the same
+// order, as the step-by-step launches (panel_role, IMHK) -- chain states are bit-identical between the two.
+__global__ void __launch_bounds__(128) imhk_scan_kernel(const ScanArgs A) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= A.C) return;
+    const Philox gen(A.seed);
+    const uint64_t id = A.first_id + (uint64_t)c;
+    double lw = A.lw_cur[c];
+    int src = -1, acc_n = 0, tot_n = 0;
+    int next_keep = A.keep_first, slot = 0;
+    for (int j = 0; j < A.nsteps; j++) {
+        const double lw_prop = A.exact ? A.lz[(size_t)j * A.cpad + c] : A.sum_lognorm;
+        if (A.first_is_init && j == 0) {
+            lw = lw_prop;
+            src = 0;
+        } else {
+            bool acc = true;
+            if (A.exact) {
+                const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
+                acc = philox_uniform(gen, id, kAcceptDraw, A.tag + (uint32_t)j) < ratio;
+            }
+            tot_n++;
+            if (acc) {
+                acc_n++;
+                lw = lw_prop;
+                src = j;
+            }
+        }
+        if (slot < A.nkeep && j == next_keep) {
+            A.keep_src[(size_t)slot * A.cpad + c] = src;
+            slot++;
+            next_keep += A.thin;
+        }
+    }
+    A.final_src[c] = src;
+    A.lw_cur[c] = lw;
+    if (tot_n) {
+        A.counts[2 * c] += acc_n;
+        A.counts[2 * c + 1] += tot_n;
+    }
+}
+
+// Column copies between tiled matrices: slot m of `dst` (tile = m * tps + chain tile) <- the proposal src[m][c] of
+// `prop` (tile = src * tps + chain tile), or the chain's column of `cur` when src < 0 (skipped when skip_neg: the
+// destination already is `cur`).  One block = the 128 chains of a tile x a strip of coordinates.
+__global__ void __launch_bounds__(128)
+imhk_gather_kernel(const double* __restrict__ prop, const double* __restrict__ cur, double* __restrict__ dst,
+                   const int* __restrict__ src, int64_t C, int64_t cpad, int tps, int npad, int skip_neg) {
+    const int ct = blockIdx.x, m = blockIdx.z;
+    const int64_t c = (int64_t)ct * kTile + threadIdx.x;
+    if (c >= C) return;
+    const int sj = src[(size_t)m * cpad + c];
+    if (sj < 0 && skip_neg) return;
+    const double* __restrict__ from = (sj < 0 ? cur + (size_t)ct * npad * kRowLd
+                                              : prop + ((size_t)sj * tps + ct) * npad * kRowLd) + threadIdx.x;
+    double* __restrict__ to = dst + ((size_t)m * tps + ct) * npad * kRowLd + threadIdx.x;
+    const int rows = (npad + gridDim.y - 1) / gridDim.y;
+    const int r0 = blockIdx.y * rows, r1 = r0 + rows < npad ? r0 + rows : npad;
+#pragma unroll 4
+    for (int i = r0; i < r1; i++) to[(size_t)i * kRowLd] = from[(size_t)i * kRowLd];
+}
+
 __global__ void chain_finish_logq_kernel(const double* __restrict__ lp, double sum_lognorm, int64_t S,
                                          double* __restrict__ logq) {
     int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1209,6 +1302,7 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
         return e;
     LGS_CHAIN_ATTR(false, false, false)
     LGS_CHAIN_ATTR(false, true, false)
+    LGS_CHAIN_ATTR(true, false, false)
     LGS_CHAIN_ATTR(false, false, true)
     LGS_CHAIN_ATTR(true, false, true)
 #undef LGS_CHAIN_ATTR
@@ -1259,7 +1353,7 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     a.inv_two_sigma2 = 1.0 / bc.two_sigma2;
     a.sum_lognorm = bc.sum_lognorm;
     a.npad = cc.npad; a.n_valid = bc.n;
-    a.ntiles = (int)((a.S + kTile - 1) / kTile);
+    if (!(a.tiles_per_step > 0 && a.ntiles > 0)) a.ntiles = (int)((a.S + kTile - 1) / kTile);
     a.want_lz = want_lz ? 1 : 0;
     const int sms = bc.sm_count > 0 ? bc.sm_count : 148;
     const int grid = a.ntiles < sms ? a.ntiles : sms;
@@ -1281,6 +1375,7 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
             else klein_chain_kernel<false, true, false, false, true><<<grid, kThreads, sizeof(ChainSmem), st>>>(a);
         } else if (imhk && want_lz) LGS_CHAIN_GO(true, false, true);
         else if (imhk) LGS_CHAIN_GO(false, false, true);
+        else if (want_lz) LGS_CHAIN_GO(true, false, false);   // step-parallel IMHK proposals with exact weights
         else if (want_d2) LGS_CHAIN_GO(false, true, false);
         else LGS_CHAIN_GO(false, false, false);
 #undef LGS_CHAIN_GO
@@ -1375,7 +1470,7 @@ cudaError_t launch_klein_chain(BlockedCtx& bc, int64_t S, uint64_t seed, uint64_
 // A launch ends at a kept step when kept states are wanted: its last step moves every current state into Xcur and
 // the lattice points are contracted from there inside the same launch.
 // ---------------------------------------------------------------------------------------------------------
-static cudaError_t chain_ensure_chains(BlockedCtx& bc, ChainSet& cs) {
+static cudaError_t chain_ensure_chains(BlockedCtx& bc, ChainSet& cs, bool with_proposal_buffers = true) {
     ChainCtx& cc = bc.chain;
     const int64_t cap = (cs.chains + kTile - 1) / kTile * kTile;
     cudaError_t e;
@@ -1392,6 +1487,7 @@ static cudaError_t chain_ensure_chains(BlockedCtx& bc, ChainSet& cs) {
         if ((e = cudaMemset(cs.flags, 0, cap)) != cudaSuccess) return e;
         cs.bl_cap = cap;
     }
+    if (!with_proposal_buffers) return cudaSuccess;
     for (int b = 1; b <= 2; b++) {
         BlockedWork& w = cc.work[b];
         if (w.cap != cs.bl_cap) {
@@ -1417,10 +1513,168 @@ static void chain_imhk_args(BlockedCtx& bc, ChainSet& cs, ChainArgs& a, int weig
     a.exact = weight_mode == LGS_WEIGHT_EXACT ? 1 : 0;
 }
 
+// every chain's current state into Xcur (states accepted by step-by-step launches may still live in a proposal buffer)
+static cudaError_t chain_imhk_flush_states(BlockedCtx& bc, ChainSet& cs, cudaStream_t st) {
+    if (!cs.bl_loc_dirty) return cudaSuccess;
+    ChainArgs a{};
+    chain_imhk_args(bc, cs, a, LGS_WEIGHT_REFERENCE);
+    a.nsteps = 0;
+    a.flush = 1;
+    cudaError_t e = chain_launch(bc, a, true, false, false, st);
+    if (e == cudaSuccess) cs.bl_loc_dirty = false;
+    return e;
+}
+
+// Step-parallel IMHK: see ChainArgs::tiles_per_step.  Used when the chain set is small against one batch of the chain
+// kernel (BASELINE config 2: 4096 chains at n = 64 are 32 tiles -- a step-by-step launch occupies 32 of 148 SMs and every
+// chain waits for its own serial SampleZ walk; here one launch draws the proposals of up to batch / chains steps at the
+// kernel's full batched rate).  Proposals, accept draws and weights are keyed and computed exactly as in the
+// step-by-step launches: the chains are bit-identical either way (tests/test_gpu_chain.py).
+constexpr int kMaxKeepPerLaunch = 32;
+
+static cudaError_t launch_imhk_chain_steppar(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin,
+                                             int weight_mode, double* V, int64_t* X, cudaStream_t st) {
+    ChainCtx& cc = bc.chain;
+    cudaError_t e;
+    if ((e = chain_ensure_chains(bc, cs, false)) != cudaSuccess) return e;
+    if ((e = chain_imhk_flush_states(bc, cs, st)) != cudaSuccess) return e;
+    const bool exact = weight_mode == LGS_WEIGHT_EXACT;
+    const int64_t C = cs.chains, cpad = cs.bl_cap;
+    const int tps = (int)(cpad / kTile);
+    const int n = bc.n;
+    int64_t max_steps = cc.batch / cpad;
+    if (max_steps > 4096) max_steps = 4096;
+    BlockedWork& w = cc.work[0];
+    const bool want_states = (V || X) && keep > 0;
+    if (!cs.bl_init && (e = cudaMemsetAsync(cs.flags, 0, (size_t)cs.bl_cap, st)) != cudaSuccess) return e;
+    // scan outputs + kept-state staging
+    const size_t need_src = sizeof(int) * (size_t)(kMaxKeepPerLaunch + 1) * cpad;
+    if (cs.sp_src_cap < need_src) {
+        cudaFree(cs.sp_src);
+        cs.sp_src = nullptr, cs.sp_src_cap = 0;
+        if ((e = cudaMalloc(&cs.sp_src, need_src)) != cudaSuccess) return e;
+        cs.sp_src_cap = need_src;
+    }
+    const size_t slot_doubles = (size_t)tps * cc.npad * kRowLd;
+    if (want_states) {
+        const int64_t kmax = keep < kMaxKeepPerLaunch ? keep : kMaxKeepPerLaunch;
+        const size_t need = sizeof(double) * slot_doubles * (size_t)kmax;
+        if (cs.sp_keep_cap < need) {
+            cudaFree(cs.sp_keep);
+            cs.sp_keep = nullptr, cs.sp_keep_cap = 0;
+            if ((e = cudaMalloc(&cs.sp_keep, need)) != cudaSuccess) return e;
+            if ((e = cudaMemsetAsync(cs.sp_keep, 0, need, st)) != cudaSuccess) return e;   // padding columns stay finite
+            cs.sp_keep_cap = need;
+        }
+    }
+    int64_t remaining = burn_in + keep * thin, done = 0;
+    while (remaining > 0 || !cs.bl_init) {
+        const int init = cs.bl_init ? 0 : 1;
+        int64_t now = remaining + init < max_steps ? remaining + init : max_steps;
+        // kept states inside this launch: call-steps g in (done, done + now - init], kept when g > burn_in and
+        // (g - burn_in) % thin == 0; local proposal index j = g - done - 1 + init
+        int64_t g0 = -1, nkeep = 0;
+        if (want_states) {
+            int64_t g = done + 1 > burn_in + thin ? done + 1 : burn_in + thin;
+            const int64_t r = (g - burn_in) % thin;
+            if (r) g += thin - r;
+            if (g <= done + now - init) {
+                g0 = g;
+                nkeep = (done + now - init - g) / thin + 1;
+                if (nkeep > kMaxKeepPerLaunch) {
+                    nkeep = kMaxKeepPerLaunch;
+                    now = g0 + (nkeep - 1) * thin - done + init;   // end the launch at its last kept state
+                }
+            }
+        }
+        if ((e = chain_ensure_work(cc, w, now * cpad)) != cudaSuccess) return e;
+        {   // proposals of `now` steps of every chain: one Klein-mode batch
+            ChainArgs a{};
+            a.Xbuf[0] = a.Xbuf[1] = w.X;
+            a.lp = w.lp; a.d2 = w.d2; a.lz = w.lz;
+            a.S = now * cpad;
+            a.seed = cs.seed; a.first_id = cs.first_id;
+            a.tag = init ? 0u : (uint32_t)(cs.bl_steps + 1);
+            a.nsteps = 1;
+            a.tiles_per_step = tps;
+            a.ntiles = (int)(now * tps);
+            if ((e = chain_launch(bc, a, false, exact, false, st)) != cudaSuccess) return e;
+        }
+        int* keep_src = cs.sp_src;
+        int* final_src = cs.sp_src + (size_t)kMaxKeepPerLaunch * cpad;
+        {
+            ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+            ScanArgs sa{};
+            sa.C = C; sa.cpad = cpad; sa.nsteps = (int)now; sa.first_is_init = init; sa.exact = exact ? 1 : 0;
+            sa.seed = cs.seed; sa.first_id = cs.first_id; sa.tag = init ? 0u : (uint32_t)(cs.bl_steps + 1);
+            sa.sum_lognorm = bc.sum_lognorm; sa.lz = w.lz; sa.lw_cur = cs.logw;
+            sa.counts = reinterpret_cast<long long*>(cs.counts);
+            sa.keep_first = nkeep ? (int)(g0 - done - 1 + init) : -1; sa.thin = (int)thin; sa.nkeep = (int)nkeep;
+            sa.keep_src = keep_src; sa.final_src = final_src;
+            imhk_scan_kernel<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(sa);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            const int ystrips = cc.npad >= 256 ? 4 : 1;
+            if (nkeep) {
+                dim3 grid((unsigned)tps, (unsigned)ystrips, (unsigned)nkeep);
+                imhk_gather_kernel<<<grid, 128, 0, st>>>(w.X, cs.Xcur, cs.sp_keep, keep_src, C, cpad, tps, cc.npad, 0);
+                if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            }
+        }
+        if (nkeep) {
+            const int64_t kidx0 = (g0 - burn_in) / thin - 1;
+            if (V) {   // lattice points of the kept states: a points-only launch over nkeep x chains columns
+                ChainArgs a{};
+                chain_imhk_args(bc, cs, a, LGS_WEIGHT_REFERENCE);
+                a.Xcur = cs.sp_keep;
+                a.nsteps = 0;
+                a.flush = 1;
+                a.V = V + (size_t)kidx0 * n;
+                a.ldv = keep * (int64_t)n;
+                a.v_slot_stride = n;
+                a.tiles_per_step = tps;
+                a.ntiles = (int)(nkeep * tps);
+                if ((e = chain_launch(bc, a, true, false, false, st)) != cudaSuccess) return e;
+            }
+            if (X) {
+                ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+                dim3 grid((unsigned)((C + 31) / 32), (unsigned)((n + 31) / 32));
+                for (int64_t m = 0; m < nkeep; m++) {
+                    export_coeffs_tiled_kernel<<<grid, 256, 0, st>>>(cs.sp_keep + (size_t)m * slot_doubles, cc.npad, n, C,
+                                                                     X + (size_t)(kidx0 + m) * n, keep * (int64_t)n);
+                }
+                if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            }
+        }
+        {   // the state after the launch's last proposal
+            ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+            const int ystrips = cc.npad >= 256 ? 4 : 1;
+            dim3 grid((unsigned)tps, (unsigned)ystrips, 1u);
+            imhk_gather_kernel<<<grid, 128, 0, st>>>(w.X, cs.Xcur, cs.Xcur, final_src, C, cpad, tps, cc.npad, 1);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        }
+        const int64_t stepped = now - init;
+        cs.bl_steps += stepped;
+        cs.bl_init = true;
+        remaining -= stepped;
+        done += stepped;
+    }
+    return cudaSuccess;
+}
+
 cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin, int weight_mode,
                               double* V, int64_t* X, cudaStream_t st, const ChainReplay* rp) {
     cudaError_t e;
+    {
+        // few chains: draw the proposals of many steps per launch (LGS_IMHK_STEPPAR=0 / 1 forces a mode: development A/B)
+        const char* fv = getenv("LGS_IMHK_STEPPAR");   // read per call: the tests switch it between calls
+        const int force = fv ? atoi(fv) : -1;
+        const int64_t cpad = (cs.chains + kTile - 1) / kTile * kTile;
+        const bool few = 4 * cpad <= bc.chain.batch;
+        if (!rp && (force == 1 || (force != 0 && few)) && 2 * cpad <= bc.chain.batch)
+            return launch_imhk_chain_steppar(bc, cs, burn_in, keep, thin, weight_mode, V, X, st);
+    }
     if ((e = chain_ensure_chains(bc, cs)) != cudaSuccess) return e;
+    cs.bl_loc_dirty = true;
     int64_t call_done = 0;   // replay: steps of this call performed by earlier launches
     if (rp) {  // stream positions are per call: chain k reads U[k * stride ...) from its start
         if (!cs.upos) return cudaErrorInvalidValue;
@@ -1502,6 +1756,7 @@ cudaError_t launch_imhk_chain_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* c
         a.V = V;
         a.ldv = n;
         if ((e = chain_launch(bc, a, true, false, false, st)) != cudaSuccess) return e;
+        cs.bl_loc_dirty = false;
         if (X) {
             dim3 grid((unsigned)((C + 31) / 32), (unsigned)((n + 31) / 32));
             export_coeffs_tiled_kernel<<<grid, 256, 0, st>>>(cs.Xcur, bc.chain.npad, n, C, X, n);
@@ -1529,6 +1784,7 @@ cudaError_t launch_imhk_chain_set_state(BlockedCtx& bc, ChainSet& cs, const int6
     if (e != cudaSuccess) return e;
     cs.bl_steps = steps_done;
     cs.bl_init = true;
+    cs.bl_loc_dirty = false;
     return cudaSuccess;
 }
 

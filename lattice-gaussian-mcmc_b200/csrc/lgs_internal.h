@@ -41,6 +41,12 @@ struct ChainSet {
     int64_t bl_steps = 0;         // steps performed so far by every chain (Philox stream index)
     bool bl_init = false;
     int64_t steps_total = 0;      // host mirror, both paths: Metropolis-Hastings steps every chain has performed
+    bool bl_loc_dirty = false;    // chain kernel: some current states may live in a proposal buffer (flags != 0)
+    // step-parallel IMHK (lgs_chain.cu): scan outputs and the staging of kept states
+    int* sp_src = nullptr;        // [kMaxKeepPerLaunch + 1][cap]
+    size_t sp_src_cap = 0;
+    double* sp_keep = nullptr;    // [kept slots][cap / 128][npad][132]
+    size_t sp_keep_cap = 0;
 };
 
 // ---- blocked (DMMA) path -------------------------------------------------------------------------------

@@ -115,8 +115,18 @@ def _run(kind, basis, sigma, procs, count, seed, thin=1):
         # dimension_scaling.py:841-845 uses Pool(n) (fork); here the parent may hold CUDA / OpenMP threads, so the
         # workers are spawned: same processes, same seeding, and the timed region lies inside the worker
         ctx = mp.get_context("spawn")
-        with ctx.Pool(procs) as pool:
-            res = pool.map(_worker, jobs)
+        saved = {k: os.environ.get(k) for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS")}
+        for k in saved:                                    # inherited by the workers BEFORE they import numpy
+            os.environ[k] = "1"
+        try:
+            with ctx.Pool(procs) as pool:
+                res = pool.map(_worker, jobs)
+        finally:
+            for k, v in saved.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
     wall = time.perf_counter() - t0
     units = sum(r[0] for r in res)
     per_core = float(np.mean([r[0] / r[1] for r in res]))
