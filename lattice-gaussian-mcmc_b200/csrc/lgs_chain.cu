@@ -231,6 +231,7 @@ struct ChainArgs {
     // t / tiles_per_step, Philox key (chain id, tag + step) exactly as the step-by-step launch -- and the accept /
     // reject recursion runs afterwards over the per-proposal log-weights (imhk_scan_kernel).  0 = off.
     int tiles_per_step;
+    int skip0;              // all-padding sub-blocks at the top of the first pair (see panel_role)
     int64_t v_slot_stride;  // lattice points of a step-parallel points launch: slot (= tile / tiles_per_step) stride in V
     // Replay (the REPLAY instantiations; lgs_klein_replay / lgs_imhk_replay on LGS_PATH_BLOCKED): the panel threads take
     // their uniforms from the reference's recorded stream instead of Philox -- unit s reads U[s * u_stride + position],
@@ -540,8 +541,9 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     auto issue_point = [&](int tile, int rt) {
         const double* a = P.Bpk + (size_t)rt * nkt * (kPair * kLdA);
         const double* b = (P.flush ? P.Xcur : P.Xbuf[0]) + (size_t)tile * P.npad * kRowLd;
-        for (int kt = 0; kt < nkt; kt++, a += kPair * kLdA, b += kBK * kRowLd)
-            push(F_POINT | (kt == 0 ? F_FIRST : 0) | (kt == nkt - 1 ? F_LAST : 0), 0, rt * kPair, tile, a, b);
+        const int nkv = (P.n_valid + kBK - 1) / kBK;   // k-tiles beyond the last coordinate multiply zeros
+        for (int kt = 0; kt < nkv; kt++, a += kPair * kLdA, b += kBK * kRowLd)
+            push(F_POINT | (kt == 0 ? F_FIRST : 0) | (kt == nkv - 1 ? F_LAST : 0), 0, rt * kPair, tile, a, b);
     };
 
     int next_tile = blockIdx.x;
@@ -694,6 +696,10 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     const int wbase = sl & ~31;  // first sample of this warp inside the tile
     const int npairs = P.npad / kPair;
     const int nsub = P.npad / kSubW;
+    // Sub-blocks of the top pair that consist of padding only (n not a multiple of 64: coordinates n .. npad - 1 are
+    // centred at 0 with x = 0) are not walked at all: their rows keep the zeros the workspace was cleared to / the top
+    // pair's centers item writes (t = 0 there).  n = 16 walks 2 sub-blocks instead of 8, n = 10 two (16 coordinates).
+    // (ChainArgs::skip0, set by chain_launch: a kernel parameter costs the panel loop no register)
     const Philox gen(P.seed);
     double* __restrict__ xs = &sm.xs[slot][0][sl];        // this thread's column of the sub-block's draws
     double* __restrict__ xsw = &sm.xs[slot][0][wbase];    // the warp's 32 columns (DMMA fragments)
@@ -724,9 +730,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
         };
         const int64_t s = (int64_t)tile * kTile + sl;
         // step-parallel proposals: the tile's chains and its step (see ChainArgs::tiles_per_step)
-        const int tps = IMHK ? 0 : P.tiles_per_step;
-        const uint32_t tile_step = tps ? (uint32_t)(tile / tps) : 0u;
-        const uint64_t id = P.first_id + (uint64_t)(tps ? (int64_t)(tile % tps) * kTile + sl : s);
+        const uint64_t id = P.first_id + (uint64_t)((!IMHK && P.tiles_per_step) ? (int64_t)(tile % P.tiles_per_step) * kTile + sl : s);
         // IMHK chain state of this thread's chain (imhk.py:126-177)
         double lw = 0.0;
         int loc = 0, acc_n = 0, tot_n = 0;
@@ -759,11 +763,11 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
             cr_par ^= 1;
         }
         if (sl == 0) {  // every warp of the slot has finished the previous step (pdone -> scheduler -> cready)
-            load_sub(0, q);
-            load_sub(1, q + 1);
+            load_sub(P.skip0, q);
+            if (P.skip0 + 1 < nsub) load_sub(P.skip0 + 1, q + 1);
         }
-        int isub = 0;
-        const uint32_t tagv = P.tag + (uint32_t)step + tile_step;
+        int isub = P.skip0;
+        const uint32_t tagv = P.tag + (uint32_t)step + ((!IMHK && P.tiles_per_step) ? (uint32_t)(tile / P.tiles_per_step) : 0u);
         double* __restrict__ xtile = P.Xbuf[tagv & 1] + (size_t)tile * P.npad * kRowLd;
         double* __restrict__ xt = xtile + sl;
         double d2a = 0.0, lza = 0.0;
@@ -778,14 +782,15 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                 cr_par ^= 1;
             }
             const int lo = P.npad - kPair * (p + 1);
+            const int base_top = kPair - kSubW - (p == 0 ? P.skip0 * kSubW : 0);   // first sub-block with a coordinate < n
             double c[kSubW];
             {
-                const double* xl = xt + (size_t)(lo + kPair - kSubW) * kRowLd;
+                const double* xl = xt + (size_t)(lo + base_top) * kRowLd;
 #pragma unroll
                 for (int k = 0; k < kSubW; k++) c[k] = __ldcg(xl + (size_t)k * kRowLd);
             }
 #pragma unroll 1
-            for (int base = kPair - kSubW; base >= 0; base -= kSubW) {
+            for (int base = base_top; base >= 0; base -= kSubW) {
                 const int buf = q & 1;
                 // done with this buffer: the last of the slot's four warps to say so refills it with the constants of
                 // the sub-block after next (no warpgroup-wide barrier in the coordinate loop)
@@ -861,6 +866,12 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                             done = samplez_smooth_screen(dlf, sp.cf[j], kind, ci.y, uhi, &off, &corr);
                             x = rmean + (double)off;
                             if (WANT_LZ && done) lza += cc.lognz + (double)corr;
+                        } else if (WIDE && !WANT_LZ && ci.x == 3 && dl_ok) {
+                            // wide truncated window: FP32 screen of the closed-form draw (the exact-weight
+                            // instantiations need log Z in FP64 and stay on the FP64 path)
+                            float off;
+                            done = samplez_wide_screen(dlf, sp.cf[j], ci.y, uhi, &off);
+                            x = rmean + (double)off;
                         }
                         if (!done) {
                             const double u = u53(uhi, ulo);
@@ -1268,7 +1279,16 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
                 f.a = (float)c.a; f.sq = (float)c.sq; f.q = (float)c.q; f.znorm = (float)c.znorm; f.eps1 = (float)c.eps1;
                 f.tol_r = (float)(4e-6 + 4e-7 * sg * sg);
                 f.tol_a = (float)(1.6e-7 * c.znorm);
-                sp.ci[j] = make_int4(hc.kind[gi] | (f32ok ? 0 : 4), hc.dmax[gi], hc.uidx[gi], hc.mode[gi]);
+                bool wide_f32 = false;
+                if (hc.kind[gi] == 3) {  // constants of samplez_wide_screen
+                    static const bool wide_screen = [] { const char* v = getenv("LGS_WIDE_SCREEN"); return !(v && v[0] == '0'); }();
+                    const double sa = std::sqrt(c.a);
+                    f.a = (float)c.a; f.sq = (float)sa; f.q = (float)(0.88622692545275801365 / sa);
+                    f.znorm = (float)(sa * 0.56418958354775628695); f.eps1 = (float)(1.0 / sa);
+                    f.tol_r = 4e-6f; f.tol_a = 0.0f;
+                    wide_f32 = wide_screen;
+                }
+                sp.ci[j] = make_int4(hc.kind[gi] | ((f32ok || wide_f32) ? 0 : 4), hc.dmax[gi], hc.uidx[gi], hc.mode[gi]);
             } else {  // padding coordinate: center 0, R_ii = 1, rounded => x = 0
                 sp.cc[j].inv_r = 1.0;
                 sp.ci[j] = make_int4(0, 0, 0, 1);
@@ -1353,6 +1373,7 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     a.inv_two_sigma2 = 1.0 / bc.two_sigma2;
     a.sum_lognorm = bc.sum_lognorm;
     a.npad = cc.npad; a.n_valid = bc.n;
+    a.skip0 = (cc.npad - (bc.n + kSubW - 1) / kSubW * kSubW) / kSubW;
     if (!(a.tiles_per_step > 0 && a.ntiles > 0)) a.ntiles = (int)((a.S + kTile - 1) / kTile);
     a.want_lz = want_lz ? 1 : 0;
     const int sms = bc.sm_count > 0 ? bc.sm_count : 148;

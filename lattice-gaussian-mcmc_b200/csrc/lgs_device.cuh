@@ -448,6 +448,57 @@ __device__ __forceinline__ bool samplez_smooth_screen(float dl, const SmoothF32&
     return (t < cum) && fabsf(t - cprev) > tol && fabsf(t - cu) > tol && fabsf(t - cum) > tol;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Single-precision screen of the wide truncated windows (kind 3; samplez_fast<WIDE>): sigma_i >= 50, the reference's
+// table cut to max_range + 1 entries (klein.py:122-126).  The draw is the index d >= 1 with M(d - 1) <= u Z < M(d),
+// M(d) = sum_{|j| <= d} exp(-a (j + delta)^2), and the side of c0 it falls on.  In FP32: Z = M(D) and M(d0 - 1) from the
+// closed form (integral + end-point mean + the B2 term; the B4 term is < 1e-9 of the sum at a <= 2e-4), d0 from erfinv,
+// then at most four outward steps with directly evaluated weights.  Error budget against the FP64 path, relative to Z:
+// erff 2 ulp and three roundings per closed form (3.6e-7, twice), the 29 dropped bits of u (6e-8), <= 8 additions of
+// the walk (5e-7) -- under 1.4e-6; a draw is accepted only when u Z clears every threshold it is compared with by
+// tol = 4e-6 Z, otherwise the caller runs the FP64 closed form (about 1 % of the draws on a flat window), so the map
+// u -> x stays the FP64 one.  Constants (SmoothF32): a, sq = sqrt(a), q = sqrt(pi) / (2 sqrt(a)), znorm = sqrt(a / pi),
+// eps1 = 1 / sqrt(a), tol_r = 4e-6.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool samplez_wide_screen(float dl, const SmoothF32& k, int dmax, uint32_t uhi, float* off) {
+    const float a = k.a, s = k.sq, c1 = k.q;
+    const float a6 = a * (1.0f / 6.0f);
+    const float D = (float)dmax;
+    float su = D + dl, sd = D - dl;
+    float gu = __expf(-a * su * su), gd = __expf(-a * sd * sd);
+    const float Z = fmaf(c1, erff(s * su) + erff(s * sd), fmaf(0.5f, gu + gd, -a6 * fmaf(su, gu, sd * gd)));
+    const float T = (float)(uhi >> 8) * 5.9604644775390625e-8f * Z;
+    const float tol = k.tol_r * Z;
+    const float y = T * k.znorm;
+    if (!(y < 0.9999f)) return false;
+    int d0 = (int)floorf(fmaf(erfinvf(y), k.eps1, -0.5f)) - 1;
+    d0 = d0 < 1 ? 1 : d0;
+    const float e = (float)(d0 - 1);
+    su = e + dl, sd = e - dl;
+    gu = __expf(-a * su * su), gd = __expf(-a * sd * sd);
+    float cum = fmaf(c1, erff(s * su) + erff(s * sd), fmaf(0.5f, gu + gd, -a6 * fmaf(su, gu, sd * gd)));
+    if (!(T > cum + tol)) return false;   // at or below M(d0 - 1), or too close to call
+#pragma unroll 1
+    for (int i = 0; i < 4; i++) {
+        const float d = (float)(d0 + i);
+        if (d > D) return false;
+        su = d + dl, sd = d - dl;
+        cum += __expf(-a * su * su);
+        if (T < cum) {
+            *off = d;
+            return T < cum - tol;
+        }
+        if (!(T > cum + tol)) return false;
+        cum += __expf(-a * sd * sd);
+        if (T < cum) {
+            *off = -d;
+            return T < cum - tol;
+        }
+        if (!(T > cum + tol)) return false;
+    }
+    return false;
+}
+
 // delta = rint(mean) - mean as a float WITHOUT FP64 arithmetic: the mantissa of `mean` is shifted to a fixed-point
 // number with 32 fractional bits with integer instructions and the fraction is taken from there (absolute error
 // < 2^-32 plus one FP32 rounding, inside the screen's tolerance).  Returns false for a fraction of exactly one half

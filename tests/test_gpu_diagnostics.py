@@ -147,7 +147,7 @@ def test_device_tvd_default_call_at_the_headline_dimension(lgs):
     got = device_tvd(smp, Va, Vb)
     want = compute_tvd(Va.cpu().numpy(), Vb.cpu().numpy())
     assert abs(got - want) < 1e-12, (got, want)
-    assert 0.3 < got < 1.0          # 3000 samples over ~1000 occupied values per marginal: mostly sampling noise
+    assert 0.1 < got < 1.0          # 3000 samples over ~1000 occupied values per marginal: mostly sampling noise
     # a subset of coordinates through the shared-memory variant, more than 256 through the chunked one
     dims = np.arange(0, 1024, 3)
     got2 = device_tvd(smp, Va, Vb, dims=dims)
