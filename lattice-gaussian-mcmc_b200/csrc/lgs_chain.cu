@@ -82,6 +82,14 @@ template <int N>
 __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N>
 __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -230,6 +238,16 @@ struct ChainArgs {
     // the same chains are drawn as one Klein-mode batch -- tile t holds chains [(t % tiles_per_step) * 128, +128) at step
     // t / tiles_per_step, Philox key (chain id, tag + step) exactly as the step-by-step launch -- and the accept /
     // reject recursion runs afterwards over the per-proposal log-weights (imhk_scan_kernel).  0 = off.
+    // Global lattice-point queue (gq != 0).  The lattice points of a finished tile are npairs work items (64 rows
+    // each) that stream the tile's whole coefficient block; served per CTA as filler they are spread over the launch and
+    // every one of them re-reads the block from DRAM (the blocks in flight, 3 x 148 x 1 MB, do not fit the L2).  With the
+    // queue a finished tile is published in pt_list and EVERY CTA claims items from it in order, so at any time the
+    // SMs work on the row blocks of the same ~10 tiles: their blocks stay in L2 and are read from DRAM once.  It also
+    // balances the tail of a launch.  pt_list[i] = tile + 1 once published (zeroed per launch); pt_ctr[0] = list slots
+    // handed out, pt_ctr[1] = next item to claim (item = list position * npairs + row block).
+    int gq;
+    int* pt_list;
+    unsigned* pt_ctr;
     int tiles_per_step;
     int skip0;              // all-padding sub-blocks at the top of the first pair (see panel_role)
     int64_t v_slot_stride;  // lattice points of a step-parallel points launch: slot (= tile / tiles_per_step) stride in V
@@ -414,11 +432,14 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
                 }
                 if (bad) atomicOr(P.ovf, 1);
                 __syncwarp();   // the staging rows are rewritten by the warp's next lattice-point item
-                if (h.r0 + kPair == P.npad) {
-                    // the tile's last 64 rows (its items arrive in row order): everything this warp has stored for
-                    // the tile becomes visible system-wide, then the warp is counted; the eighth warp publishes
+                if (P.gq || h.r0 + kPair == P.npad) {
+                    // Per-CTA order (gq == 0): the tile's last 64 rows (its items arrive in row order): everything this
+                    // warp has stored for the tile becomes visible system-wide, then the warp is counted; the eighth
+                    // warp publishes.  Global queue (V16 in device memory): the row blocks of a tile finish on
+                    // different SMs in any order, so every (row block, warp) is counted after a device-scope fence and
+                    // the last of the 8 npairs arrivals publishes behind a system-scope fence.
 #if !LGS_ZC_NOFENCE
-                    __threadfence_system();
+                    if (P.gq) __threadfence(); else __threadfence_system();
 #endif
                     __syncwarp();
                     if (lane == 0) {
@@ -546,6 +567,29 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
             push(F_POINT | (kt == 0 ? F_FIRST : 0) | (kt == nkv - 1 ? F_LAST : 0), 0, rt * kPair, tile, a, b);
     };
 
+    // global lattice-point queue (ChainArgs::gq)
+    const unsigned gq_total = (unsigned)P.ntiles * (unsigned)npairs;
+    auto gq_publish = [&](int tile) {
+        // the tile's coefficients were stored by the panel threads (generic proxy, fence.proxy.async, pdone observed
+        // above); the release below orders them before the list entry for whichever CTA claims the tile's items
+        const unsigned slot = atomicAdd(&P.pt_ctr[0], 1u);
+        __threadfence();
+        st_release_gpu(&P.pt_list[slot], tile + 1);
+    };
+    auto gq_claim = [&](int& tile, int& rt) -> bool {
+        for (;;) {
+            const unsigned idx = *reinterpret_cast<volatile unsigned*>(&P.pt_ctr[1]);
+            if (idx >= gq_total) return false;
+            const int t = ld_acquire_gpu(&P.pt_list[idx / (unsigned)npairs]);
+            if (t == 0) return false;   // the next tile in line is not finished yet
+            if (atomicCAS(&P.pt_ctr[1], idx, idx + 1u) == idx) {
+                tile = t - 1;
+                rt = (int)(idx % (unsigned)npairs);
+                fence_proxy_async();    // the claimed tile's rows are read next by this thread's bulk copies
+                return true;
+            }
+        }
+    };
     int next_tile = blockIdx.x;
     int s_pair[kSlots] = {}, s_tile[kSlots] = {};   // s_pair: pairs whose centers have been completed (part B issued)
     int s_ahead[kSlots] = {};             // next pair whose part A has not been issued yet
@@ -602,7 +646,10 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
                         s_step[s]++;
                         start_step(s);
                     } else {
-                        if (P.V || P.V16) { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
+                        if (P.V || P.V16) {
+                            if (P.gq) gq_publish(s_tile[s]);
+                            else { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
+                        }
                         assign(s);
                     }
                 } else {
@@ -642,7 +689,15 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
             }
             continue;
         }
-        if (n_active == 0) break;
+        if (P.gq && (P.V || P.V16)) {
+            int gt, grt;
+            if (gq_claim(gt, grt)) {
+                issue_point(gt, grt);
+                continue;
+            }
+            // leave only when every item of the launch has been claimed (by this CTA or another)
+            if (n_active == 0 && *reinterpret_cast<volatile unsigned*>(&P.pt_ctr[1]) >= gq_total) break;
+        } else if (n_active == 0) break;
         if (rec) {
             const long long t0 = clock64();
             __nanosleep(200);
@@ -1203,6 +1258,7 @@ void chain_free(BlockedCtx& bc) {
     cudaFree(cc.invr);
     cudaFree(cc.sig);
     cudaFree(cc.subs);
+    cudaFree(cc.pt_buf);
     for (auto& w : cc.work) {
         cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
         w = BlockedWork{};
@@ -1378,6 +1434,30 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     a.want_lz = want_lz ? 1 : 0;
     const int sms = bc.sm_count > 0 ? bc.sm_count : 148;
     const int grid = a.ntiles < sms ? a.ntiles : sms;
+    {
+        // global lattice-point queue (ChainArgs::gq): every launch that produces lattice points, except the mapped
+        // zero-copy transport, whose per-tile completion word relies on a tile's row blocks finishing in order on one SM.
+        // LGS_CHAIN_GQ=0: per-CTA filler order (development A/B)
+        static const bool gq_on = [] { const char* v = getenv("LGS_CHAIN_GQ"); return !(v && v[0] == '0'); }();
+        a.gq = 0;
+        if (gq_on && (a.V || (a.V16 && a.group_cnt)) && grid > 1) {
+            const size_t need = sizeof(int) * (size_t)(a.ntiles + 2);
+            if (cc.pt_cap < need) {
+                cudaFree(cc.pt_buf);
+                cc.pt_buf = nullptr, cc.pt_cap = 0;
+                const size_t cap = need < 65536 ? 65536 : need * 2;
+                cudaError_t e = cudaMalloc(&cc.pt_buf, cap);
+                if (e != cudaSuccess) return e;
+                cc.pt_cap = cap;
+            }
+            cudaError_t e = cudaMemsetAsync(cc.pt_buf, 0, need, st);
+            if (e != cudaSuccess) return e;
+            a.gq = 1;
+            a.pt_ctr = reinterpret_cast<unsigned*>(cc.pt_buf);
+            a.pt_list = reinterpret_cast<int*>(cc.pt_buf) + 2;
+            if (a.V16) a.tile_target = (unsigned)(kDmmaThreads / 32) * (unsigned)(cc.npad / kPair);
+        }
+    }
     static const bool want_stats = kStatsBuild && getenv("LGS_CHAIN_STATS") != nullptr;
     static unsigned long long* stats_dev = nullptr;
     if (want_stats && !stats_dev) cudaMalloc(&stats_dev, sizeof(unsigned long long) * 12 * 1024);

@@ -138,6 +138,8 @@ struct ChainCtx {
     BlockedWork work[3];          // tiled: X = [cap/128][npad][132]; [0] Klein, [1]/[2] IMHK proposals
     int64_t batch = 0;            // samples per full batch: sm_count x 128 x 9
     bool wide = false;            // some coordinate has a wide truncated window (kind 3): the WIDE kernel instantiations
+    void* pt_buf = nullptr;       // global lattice-point queue of a launch: [slots handed out, next item, list ...]
+    size_t pt_cap = 0;
 };
 
 struct BlockedCtx {
