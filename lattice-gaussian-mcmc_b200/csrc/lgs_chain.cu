@@ -244,7 +244,7 @@ struct ChainArgs {
     // queue a finished tile is published in pt_list and EVERY CTA claims items from it in order, so at any time the
     // SMs work on the row blocks of the same ~10 tiles: their blocks stay in L2 and are read from DRAM once.  It also
     // balances the tail of a launch.  pt_list[i] = tile + 1 once published (zeroed per launch); pt_ctr[0] = list slots
-    // handed out, pt_ctr[1] = next item to claim (item = list position * npairs + row block).
+    // handed out, pt_ctr[1] = next ticket (item = list position * npairs + row block), drawn by fetch-and-add.
     int gq;
     int* pt_list;
     unsigned* pt_ctr;
@@ -576,19 +576,29 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
         __threadfence();
         st_release_gpu(&P.pt_list[slot], tile + 1);
     };
+    // Tickets: an item is claimed with one fetch-and-add (it cannot fail, however many CTAs claim at once -- a
+    // compare-and-swap loop here retried for most of its attempts: 148 schedulers claim ~2 items per microsecond in
+    // total and a claim takes longer than that).  The ticket may be ahead of the published tiles; it is then kept
+    // (gq_ticket) and re-examined on later passes of the scheduling loop, which goes on serving this CTA's own
+    // panels in between -- so a pending ticket never holds up the tile it waits for.
+    unsigned gq_ticket = 0xffffffffu;   // none
+    bool gq_drained = !(P.gq && (P.V || P.V16));   // this CTA has drawn a ticket past the last item
     auto gq_claim = [&](int& tile, int& rt) -> bool {
-        for (;;) {
-            const unsigned idx = *reinterpret_cast<volatile unsigned*>(&P.pt_ctr[1]);
-            if (idx >= gq_total) return false;
-            const int t = ld_acquire_gpu(&P.pt_list[idx / (unsigned)npairs]);
-            if (t == 0) return false;   // the next tile in line is not finished yet
-            if (atomicCAS(&P.pt_ctr[1], idx, idx + 1u) == idx) {
-                tile = t - 1;
-                rt = (int)(idx % (unsigned)npairs);
-                fence_proxy_async();    // the claimed tile's rows are read next by this thread's bulk copies
-                return true;
+        if (gq_drained) return false;
+        if (gq_ticket == 0xffffffffu) {
+            gq_ticket = atomicAdd(&P.pt_ctr[1], 1u);
+            if (gq_ticket >= gq_total) {
+                gq_drained = true;
+                return false;
             }
         }
+        const int t = ld_acquire_gpu(&P.pt_list[gq_ticket / (unsigned)npairs]);
+        if (t == 0) return false;       // the ticket's tile is not finished yet
+        tile = t - 1;
+        rt = (int)(gq_ticket % (unsigned)npairs);
+        gq_ticket = 0xffffffffu;
+        fence_proxy_async();            // the claimed tile's rows are read next by this thread's bulk copies
+        return true;
     };
     int next_tile = blockIdx.x;
     int s_pair[kSlots] = {}, s_tile[kSlots] = {};   // s_pair: pairs whose centers have been completed (part B issued)
@@ -695,8 +705,8 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
                 issue_point(gt, grt);
                 continue;
             }
-            // leave only when every item of the launch has been claimed (by this CTA or another)
-            if (n_active == 0 && *reinterpret_cast<volatile unsigned*>(&P.pt_ctr[1]) >= gq_total) break;
+            // leave when this CTA has no tile left and the queue has no item left for it
+            if (n_active == 0 && gq_drained) break;
         } else if (n_active == 0) break;
         if (rec) {
             const long long t0 = clock64();
@@ -1440,7 +1450,9 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
         // LGS_CHAIN_GQ=0: per-CTA filler order (development A/B)
         static const bool gq_on = [] { const char* v = getenv("LGS_CHAIN_GQ"); return !(v && v[0] == '0'); }();
         a.gq = 0;
-        if (gq_on && (a.V || (a.V16 && a.group_cnt)) && grid > 1) {
+        // Small dimensions keep the per-CTA order: a tile's lattice points are then one or two short items and the
+        // ticket costs more than the re-read (n = 64: -2 %; n = 512: +3.6 %; n = 1024: +0.3 %, DRAM reads per launch cut)
+        if (gq_on && (a.V || (a.V16 && a.group_cnt)) && grid > 1 && cc.npad >= 4 * kPair) {
             const size_t need = sizeof(int) * (size_t)(a.ntiles + 2);
             if (cc.pt_cap < need) {
                 cudaFree(cc.pt_buf);
