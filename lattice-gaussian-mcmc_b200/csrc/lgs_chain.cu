@@ -120,24 +120,24 @@ constexpr int kPair = 64;             // coordinates per work item (a pair of 32
 constexpr int kBK = LGS_CHAIN_BK;     // contraction depth of one stage
 constexpr int kLdA = kBK + 4;         // 20: row stride of an A sliver (conflict-free LDS.64 fragment loads)
 constexpr int kSubW = 8;              // coordinates per sub-block of the panel (width of the register window)
-#ifndef LGS_CHAIN_SLOTS
-#define LGS_CHAIN_SLOTS 3
+#ifndef LGS_CHAIN_TPW
+#define LGS_CHAIN_TPW 2   // tiles a panel warpgroup alternates between (1: the round-1 kernel, three tiles in flight)
 #endif
 #ifndef LGS_CHAIN_DEPDIST
 #define LGS_CHAIN_DEPDIST 0   // 0: m16n8k8 in compiler order; D > 0: m8n8k4, dependent instructions D places apart
-#endif
-#ifndef LGS_CHAIN_INTDELTA
-#define LGS_CHAIN_INTDELTA 0
-#endif
-#ifndef LGS_CHAIN_NOBAR
-#define LGS_CHAIN_NOBAR 0
 #endif
 #ifndef LGS_CHAIN_STAGES
 #define LGS_CHAIN_STAGES 5
 #endif
 constexpr int kStages = LGS_CHAIN_STAGES;
-constexpr int kSlots = LGS_CHAIN_SLOTS;  // tiles in flight per CTA = panel warpgroups
-constexpr int kDmmaThreads = 256, kProdThreads = 128, kPanelThreads = kSlots * 128;
+constexpr int kWgs = 3;                  // panel warpgroups
+// Tiles in flight per CTA ("slots"): every panel warpgroup alternates between kTpw tiles, pair by pair -- while the
+// centers of one tile's next pair are being contracted it draws a pair of the other, and the DMMA warps always have
+// the look-ahead items of 2 x 3 tiles to choose from.  Slot = warpgroup * tpw + k.  (The replay instantiations keep
+// one tile per warpgroup: their stream position lives in a register across pairs.)
+constexpr int kTpw = LGS_CHAIN_TPW;
+constexpr int kMaxSlots = kWgs * kTpw;
+constexpr int kDmmaThreads = 256, kProdThreads = 128, kPanelThreads = kWgs * 128;
 constexpr int kThreads = kDmmaThreads + kProdThreads + kPanelThreads;  // 768
 // thread layout: panel warpgroups first (lowest warp ids), then the producer warpgroup, then the DMMA warpgroups
 #ifndef LGS_CHAIN_PANEL_FIRST
@@ -146,8 +146,8 @@ constexpr int kThreads = kDmmaThreads + kProdThreads + kPanelThreads;  // 768
 constexpr int kPanelBase = LGS_CHAIN_PANEL_FIRST ? 0 : kDmmaThreads + kProdThreads;
 constexpr int kProdBase = LGS_CHAIN_PANEL_FIRST ? kPanelThreads : kDmmaThreads;
 constexpr int kDmmaBase = LGS_CHAIN_PANEL_FIRST ? kPanelThreads + kProdThreads : 0;
-// registers: 768 x 80 at launch (3 slots) or 896 x 72 (4 slots), rebalanced between the roles with setmaxnreg
-constexpr int kRegsDmma = kSlots == 3 ? 120 : 112, kRegsProd = 24, kRegsPanel = kSlots == 3 ? 72 : 64;
+// registers: 768 x 80 at launch, rebalanced between the roles with setmaxnreg
+constexpr int kRegsDmma = 120, kRegsProd = 24, kRegsPanel = 72;
 constexpr uint32_t kABytes = kPair * kLdA * 8;   // 10 240
 constexpr uint32_t kBBytes = kBK * kRowLd * 8;   // 16 896
 
@@ -167,17 +167,33 @@ struct StageHdr {
     int tile;
 };
 
+// panel_role's bookkeeping, kept in shared memory so that it costs the coordinate loop no registers
+struct PanelSlot {
+    int tile;        // tile being processed; -1: the slot waits for its next tile; -2: no tile left
+    int step;        // Metropolis-Hastings step of the launch (Klein: 0)
+    int pair;        // next pair of the step
+    uint32_t crp;    // parity of the slot's centers-ready barrier
+};
+struct PanelIssue {
+    uint32_t q_iss;  // constants loads issued so far (load number q goes to buffer q & 1)
+    int cur;         // next sub-block of the current job to request
+    int end;         // one past the current job's last sub-block
+    int nstart;      // first sub-block of the job that follows, or -1 while that depends on a tile assignment
+    int nj;          // sub-blocks of the following job already requested
+};
+
 struct ChainSmem {
     double A[kStages][kPair][kLdA];
     double B[kStages][kBK][kRowLd];
-    SubPack sub[kSlots][2];            // double-buffered constants of the sub-block being drawn
-    alignas(16) double xs[kSlots][kSubW][kRowLd];  // the sub-block's draws (B operand of the rows-below update), then
+    SubPack sub[kWgs][2];              // double-buffered constants of the sub-block being drawn (per warpgroup)
+    alignas(16) double xs[kWgs][kSubW][kRowLd];    // the sub-block's draws (B operand of the rows-below update), then
                                                    // the next window on its way back to one-thread-per-sample
     StageHdr hdr[kStages];
     uint64_t full[kStages], empty[kStages];
-    uint64_t cready[kSlots], pdone[kSlots], cfull[kSlots][2];
-    int slot_tile[kSlots];
-    int cdone[kSlots][2];              // warps of the slot that have finished with a constants buffer
+    uint64_t cready[kMaxSlots], pdone[kMaxSlots], cfull[kWgs][2];
+    int slot_tile[kMaxSlots];
+    PanelSlot pst[kWgs][4][2];         // per panel warp: where each of its warpgroup's slots stands (panel_role)
+    PanelIssue iss[kWgs];              // per warpgroup: the constants loads in flight (thread 0 of the warpgroup only)
     // packed lattice-point output (ChainArgs::V16): per DMMA warp, its 32 samples x 32 rows as int16, one 80-byte
     // row per sample so that a lane reads its sample's 64 bytes as four conflict-free 16-byte words
     alignas(16) int16_t pk16[kDmmaThreads / 32][32][40];
@@ -246,6 +262,9 @@ struct ChainArgs {
     // balances the tail of a launch.  pt_list[i] = tile + 1 once published (zeroed per launch); pt_ctr[0] = list slots
     // handed out, pt_ctr[1] = next ticket (item = list position * npairs + row block), drawn by fetch-and-add.
     int gq;
+    int lookahead;          // centers of a pair in two items (see F_PART_OUT): 0 never, 1 always, 2 when the DMMA warps
+                            // would otherwise idle
+    int stagger;            // slots started a sixth of a step apart (producer_role)
     int* pt_list;
     unsigned* pt_ctr;
     int tiles_per_step;
@@ -509,7 +528,7 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
 // ---------------------------------------------------------------------------------------------------------
 // producer / scheduler: one thread
 // ---------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P) {
+__device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P, const int nslots) {
     const int G = gridDim.x;
     const int npairs = P.npad / kPair;
     const int nkt = P.npad / kBK;
@@ -601,11 +620,11 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
         return true;
     };
     int next_tile = blockIdx.x;
-    int s_pair[kSlots] = {}, s_tile[kSlots] = {};   // s_pair: pairs whose centers have been completed (part B issued)
-    int s_ahead[kSlots] = {};             // next pair whose part A has not been issued yet
-    int s_step[kSlots] = {};              // Metropolis-Hastings step of the launch the slot's tile is in (Klein: 0)
-    uint32_t pd_par[kSlots];
-    bool s_active[kSlots];
+    int s_pair[kMaxSlots] = {}, s_tile[kMaxSlots] = {};   // s_pair: pairs whose centers have been completed (part B issued)
+    int s_ahead[kMaxSlots] = {};          // next pair whose part A has not been issued yet
+    int s_step[kMaxSlots] = {};           // Metropolis-Hastings step of the launch the slot's tile is in (Klein: 0)
+    uint32_t pd_par[kMaxSlots];
+    bool s_active[kMaxSlots];
     int n_active = 0;
     auto xsel_of = [&](int step) { return (int)((P.tag + (uint32_t)step) & 1u); };
     auto start_step = [&](int s) {
@@ -633,11 +652,26 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
             push(F_FIRST | F_LAST | F_NODATA | F_NOSTORE, s, 0, -1, nullptr, nullptr);
         }
     };
-    for (int s = 0; s < kSlots; s++) {
+    // Staggered start.  The centers of pair p cost 4 p stages while a panel takes the same time for every pair, so
+    // tiles that walk their pairs in phase starve the DMMA warps at the top of a step and queue behind them at the
+    // bottom.  The slots are therefore started 1/6 of a step apart -- warpgroup w's first slot once slot 0 has drawn
+    // w npairs / 6 pairs, a warpgroup's second slot once its first has drawn npairs / 2 -- and the alternation inside
+    // a warpgroup and the equal length of all tiles keep them there for the rest of the launch.  A warpgroup whose
+    // second slot is not started yet is told so at each of its turns (slot_tile = -3) and goes on with the first.
+    const int tpw = nslots / kWgs;
+    const bool stagger = P.stagger && npairs >= 2 * nslots && P.nsteps > 0 && P.ntiles >= nslots * G;
+    int s_jobs[kMaxSlots] = {};           // pairs the slot's panel has drawn since the launch began
+    bool s_defer[kMaxSlots] = {};
+    auto not_yet = [&](int s) {
+        sm.slot_tile[s] = -3;
+        push(F_FIRST | F_LAST | F_NODATA | F_NOSTORE, s, 0, -1, nullptr, nullptr);
+    };
+    for (int s = 0; s < nslots; s++) {
         pd_par[s] = 0;
         s_active[s] = true;
         n_active++;
-        assign(s);
+        if (stagger && s > 0) s_defer[s] = true;
+        else assign(s);
     }
     // finished tiles whose lattice points are still to be contracted (filler work for the DMMA warps)
     constexpr int kQ = 32;
@@ -647,10 +681,29 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
     for (;;) {
         bool progressed = false;
         if (pq_cnt < kQ) {
-            for (int i = 0; i < kSlots; i++) {
-                const int s = (rr + i) % kSlots;
-                if (!s_active[s] || !mbar_test_wait(&sm.pdone[s], pd_par[s])) continue;
+            for (int i = 0; i < nslots; i++) {
+                const int s = (rr + i) % nslots;
+                if (!s_active[s] || s_defer[s] || !mbar_test_wait(&sm.pdone[s], pd_par[s])) continue;
                 pd_par[s] ^= 1;
+                if (stagger) {
+                    s_jobs[s]++;
+                    if (s == 0)
+                        for (int w = 1; w < kWgs; w++)
+                            if (s_defer[w * tpw] && s_jobs[0] >= w * npairs / nslots) {
+                                s_defer[w * tpw] = false;
+                                assign(w * tpw);
+                            }
+                    if (tpw == 2 && !(s & 1) && s_defer[s + 1]) {
+                        // the warpgroup turns to its second slot next: start it, or send it back to this one
+                        const bool ends = s_pair[s] == npairs && s_step[s] + 1 >= P.nsteps && next_tile >= P.ntiles;
+                        if (s_jobs[s] >= npairs / 2 || ends) {
+                            s_defer[s + 1] = false;
+                            assign(s + 1);
+                        } else {
+                            not_yet(s + 1);
+                        }
+                    }
+                }
                 if (s_pair[s] == npairs) {
                     if (s_step[s] + 1 < P.nsteps) {  // next Metropolis-Hastings step of the same chains
                         s_step[s]++;
@@ -665,11 +718,18 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
                 } else {
                     const int pr = s_pair[s];  // its panel may start once part B is through
                     const int xs_ = xsel_of(s_step[s]);
-                    if (pr >= 2 && s_ahead[s] <= pr) {
+                    if (P.lookahead == 1 && pr >= 2 && s_ahead[s] <= pr) {   // eager look-ahead: every pair in two items
                         issue_A(s, pr, s_tile[s], xs_);
                         s_ahead[s] = pr + 1;
                     }
-                    issue_B(s, pr, s_tile[s], xs_);
+                    if (pr >= 2 && s_ahead[s] > pr) {
+                        issue_B(s, pr, s_tile[s], xs_);   // part A is parked in the pair's rows
+                    } else {
+                        // one item over every column above the pair: no parked partial sums, one epilogue
+                        const int lo = P.npad - kPair * (pr + 1);
+                        issue_range(0, s, lo, s_tile[s], xs_, lo + kPair, P.npad);
+                        s_ahead[s] = pr + 1;
+                    }
                     s_pair[s]++;
                 }
                 rr = s + 1;
@@ -678,18 +738,25 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
             }
         }
         if (progressed) continue;
-        // look-ahead: part A of pair s_pair (its columns, the pairs up to s_pair - 2, are all drawn) while the
-        // slot's panel warps work on pair s_pair - 1
-        for (int i = 0; i < kSlots; i++) {
-            const int s = (ra + i) % kSlots;
-            if (!s_active[s] || s_ahead[s] > s_pair[s] || s_ahead[s] >= npairs) continue;
-            issue_A(s, s_ahead[s], s_tile[s], xsel_of(s_step[s]));
-            s_ahead[s]++;
-            ra = s + 1;
-            progressed = true;
-            break;
-        }
-        if (progressed) continue;
+        // Look-ahead: part A of pair s_pair (its columns, the pairs up to s_pair - 2, are all drawn) while the slot's
+        // panel warps work on pair s_pair - 1.  It costs a second epilogue and the re-read of the parked sums by the
+        // DMMA warps (8.7 % of their time when every pair is split, ncu).  With two tiles per panel warpgroup a
+        // finished pair no longer waits for its centers -- the warpgroup draws its other tile meanwhile -- and the
+        // split costs more than it hides: default 0 (one item per pair).  1 = every pair split (the round-1 kernel),
+        // 2 = split only when the ring has run dry and there are no lattice points to contract either; measured at
+        // n = 1024 / 512: IMHK 73.4 / 73.9 / 73.4 ms per 10 steps, Klein without points 4.61 / 4.95 / 4.98 ms at n = 512.
+        auto look_ahead = [&]() -> bool {
+            for (int i = 0; i < nslots; i++) {
+                const int s = (ra + i) % nslots;
+                if (!s_active[s] || s_defer[s] || s_ahead[s] > s_pair[s] || s_ahead[s] >= npairs) continue;
+                issue_A(s, s_ahead[s], s_tile[s], xsel_of(s_step[s]));
+                s_ahead[s]++;
+                ra = s + 1;
+                return true;
+            }
+            return false;
+        };
+        if (P.lookahead == 1 && look_ahead()) continue;
         if (pq_cnt > 0) {
             issue_point(pq[pq_head], pq_rt);
             if (++pq_rt == npairs) {
@@ -699,15 +766,22 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P)
             }
             continue;
         }
-        if (P.gq && (P.V || P.V16)) {
+        const bool use_gq = P.gq && (P.V || P.V16);
+        if (use_gq) {
             int gt, grt;
             if (gq_claim(gt, grt)) {
                 issue_point(gt, grt);
                 continue;
             }
-            // leave when this CTA has no tile left and the queue has no item left for it
-            if (n_active == 0 && gq_drained) break;
-        } else if (n_active == 0) break;
+        }
+        if (P.lookahead == 2) {
+            // every stage but the last one pushed has been consumed
+            const uint32_t j = it - 2u;
+            const bool ring_low = it < 2u || mbar_test_wait(&sm.empty[j % kStages], (j / kStages) & 1);
+            if (ring_low && look_ahead()) continue;
+        }
+        // leave when this CTA has no tile left and (global queue) the queue has no item left for it
+        if (n_active == 0 && (!use_gq || gq_drained)) break;
         if (rec) {
             const long long t0 = clock64();
             __nanosleep(200);
@@ -754,7 +828,14 @@ __device__ __noinline__ bool chain_samplez_table_call(double mean, double sig, i
 // larger callee costs the panel loop spills (+1 % on the NTRU workload, which has none)
 // REPLAY: uniforms from the recorded stream + the reference's table SampleZ (see ChainArgs::U)
 template <bool WANT_LZ, bool WANT_D2, bool IMHK, bool WIDE, bool REPLAY>
-__device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, const int slot) {
+__device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, const int wg) {
+    // The warpgroup's work is a sequence of JOBS: one job = one 64-coordinate pair of one tile.  With TPW = 2 the
+    // warpgroup owns two slots (tiles) and takes their jobs in strict alternation, so the 4-stage item that finishes
+    // the centers of a tile's next pair (and the look-ahead item before it) runs while the warpgroup draws a pair of
+    // the other tile.  Nothing per-thread survives a job in registers except with TPW = 1: the partial log-density
+    // sums are parked in their output arrays, the chain state (log weight, location, counters) is read and written
+    // back around the accept test, the window is reloaded from the workspace at every pair as before.
+    constexpr int TPW = REPLAY ? 1 : kTpw;
     const int sl = (threadIdx.x - kPanelBase) & 127;
     const int lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
@@ -766,10 +847,9 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     // pair's centers item writes (t = 0 there).  n = 16 walks 2 sub-blocks instead of 8, n = 10 two (16 coordinates).
     // (ChainArgs::skip0, set by chain_launch: a kernel parameter costs the panel loop no register)
     const Philox gen(P.seed);
-    double* __restrict__ xs = &sm.xs[slot][0][sl];        // this thread's column of the sub-block's draws
-    double* __restrict__ xsw = &sm.xs[slot][0][wbase];    // the warp's 32 columns (DMMA fragments)
-    uint32_t cr_par = 0, q = 0;
-    const bool rec = kStatsBuild && P.stats && slot == 0 && sl == 0;
+    double* __restrict__ xs = &sm.xs[wg][0][sl];        // this thread's column of the sub-block's draws
+    double* __restrict__ xsw = &sm.xs[wg][0][wbase];    // the warp's 32 columns (DMMA fragments)
+    const bool rec = kStatsBuild && P.stats && wg == 0 && sl == 0;
     constexpr bool kDetail = LGS_CHAIN_STATS_DETAIL != 0;
     const bool rec2 = kDetail && rec;
     long long t_cwait = 0, t_top = 0, t_cfull = 0, t_bar = 0;
@@ -778,35 +858,78 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     auto sub_bytes = [](int base) -> uint32_t {
         return (uint32_t)(offsetof(SubPack, rect) + ((base + 15) / 16 * 16) * kRectLd * sizeof(double));
     };
-    for (;;) {
-        {
-            const long long t0 = rec2 ? clock64() : 0;
-            mbar_wait(&sm.cready[slot], cr_par);
-            if (rec2) t_top += clock64() - t0;
-        }
-        cr_par ^= 1;
-        const int tile = sm.slot_tile[slot];
-        if (tile < 0) break;
-        // constants of sub-block i of a step (i = 0 is the top one): SubPack nsub - 1 - i, rows below = 8 (7 - i % 8)
-        auto load_sub = [&](int i, uint32_t qq) {
+    // Constants of the sub-blocks, double-buffered per warpgroup: load number q goes to buffer q & 1.  q_cons counts the
+    // loads consumed and released (every thread); the issuing side is thread 0 of the warpgroup alone, its state in
+    // sm.iss[wg].  Loads are issued in processing order, at most two ahead, across job boundaries when the next job is
+    // certain (PanelIssue::nstart): its first sub-blocks are then in flight before the job begins.
+    uint32_t q_cons = 0;
+    PanelIssue& iss = sm.iss[wg];
+    // constants of sub-block i of a step (i = 0 is the top one): SubPack nsub - 1 - i, rows below = 8 (7 - i % 8)
+    auto topup = [&]() {   // thread 0 of the warpgroup
+        uint32_t qi = iss.q_iss;
+        int cur = iss.cur, nj = iss.nj;
+        const int end = iss.end, nstart = iss.nstart;
+        while (qi - q_cons < 2u) {
+            int i;
+            if (cur < end) i = cur++;
+            else if (nstart >= 0 && nstart + nj < (nstart / (kPair / kSubW) + 1) * (kPair / kSubW)) i = nstart + nj++;
+            else break;
             const uint32_t nb = sub_bytes(kSubW * (7 - (i & 7)));
-            mbar_arrive_expect_tx(&sm.cfull[slot][qq & 1], nb);
-            bulk_g2s(&sm.sub[slot][qq & 1], &P.subs[nsub - 1 - i], nb, &sm.cfull[slot][qq & 1]);
-        };
+            mbar_arrive_expect_tx(&sm.cfull[wg][qi & 1], nb);
+            bulk_g2s(&sm.sub[wg][qi & 1], &P.subs[nsub - 1 - i], nb, &sm.cfull[wg][qi & 1]);
+            qi++;
+        }
+        iss.q_iss = qi;
+        iss.cur = cur;
+        iss.nj = nj;
+    };
+    if (sl == 0) iss = PanelIssue{0u, 0, 0, -1, 0};
+    PanelSlot* pst = sm.pst[wg][sl >> 5];
+    if (lane == 0) {
+        pst[0] = PanelSlot{-1, 0, 0, 0u};
+        pst[1] = PanelSlot{TPW == 2 ? -1 : -2, 0, 0, 0u};
+    }
+    __syncwarp();
+    // TPW = 1: these stay in registers from pair to pair
+    double d2a = 0.0, lza = 0.0;
+    long long upos = 0;   // replay: position inside this unit's recorded stream
+    int k = 0;
+    for (;;) {
+        PanelSlot me = pst[k];
+        if (me.tile == -2) {
+            if (TPW == 1) break;
+            k ^= 1;
+            me = pst[k];
+            if (me.tile == -2) break;
+        }
+        const int slot = wg * TPW + k;
+        {
+            const long long t0 = rec ? clock64() : 0;
+            mbar_wait(&sm.cready[slot], me.crp);
+            if (rec) t_cwait += clock64() - t0;
+        }
+        me.crp ^= 1;
+        const bool tile_start = me.tile < 0;
+        if (tile_start) {
+            me.tile = sm.slot_tile[slot];
+            me.step = 0;
+            me.pair = 0;
+            if (me.tile == -3) me.tile = -1;       // not started yet (staggered start): ask again at the next turn
+            else if (me.tile < 0) me.tile = -2;
+        }
+        __syncwarp();
+        if (lane == 0) pst[k] = me;   // re-read at the end of the job: nothing of it stays in registers meanwhile
+        __syncwarp();
+        if (me.tile < 0) {
+            if (TPW == 2 && me.tile == -1) k ^= 1;
+            continue;
+        }
+        const int tile = me.tile;
+        const int step = me.step;
+        const int p = me.pair;
         const int64_t s = (int64_t)tile * kTile + sl;
         // step-parallel proposals: the tile's chains and its step (see ChainArgs::tiles_per_step)
         const uint64_t id = P.first_id + (uint64_t)((!IMHK && P.tiles_per_step) ? (int64_t)(tile % P.tiles_per_step) * kTile + sl : s);
-        // IMHK chain state of this thread's chain (imhk.py:126-177)
-        double lw = 0.0;
-        int loc = 0, acc_n = 0, tot_n = 0;
-        long long upos = 0;   // replay: position inside this unit's recorded stream
-        if (IMHK && s < P.S) {
-            lw = P.lw_cur[s];
-            loc = P.loc[s];
-            if (REPLAY && P.upos) upos = P.upos[s];
-            // the state a call starts from (launches of initialised chains): entry 0 of the log-weight row
-            if (REPLAY && P.logw_out && P.step_off == 0 && !P.first_is_init) P.logw_out[s * (P.call_steps + 1)] = lw;
-        }
         const double* __restrict__ urow = REPLAY ? P.U + (size_t)(s < P.S ? s : 0) * P.u_stride : nullptr;
         // column copy of one chain's coefficients between tiled matrices (predicated per lane, coalesced per row)
         auto copy_column = [&](const double* __restrict__ src, double* __restrict__ dst) {
@@ -814,80 +937,89 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
 #pragma unroll 8
             for (int i = 0; i < P.npad; i++) dst[o + (size_t)i * kRowLd] = src[o + (size_t)i * kRowLd];
         };
-        if (IMHK && P.nsteps == 0) {  // flush only
-            if (loc) copy_column(P.Xbuf[loc - 1], P.Xcur);
-            loc = 0;
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.pdone[slot]);
+        if (REPLAY && tile_start) upos = 0;
+        if (IMHK && tile_start) {
+            if (REPLAY && s < P.S) {
+                if (P.upos) upos = P.upos[s];
+                // the state a call starts from (launches of initialised chains): entry 0 of the log-weight row
+                if (P.logw_out && P.step_off == 0 && !P.first_is_init) P.logw_out[s * (P.call_steps + 1)] = P.lw_cur[s];
+            }
+            if (P.nsteps == 0) {  // flush only: every current state into Xcur
+                if (s < P.S) {
+                    const int loc = P.loc[s];
+                    if (loc) copy_column(P.Xbuf[loc - 1], P.Xcur);
+                    P.loc[s] = 0;
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(&sm.pdone[slot]);
+                    pst[k].tile = -1;
+                }
+                __syncwarp();
+                if (TPW == 2) k ^= 1;
+                continue;
+            }
         }
-#pragma unroll 1
-        for (int step = 0; step < P.nsteps; step++) {
-        if (step > 0) {
-            mbar_wait(&sm.cready[slot], cr_par);
-            cr_par ^= 1;
+        if (sl == 0) {
+            // first sub-block of the job that follows this one, or -1 when that depends on a tile assignment not made yet
+            int nstart = -1;
+            const PanelSlot ot = pst[k ^ 1];
+            if (TPW == 2 && ot.tile != -2) {
+                if (ot.tile >= 0) nstart = ot.pair == 0 ? P.skip0 : ot.pair * (kPair / kSubW);
+            } else if (p + 1 < npairs) {
+                nstart = (p + 1) * (kPair / kSubW);
+            } else if (step + 1 < P.nsteps) {
+                nstart = P.skip0;
+            }
+            // the job starts at sub-block skip0 / 8 p; iss.nj of its sub-blocks were requested during the previous job
+            iss.cur = (p == 0 ? P.skip0 : p * (kPair / kSubW)) + iss.nj;
+            iss.end = (p + 1) * (kPair / kSubW);
+            iss.nstart = nstart;
+            iss.nj = 0;
+            topup();
         }
-        if (sl == 0) {  // every warp of the slot has finished the previous step (pdone -> scheduler -> cready)
-            load_sub(P.skip0, q);
-            if (P.skip0 + 1 < nsub) load_sub(P.skip0 + 1, q + 1);
-        }
-        int isub = P.skip0;
         const uint32_t tagv = P.tag + (uint32_t)step + ((!IMHK && P.tiles_per_step) ? (uint32_t)(tile / P.tiles_per_step) : 0u);
         double* __restrict__ xtile = P.Xbuf[tagv & 1] + (size_t)tile * P.npad * kRowLd;
         double* __restrict__ xt = xtile + sl;
-        double d2a = 0.0, lza = 0.0;
-        uint4 w = make_uint4(0, 0, 0, 0);
-        int wpair = -1;
-#pragma unroll 1
-        for (int p = 0; p < npairs; p++) {
-            if (p > 0) {
-                const long long t0 = rec ? clock64() : 0;
-                mbar_wait(&sm.cready[slot], cr_par);
-                if (rec) t_cwait += clock64() - t0;
-                cr_par ^= 1;
-            }
+        if (p == 0) {
+            d2a = 0.0;
+            lza = 0.0;
+        } else if (TPW == 2) {  // partial sums of the pairs above, parked in the output arrays
+            if (WANT_D2) d2a = P.d2[s];
+            if (WANT_LZ) lza = P.lz[s];
+        }
+        uint32_t wz = 0, ww = 0;
+        bool wfresh = true;
+        {
             const int lo = P.npad - kPair * (p + 1);
             const int base_top = kPair - kSubW - (p == 0 ? P.skip0 * kSubW : 0);   // first sub-block with a coordinate < n
             double c[kSubW];
             {
                 const double* xl = xt + (size_t)(lo + base_top) * kRowLd;
 #pragma unroll
-                for (int k = 0; k < kSubW; k++) c[k] = __ldcg(xl + (size_t)k * kRowLd);
+                for (int kk = 0; kk < kSubW; kk++) c[kk] = __ldcg(xl + (size_t)kk * kRowLd);
             }
 #pragma unroll 1
             for (int base = base_top; base >= 0; base -= kSubW) {
-                const int buf = q & 1;
-                // done with this buffer: the last of the slot's four warps to say so refills it with the constants of
-                // the sub-block after next (no warpgroup-wide barrier in the coordinate loop)
-                auto release_sub = [&](int b) {
-#if !LGS_CHAIN_NOBAR
+                const int buf = q_cons & 1;
+                // done with this buffer: once all four warps of the warpgroup say so it is refilled with the constants
+                // of the sub-block after next
+                auto release_sub = [&]() {
                     {
                         const long long t0 = rec2 ? clock64() : 0;
-                        named_bar_sync(1 + slot, 128);
+                        named_bar_sync(1 + wg, 128);
                         if (rec2) t_bar += clock64() - t0;
                     }
-                    if (sl == 0 && isub + 2 < nsub) load_sub(isub + 2, q + 1);
-                    isub++;
-                    return;
-#endif
-                    __syncwarp();
-                    if (lane == 0) {
-                        __threadfence_block();
-                        if (atomicAdd(&sm.cdone[slot][b], 1) == 3) {
-                            sm.cdone[slot][b] = 0;
-                            if (isub + 2 < nsub) load_sub(isub + 2, q + 1);  // q was already advanced: (q + 1) & 1 == b
-                        }
-                    }
-                    __syncwarp();
-                    isub++;
+                    q_cons++;
+                    if (sl == 0) topup();
                 };
                 {
                     const long long t0 = rec2 ? clock64() : 0;
-                    mbar_wait(&sm.cfull[slot][buf], (q >> 1) & 1);
+                    mbar_wait(&sm.cfull[wg][buf], (q_cons >> 1) & 1);
                     if (rec2) t_cfull += clock64() - t0;
                 }
-                q++;
-                const SubPack& sp = sm.sub[slot][buf];
+                const SubPack& sp = sm.sub[wg][buf];
                 double* __restrict__ xp = xt + (size_t)(lo + base + kSubW - 1) * kRowLd;
 #pragma unroll 1
                 for (int j = kSubW - 1; j >= 0; j--, xp -= kRowLd) {
@@ -909,29 +1041,29 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                         else if (P.fallback && s < P.S) atomicAdd(P.fallback, 1);
                         if (WANT_LZ) lza += lse;
                     } else {
-                        if ((ci.z >> 1) != wpair) {
-                            wpair = ci.z >> 1;
-                            w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)wpair, tagv);
-                        }
+                        // one Philox call serves the draws 2m and 2m + 1: computed at the even one (or at the odd one
+                        // when a job starts there), its second half kept for the odd one
                         const bool odd = ci.z & 1;
-                        const uint32_t uhi = odd ? w.z : w.x, ulo = odd ? w.w : w.y;
+                        uint32_t uhi = wz, ulo = ww;
+                        if (!odd || wfresh) {
+                            const uint4 w = gen((uint32_t)id, (uint32_t)(id >> 32), (uint32_t)(ci.z >> 1), tagv);
+                            wfresh = false;
+                            wz = w.z;
+                            ww = w.w;
+                            uhi = odd ? w.z : w.x;
+                            ulo = odd ? w.w : w.y;
+                        }
                         const int kind = ci.x & 3;
                         bool done = false;
-                        float dlf;
-#if LGS_CHAIN_INTDELTA
-                        const bool dl_ok = rint_delta_f32(mean, &dlf);
-#else
-                        const bool dl_ok = true;
-                        dlf = (float)(rmean - mean);
-#endif
-                        if (ci.x <= 1 && dl_ok) {  // smooth regime, eligible for the FP32 screen
+                        const float dlf = (float)(rmean - mean);
+                        if (ci.x <= 1) {  // smooth regime, eligible for the FP32 screen
                             // no FP64 instruction between the window update above and x below: a panel warp's first
                             // FP64 instruction after a stretch of other work waits for a whole DMMA burst
                             float off, corr;
                             done = samplez_smooth_screen(dlf, sp.cf[j], kind, ci.y, uhi, &off, &corr);
                             x = rmean + (double)off;
                             if (WANT_LZ && done) lza += cc.lognz + (double)corr;
-                        } else if (WIDE && !WANT_LZ && ci.x == 3 && dl_ok) {
+                        } else if (WIDE && !WANT_LZ && ci.x == 3) {
                             // wide truncated window: FP32 screen of the closed-form draw (the exact-weight
                             // instantiations need log Z in FP64 and stay on the FP64 path)
                             float off;
@@ -965,7 +1097,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     c[0] = 0.0;
                 }
                 if (base == 0) {
-                    release_sub(buf);
+                    release_sub();
                     continue;
                 }
                 // Contribution of the sub-block to the rows below it (rows [0, base) of the pair) as warp-level DMMA:
@@ -1018,74 +1150,96 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                             *reinterpret_cast<double2*>(r_hi + nt * 8) = make_double2(d[nt][2], d[nt][3]);
                     }
                 }
-                release_sub(buf);
+                release_sub();
 #pragma unroll
-                for (int k = 0; k < kSubW; k++) c[k] = xs[k * kRowLd];
+                for (int kk = 0; kk < kSubW; kk++) c[kk] = xs[kk * kRowLd];
             }
-            if (IMHK && p == npairs - 1) {
-                // imhk.py:102-124 + 156-174.  Reference weights: log rho(v) - log q(v) is the constant sum_lognorm
-                // here (both are the same sum r_ii^2 (x_i - m_i)^2 / (2 sigma^2)): always accepted, as the reference.
-                const int buf = 1 + (int)(tagv & 1);
-                const double lw_prop = P.exact ? lza : P.sum_lognorm;
-                if (P.first_is_init && step == 0) {
+        }
+        const PanelSlot fin = pst[k];
+        const bool last_pair = fin.pair == npairs - 1;
+        if (IMHK && last_pair) {
+            const int step = fin.step;
+            // imhk.py:102-124 + 156-174.  Reference weights: log rho(v) - log q(v) is the constant sum_lognorm
+            // here (both are the same sum r_ii^2 (x_i - m_i)^2 / (2 sigma^2)): always accepted, as the reference.
+            // The chain's state (log weight, location byte, counters) lives in its arrays between steps.
+            const int buf = 1 + (int)(tagv & 1);
+            const double lw_prop = P.exact ? lza : P.sum_lognorm;
+            const bool live = s < P.S;
+            double lw = live ? P.lw_cur[s] : 0.0;
+            int loc = live ? (int)P.loc[s] : 0;
+            if (P.first_is_init && step == 0) {
+                lw = lw_prop;
+                loc = buf;
+                if (REPLAY && P.logw_out && live) P.logw_out[s * (P.call_steps + 1)] = lw;
+            } else {
+                bool acc = true;
+                if (REPLAY) {  // imhk.py:156-174 on the recorded uniform (always drawn, imhk.py:167)
+                    const double ua = live ? __ldg(urow + upos) : 0.0;
+                    upos++;
+                    const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
+                    acc = ua < ratio;
+                    const int64_t kk = P.step_off + step - (P.first_is_init ? 1 : 0);
+                    if (live) {
+                        if (P.accept_out) P.accept_out[s * P.call_steps + kk] = acc ? 1 : 0;
+                        if (P.logw_out) P.logw_out[s * (P.call_steps + 1) + kk + 1] = lw_prop;
+                    }
+                } else if (P.exact) {
+                    const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
+                    acc = philox_uniform(gen, id, kAcceptDraw, tagv) < ratio;
+                }
+                if (live) {
+                    if (acc) P.counts[2 * s] += 1;
+                    P.counts[2 * s + 1] += 1;
+                }
+                if (acc) {
                     lw = lw_prop;
                     loc = buf;
-                    if (REPLAY && P.logw_out && s < P.S) P.logw_out[s * (P.call_steps + 1)] = lw;
-                } else {
-                    bool acc = true;
-                    if (REPLAY) {  // imhk.py:156-174 on the recorded uniform (always drawn, imhk.py:167)
-                        const double ua = s < P.S ? __ldg(urow + upos) : 0.0;
-                        upos++;
-                        const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
-                        acc = ua < ratio;
-                        const int64_t k = P.step_off + step - (P.first_is_init ? 1 : 0);
-                        if (s < P.S) {
-                            if (P.accept_out) P.accept_out[s * P.call_steps + k] = acc ? 1 : 0;
-                            if (P.logw_out) P.logw_out[s * (P.call_steps + 1) + k + 1] = lw_prop;
-                        }
-                    } else if (P.exact) {
-                        const double ratio = (lw == -INFINITY) ? 1.0 : fmin(1.0, exp(lw_prop - lw));
-                        acc = philox_uniform(gen, id, kAcceptDraw, tagv) < ratio;
-                    }
-                    tot_n++;
-                    if (acc) {
-                        acc_n++;
-                        lw = lw_prop;
-                        loc = buf;
-                    }
-                }
-                // The accepted proposal is not copied: loc records the buffer it lives in.  A state still living in the
-                // buffer the NEXT step draws into moves to Xcur now (before that step's first centers are written);
-                // at a flush every state moves there.
-                const int nbuf = 1 + (int)((tagv + 1) & 1);
-                if (loc && (loc == nbuf || (P.flush && step == P.nsteps - 1))) {
-                    copy_column(P.Xbuf[loc - 1], P.Xcur);
-                    loc = 0;
                 }
             }
-            // the pair's coefficients are read next by bulk copies (async proxy)
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.pdone[slot]);
+            // The accepted proposal is not copied: loc records the buffer it lives in.  A state still living in the
+            // buffer the NEXT step draws into moves to Xcur now (before that step's first centers are written);
+            // at a flush every state moves there.
+            const int nbuf = 1 + (int)((tagv + 1) & 1);
+            if (loc && (loc == nbuf || (P.flush && step == P.nsteps - 1))) {
+                copy_column(P.Xbuf[loc - 1], P.Xcur);
+                loc = 0;
+            }
+            if (live) {
+                P.lw_cur[s] = lw;
+                P.loc[s] = (uint8_t)loc;
+                if (REPLAY && P.upos && step == P.nsteps - 1) P.upos[s] = upos;
+            }
         }
         if (!IMHK) {
-            // sum (x_i - m_i)^2 / (2 sigma_i^2) = sum r_ii^2 (x_i - m_i)^2 / (2 sigma^2)
-            if (WANT_D2) {
-                P.lp[s] = d2a * P.inv_two_sigma2;
-                P.d2[s] = d2a;
+            if (last_pair) {
+                // sum (x_i - m_i)^2 / (2 sigma_i^2) = sum r_ii^2 (x_i - m_i)^2 / (2 sigma^2)
+                if (WANT_D2) {
+                    P.lp[s] = d2a * P.inv_two_sigma2;
+                    P.d2[s] = d2a;
+                }
+                if (WANT_LZ) P.lz[s] = lza;
+            } else if (TPW == 2) {
+                if (WANT_D2) P.d2[s] = d2a;
+                if (WANT_LZ) P.lz[s] = lza;
             }
-            if (WANT_LZ) P.lz[s] = lza;
+        } else if (TPW == 2 && WANT_LZ && !last_pair) {
+            P.lz[s] = lza;
         }
-        }  // steps
-        if (IMHK && s < P.S) {
-            P.lw_cur[s] = lw;
-            P.loc[s] = (uint8_t)loc;
-            if (REPLAY && P.upos) P.upos[s] = upos;
-            if (tot_n) {
-                P.counts[2 * s] += acc_n;
-                P.counts[2 * s + 1] += tot_n;
+        // the pair's coefficients are read next by bulk copies (async proxy)
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.pdone[slot]);
+        // the slot's next job
+        if (lane == 0) {
+            PanelSlot nx = fin;
+            if (++nx.pair == npairs) {
+                nx.pair = 0;
+                if (++nx.step >= P.nsteps) nx.tile = -1;   // the tile is finished: the slot waits for its next assignment
             }
+            pst[k] = nx;
         }
+        __syncwarp();
+        if (TPW == 2) k ^= 1;
     }
     if (rec) {
         P.stats[blockIdx.x * 12 + 5] = (unsigned long long)(clock64() - t_begin);
@@ -1105,12 +1259,13 @@ __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_c
             mbar_init(&sm.full[i], 1);
             mbar_init(&sm.empty[i], kDmmaThreads / 32);
         }
-        for (int s = 0; s < kSlots; s++) {
+        for (int s = 0; s < kMaxSlots; s++) {
             mbar_init(&sm.cready[s], kDmmaThreads / 32);
             mbar_init(&sm.pdone[s], 4);
+        }
+        for (int s = 0; s < kWgs; s++) {
             mbar_init(&sm.cfull[s][0], 1);
             mbar_init(&sm.cfull[s][1], 1);
-            sm.cdone[s][0] = sm.cdone[s][1] = 0;
         }
         fence_mbar_init();
     }
@@ -1121,7 +1276,7 @@ __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_c
         dmma_role(sm, P);
     } else if (tid >= kProdBase && tid < kProdBase + kProdThreads) {
         reg_dec<kRegsProd>();
-        if (tid == kProdBase) producer_role(sm, P);
+        if (tid == kProdBase) producer_role(sm, P, kWgs * (REPLAY ? 1 : kTpw));
     } else {
         reg_dec<kRegsPanel>();
         panel_role<WANT_LZ, WANT_D2, IMHK, WIDE, REPLAY>(sm, P, (tid - kPanelBase) >> 7);
@@ -1408,7 +1563,7 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
         int by_n = 3 * 1024 / npad;
         by_n = by_n < 3 ? 3 : by_n > 24 ? 24 : by_n;
         const int rounds = env ? atoi(env) : by_n;
-        cc.batch = (int64_t)(bc.sm_count > 0 ? bc.sm_count : 148) * kTile * kSlots * (rounds > 0 ? rounds : 3);
+        cc.batch = (int64_t)(bc.sm_count > 0 ? bc.sm_count : 148) * kTile * kWgs * (rounds > 0 ? rounds : 3);
     }
     cc.wide = false;
     for (int i = 0; i < bc.n; i++) cc.wide = cc.wide || hc.kind[i] == 3;
@@ -1442,6 +1597,14 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     a.skip0 = (cc.npad - (bc.n + kSubW - 1) / kSubW * kSubW) / kSubW;
     if (!(a.tiles_per_step > 0 && a.ntiles > 0)) a.ntiles = (int)((a.S + kTile - 1) / kTile);
     a.want_lz = want_lz ? 1 : 0;
+    {
+        static const int la = [] { const char* v = getenv("LGS_CHAIN_LOOKAHEAD"); return v ? atoi(v) : 0; }();
+        a.lookahead = la;
+        // staggered start: IMHK launches and proposal-only batches (+3.9 % / +1.5 %); a Klein batch with lattice points
+        // has filler for the top of its steps and only pays the later start (-1 %)
+        static const int sg = [] { const char* v = getenv("LGS_CHAIN_STAGGER"); return v ? atoi(v) : -1; }();
+        a.stagger = sg >= 0 ? sg : ((a.nsteps > 1 || !(a.V || a.V16)) ? 1 : 0);
+    }
     const int sms = bc.sm_count > 0 ? bc.sm_count : 148;
     const int grid = a.ntiles < sms ? a.ntiles : sms;
     {
@@ -1616,6 +1779,8 @@ static void chain_imhk_args(BlockedCtx& bc, ChainSet& cs, ChainArgs& a, int weig
     ChainCtx& cc = bc.chain;
     a.Xbuf[0] = cc.work[1].X;   // proposals of even tags (buffer id 1)
     a.Xbuf[1] = cc.work[2].X;   // proposals of odd tags (buffer id 2)
+    a.lp = cc.work[1].lp; a.d2 = cc.work[1].d2;
+    a.lz = cc.work[1].lz;       // exact weights: the proposal's partial log-weight is parked here between pairs
     a.Xcur = cs.Xcur;
     a.loc = cs.flags;
     a.lw_cur = cs.logw;
