@@ -64,6 +64,28 @@ __device__ __forceinline__ bool mbar_test_wait(uint64_t* b, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// the same on a precomputed shared-memory address
+__device__ __forceinline__ void mbar_wait_u32(uint32_t addr, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+            : "=r"(ok)
+            : "r"(addr), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void mbar_arrive_u32(uint32_t addr) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void lds_v4(uint32_t addr, int& a, int& b, int& c, int& d) {
+    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr));
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
     while (!mbar_try_wait(b, parity)) {
     }
@@ -100,14 +122,6 @@ __device__ __forceinline__ void dmma_16x8x8(double (&d)[4], const double (&a)[4]
         : "d"(a[0]), "d"(a[1]), "d"(a[2]), "d"(a[3]), "d"(b[0]), "d"(b[1]));
 }
 
-// DMMA.8x8x4, the SASS unit an m16n8k8 is split into.  volatile: the issue order of these is chosen by hand, see
-// LGS_CHAIN_DEPDIST.  Fragments: a = A[g][t], b = B[t][g], d = C[g][2t], C[g][2t+1]  (g = lane / 4, t = lane % 4)
-[[maybe_unused]] __device__ __forceinline__ void dmma_8x8x4(double (&d)[2], const double a, const double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-                 : "+d"(d[0]), "+d"(d[1])
-                 : "d"(a), "d"(b));
-}
-
 // ---------------------------------------------------------------------------------------------------------
 // geometry
 // ---------------------------------------------------------------------------------------------------------
@@ -121,10 +135,7 @@ constexpr int kBK = LGS_CHAIN_BK;     // contraction depth of one stage
 constexpr int kLdA = kBK + 4;         // 20: row stride of an A sliver (conflict-free LDS.64 fragment loads)
 constexpr int kSubW = 8;              // coordinates per sub-block of the panel (width of the register window)
 #ifndef LGS_CHAIN_TPW
-#define LGS_CHAIN_TPW 2   // tiles a panel warpgroup alternates between (1: the round-1 kernel, three tiles in flight)
-#endif
-#ifndef LGS_CHAIN_DEPDIST
-#define LGS_CHAIN_DEPDIST 0   // 0: m16n8k8 in compiler order; D > 0: m8n8k4, dependent instructions D places apart
+#define LGS_CHAIN_TPW 2   // most tiles a panel warpgroup alternates between (ChainArgs::tpw chooses 1 or 2 per launch)
 #endif
 #ifndef LGS_CHAIN_STAGES
 #define LGS_CHAIN_STAGES 5
@@ -265,6 +276,7 @@ struct ChainArgs {
     int lookahead;          // centers of a pair in two items (see F_PART_OUT): 0 never, 1 always, 2 when the DMMA warps
                             // would otherwise idle
     int stagger;            // slots started a sixth of a step apart (producer_role)
+    int tpw;                // tiles per panel warpgroup: 1 or 2 (kTpw)
     int* pt_list;
     unsigned* pt_ctr;
     int tiles_per_step;
@@ -326,101 +338,73 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
     const int warp = tid >> 5, lane = tid & 31;
     const int wm = warp >> 2, wn = warp & 3;
     const int g = lane >> 2, t = lane & 3;
-#if LGS_CHAIN_DEPDIST
-    double acc[4][4][2];   // [m8 tile][n8 tile]: rows 8 mt + g, columns 8 nt + 2t, 2t + 1
-#else
     double acc[2][4][4];
-#endif
+    // Shared-memory addresses as 32-bit offsets, computed once: the stage loop's bookkeeping (barrier wait, header read,
+    // fragment addresses) sits between the last DMMA of a stage and the first of the next on every warp, and derived
+    // from the generic `sm` it cost a special-register read, a window-base computation and a re-derivation of the lane's
+    // fragment offsets from threadIdx per stage (ncu, profiles/r02e_stall_summary_by_role.txt: 15 % of the DMMA warps'
+    // samples, a third of it the genuine wait for a full stage).
+    // (made opaque to the compiler, which otherwise re-derives them from %tid inside the loop rather than hold three
+    // registers)
+    uint32_t sbase = smem_u32(&sm);
+    uint32_t a_thr = smem_u32(&sm.A[0][wm * 32 + g][t]);   // + stage * kABytes + (16 mt + 8 h) rows + (kk + 4 c) doubles
+    uint32_t b_thr = smem_u32(&sm.B[0][t][wn * 32 + g]);   // + stage * kBBytes + (kk + 4 c) rows + 8 nt doubles
+    asm volatile("" : "+r"(sbase), "+r"(a_thr), "+r"(b_thr));
+    const uint32_t full0 = sbase + (uint32_t)offsetof(ChainSmem, full), empty0 = sbase + (uint32_t)offsetof(ChainSmem, empty),
+                   hdr0 = sbase + (uint32_t)offsetof(ChainSmem, hdr);
+    uint32_t stage = 0, par = 0;
     uint32_t it = 0;
     const bool rec = kStatsBuild && P.stats && tid == 0;
     long long t_wait = 0;
     const long long t_begin = rec ? clock64() : 0;
-    for (;; it++) {
-        const int stage = it % kStages;
+    for (;; it++, stage = (stage + 1 == (uint32_t)kStages) ? 0u : stage + 1, par ^= (stage == 0u) ? 1u : 0u) {
         if (rec) {
             const long long t0 = clock64();
-            mbar_wait(&sm.full[stage], (it / kStages) & 1);
+            mbar_wait_u32(full0 + stage * 8u, par);
             t_wait += clock64() - t0;
         } else {
-            mbar_wait(&sm.full[stage], (it / kStages) & 1);
+            mbar_wait_u32(full0 + stage * 8u, par);
         }
-        const StageHdr h = sm.hdr[stage];
+        StageHdr h;
+        lds_v4(hdr0 + stage * (uint32_t)sizeof(StageHdr), h.flags, h.slot, h.r0, h.tile);
         if (h.flags & F_EXIT) break;
         if (h.flags & F_FIRST) {
 #pragma unroll
-            for (int a = 0; a < (int)(sizeof(acc) / sizeof(acc[0])); a++)
+            for (int a = 0; a < 2; a++)
 #pragma unroll
                 for (int b = 0; b < 4; b++)
 #pragma unroll
-                    for (int c = 0; c < (int)(sizeof(acc[0][0]) / sizeof(double)); c++) acc[a][b][c] = 0.0;
+                    for (int c = 0; c < 4; c++) acc[a][b][c] = 0.0;
         }
-        {
-            if (!(h.flags & F_NODATA)) {
-#if LGS_CHAIN_DEPDIST
-                // One DMMA.8x8x4 per instruction, issued so that an instruction depends on the one LGS_CHAIN_DEPDIST
-                // places before it.  A warp that issues back-to-back independent DMMAs keeps the scheduler's greedy
-                // slot for its whole burst (1024 cycles per stage) and the panel warps' FP64 instructions wait that
-                // long; short dependency chains make the DMMA warps hand the pipe over after every few instructions.
-                constexpr int D = LGS_CHAIN_DEPDIST;
+        if (!(h.flags & F_NODATA)) {
+            const uint32_t as = a_thr + stage * kABytes, bs = b_thr + stage * kBBytes;
 #pragma unroll
-                for (int kh = 0; kh < kBK; kh += 8) {
-                    double af[4][2], bf[4][2];   // [tile][k4 step]
+            for (int kk = 0; kk < kBK; kk += 8) {
+                double af[2][4], bf[4][2];
 #pragma unroll
-                    for (int mt = 0; mt < 4; mt++) {
-                        af[mt][0] = sm.A[stage][wm * 32 + mt * 8 + g][kh + t];
-                        af[mt][1] = sm.A[stage][wm * 32 + mt * 8 + g][kh + 4 + t];
-                    }
-#pragma unroll
-                    for (int nt = 0; nt < 4; nt++) {
-                        bf[nt][0] = sm.B[stage][kh + t][wn * 32 + nt * 8 + g];
-                        bf[nt][1] = sm.B[stage][kh + 4 + t][wn * 32 + nt * 8 + g];
-                    }
-#pragma unroll
-                    for (int grp = 0; grp < 16; grp += D)
-#pragma unroll
-                        for (int ks = 0; ks < 2; ks++)
-#pragma unroll
-                            for (int i = 0; i < D; i++) {
-                                const int blk = grp + i, mt = blk >> 2, nt = blk & 3;
-                                dmma_8x8x4(acc[mt][nt], af[mt][ks], bf[nt][ks]);
-                            }
+                for (int mt = 0; mt < 2; mt++) {
+                    af[mt][0] = lds_f64(as + (uint32_t)(((mt * 16) * kLdA + kk) * 8));
+                    af[mt][1] = lds_f64(as + (uint32_t)(((mt * 16 + 8) * kLdA + kk) * 8));
+                    af[mt][2] = lds_f64(as + (uint32_t)(((mt * 16) * kLdA + kk + 4) * 8));
+                    af[mt][3] = lds_f64(as + (uint32_t)(((mt * 16 + 8) * kLdA + kk + 4) * 8));
                 }
-#else
 #pragma unroll
-                for (int kk = 0; kk < kBK; kk += 8) {
-                    double af[2][4], bf[4][2];
-#pragma unroll
-                    for (int mt = 0; mt < 2; mt++) {
-                        const double* ap = &sm.A[stage][wm * 32 + mt * 16 + g][kk + t];
-                        af[mt][0] = ap[0];
-                        af[mt][1] = ap[8 * kLdA];
-                        af[mt][2] = ap[4];
-                        af[mt][3] = ap[8 * kLdA + 4];
-                    }
-#pragma unroll
-                    for (int nt = 0; nt < 4; nt++) {
-                        const double* bp = &sm.B[stage][kk + t][wn * 32 + nt * 8 + g];
-                        bf[nt][0] = bp[0];
-                        bf[nt][1] = bp[4 * kRowLd];
-                    }
-#pragma unroll
-                    for (int mt = 0; mt < 2; mt++)
-#pragma unroll
-                        for (int nt = 0; nt < 4; nt++) dmma_16x8x8(acc[mt][nt], af[mt], bf[nt]);
+                for (int nt = 0; nt < 4; nt++) {
+                    bf[nt][0] = lds_f64(bs + (uint32_t)((kk * kRowLd + nt * 8) * 8));
+                    bf[nt][1] = lds_f64(bs + (uint32_t)(((kk + 4) * kRowLd + nt * 8) * 8));
                 }
-#endif
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int nt = 0; nt < 4; nt++) dmma_16x8x8(acc[mt][nt], af[mt], bf[nt]);
             }
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[stage]);
+        if (lane == 0) mbar_arrive_u32(empty0 + stage * 8u);
         if (!(h.flags & F_LAST)) continue;
         if (!(h.flags & F_NOSTORE)) {
             // fragment (mt, nt): rows g / g+8 of the 16-row tile, columns 2t, 2t+1 of the 8-column tile
-#if LGS_CHAIN_DEPDIST
-#define LGS_ACC(mt, hh, nt, c) acc[(mt) * 2 + (hh)][nt][c]
-#else
 #define LGS_ACC(mt, hh, nt, c) acc[mt][nt][(hh) * 2 + (c)]
-#endif
             if ((h.flags & F_POINT) && P.V16) {
                 const int64_t s0 = (int64_t)h.tile * kTile;
                 int16_t (*stg)[40] = sm.pk16[warp];
@@ -835,7 +819,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     // the other tile.  Nothing per-thread survives a job in registers except with TPW = 1: the partial log-density
     // sums are parked in their output arrays, the chain state (log weight, location, counters) is read and written
     // back around the accept test, the window is reloaded from the workspace at every pair as before.
-    constexpr int TPW = REPLAY ? 1 : kTpw;
+    const int TPW = REPLAY ? 1 : P.tpw;   // 1 or 2, the same for the whole launch
     const int sl = (threadIdx.x - kPanelBase) & 127;
     const int lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
@@ -1276,7 +1260,7 @@ __global__ void __launch_bounds__(kThreads, 1) klein_chain_kernel(const __grid_c
         dmma_role(sm, P);
     } else if (tid >= kProdBase && tid < kProdBase + kProdThreads) {
         reg_dec<kRegsProd>();
-        if (tid == kProdBase) producer_role(sm, P, kWgs * (REPLAY ? 1 : kTpw));
+        if (tid == kProdBase) producer_role(sm, P, kWgs * (REPLAY ? 1 : P.tpw));
     } else {
         reg_dec<kRegsPanel>();
         panel_role<WANT_LZ, WANT_D2, IMHK, WIDE, REPLAY>(sm, P, (tid - kPanelBase) >> 7);
@@ -1604,6 +1588,14 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
         // has filler for the top of its steps and only pays the later start (-1 %)
         static const int sg = [] { const char* v = getenv("LGS_CHAIN_STAGGER"); return v ? atoi(v) : -1; }();
         a.stagger = sg >= 0 ? sg : ((a.nsteps > 1 || !(a.V || a.V16)) ? 1 : 0);
+        // Two tiles per panel warpgroup where nothing else hides the wait for a pair's centers: IMHK launches (nine steps
+        // out of ten have no lattice points to contract: 81.0 -> 74.0 ms per 10 steps at n = 1024), proposal-only batches
+        // (7.74 -> 6.83 ms), and tiles so short that the hand-over to the next tile shows (n <= 32: +8 %).  A Klein batch
+        // with lattice points has that filler and is 1-3 % faster with one tile per warpgroup; its finished tiles also
+        // reach the host transport sooner (mapped int16 route: 19.6 against 22.3 ms per call).
+        static const int tp = [] { const char* v = getenv("LGS_CHAIN_TPW"); return v ? atoi(v) : 0; }();
+        a.tpw = (tp == 1 || tp == 2) ? tp : ((a.nsteps > 1 || (a.nsteps == 1 && !(a.V || a.V16)) || bc.n <= 32) ? 2 : 1);
+        if (a.tpw > kTpw) a.tpw = kTpw;
     }
     const int sms = bc.sm_count > 0 ? bc.sm_count : 148;
     const int grid = a.ntiles < sms ? a.ntiles : sms;
