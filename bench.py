@@ -29,6 +29,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_RING, Q, SIGMA = 512, 12289, 165.74          # NTRU n = 512, q = 12289; sampler sigma = Falcon-512's
+SIGMA_REJECT = 55.0                            # exact-weight IMHK leg that rejects (acceptance ~0.5-0.9 on this lattice)
 # config.workload of BOTH arms (the reference arm times the CPU implementation of the same path on this workload)
 WORKLOAD = (f"NTRU n={N_RING} q={Q} trapdoor basis (1024-dim, f,g ~ D_Z,4.05 = BASELINE's key-generation sigma, exact "
             f"NTRUSolve, seed 0), sampler sigma={SIGMA}, Klein sampling + IMHK")
@@ -438,7 +439,7 @@ def main():
         Vk = torch.empty((C, 1, n), dtype=torch.float64, device="cuda")
         dims = np.array([0, 1, n // 2, n - 1], dtype=np.int32)
 
-        def imhk_leg(weight, steps):
+        def imhk_leg(weight, steps, eng=eng, sigma=SIGMA):
             eng.imhk_reset(C, seed=77, first_chain_id=rank * C)
             counts = torch.zeros((C, 2), dtype=torch.int64, device="cuda")
             hist = torch.zeros((4, 64), dtype=torch.int64, device="cuda")
@@ -447,7 +448,7 @@ def main():
             def imhk_step(k):
                 eng.imhk_run_dev(0, 1, thin, "fast", weight, V=Vk.data_ptr(), stream=stream)
                 # statistics of src/diagnostics (acceptance mean, marginal histograms): accumulate per rank ...
-                eng.histogram_dev(Vk.data_ptr(), C, dims, -8 * SIGMA, SIGMA / 4, 64, hist.data_ptr(), stream=stream)
+                eng.histogram_dev(Vk.data_ptr(), C, dims, -8 * sigma, sigma / 4, 64, hist.data_ptr(), stream=stream)
 
             for w in range(2):
                 imhk_step(w)
@@ -483,6 +484,16 @@ def main():
         # tools/quick_imhk.py runs the same mode where it rejects (sigma = 60: sigma_i ~ 0.5)
         imhk_exact = imhk_leg("exact", max(3, K // 2))
         phase("imhk exact leg")
+        # ... and the same mode where it does reject: the same lattice at sigma = SIGMA_REJECT (sigma_i ~ 0.4-0.55, the
+        # window masses now depend on the centers), i.e. accept / reject, the deferred commit of accepted states and the
+        # exp per step all do work.  sigma_i < 1 takes the generic FP64 SampleZ (samplez_fast), not the FP32-screened one.
+        smp_r = lgs.KleinSampler(lat, SIGMA_REJECT, seed=2027, device=local, path="blocked")
+        imhk_exact["rejecting"] = imhk_leg("exact", max(3, K // 2), eng=smp_r._engine, sigma=SIGMA_REJECT)
+        imhk_exact["rejecting"]["sigma"] = SIGMA_REJECT
+        imhk_exact["rejecting"]["cond_sigma_range"] = [SIGMA_REJECT / lat.max_gram_schmidt_norm,
+                                                       SIGMA_REJECT / lat.min_gram_schmidt_norm]
+        del smp_r
+        phase("imhk exact leg, rejecting sigma")
 
     # ---------------------------------------------------------------- replay through the same kernel (parity mode)
     replay = None

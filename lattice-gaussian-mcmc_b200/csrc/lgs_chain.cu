@@ -135,7 +135,7 @@ constexpr int kBK = LGS_CHAIN_BK;     // contraction depth of one stage
 constexpr int kLdA = kBK + 4;         // 20: row stride of an A sliver (conflict-free LDS.64 fragment loads)
 constexpr int kSubW = 8;              // coordinates per sub-block of the panel (width of the register window)
 #ifndef LGS_CHAIN_TPW
-#define LGS_CHAIN_TPW 2   // most tiles a panel warpgroup alternates between (ChainArgs::tpw chooses 1 or 2 per launch)
+#define LGS_CHAIN_TPW 3   // most tiles a panel warpgroup rotates through (ChainArgs::tpw chooses per launch)
 #endif
 #ifndef LGS_CHAIN_STAGES
 #define LGS_CHAIN_STAGES 5
@@ -203,7 +203,7 @@ struct ChainSmem {
     uint64_t full[kStages], empty[kStages];
     uint64_t cready[kMaxSlots], pdone[kMaxSlots], cfull[kWgs][2];
     int slot_tile[kMaxSlots];
-    PanelSlot pst[kWgs][4][2];         // per panel warp: where each of its warpgroup's slots stands (panel_role)
+    PanelSlot pst[kWgs][4][kTpw];         // per panel warp: where each of its warpgroup's slots stands (panel_role)
     PanelIssue iss[kWgs];              // per warpgroup: the constants loads in flight (thread 0 of the warpgroup only)
     // packed lattice-point output (ChainArgs::V16): per DMMA warp, its 32 samples x 32 rows as int16, one 80-byte
     // row per sample so that a lane reads its sample's 64 bytes as four conflict-free 16-byte words
@@ -214,8 +214,8 @@ static_assert(sizeof(ChainSmem) <= 232448, "ChainSmem exceeds the 227 KB of shar
 struct ChainArgs {
     const double* Rpk;      // packed slivers of R: [npad/64][npad/16][64][20]
     const double* Bpk;      // packed slivers of the basis, same shape
-    const double* tvec;     // [npad]
-    const double* invr;     // [npad] 1 / R_ii (1 on the padding): centers are kept divided by their R_ii
+    const double* tvec;     // [npad] t_i / R_ii
+    int t_zero;             // t = 0 (center c = 0)
     const SubPack* subs;    // [npad/8] sub-block constants, index = first coordinate / 8
     double* Xbuf[2];        // tiled coefficient workspace(s): Klein uses [0]; an IMHK step with Philox tag g draws its
                             // proposal into Xbuf[g & 1]
@@ -275,8 +275,8 @@ struct ChainArgs {
     int gq;
     int lookahead;          // centers of a pair in two items (see F_PART_OUT): 0 never, 1 always, 2 when the DMMA warps
                             // would otherwise idle
-    int stagger;            // slots started a sixth of a step apart (producer_role)
-    int tpw;                // tiles per panel warpgroup: 1 or 2 (kTpw)
+    int stagger;            // slots started 1 / nslots of a step apart (producer_role), in per cent of that spacing; 0: together
+    int tpw;                // tiles per panel warpgroup: 1 .. kTpw
     int* pt_list;
     unsigned* pt_ctr;
     int tiles_per_step;
@@ -482,16 +482,17 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
 #pragma unroll
                     for (int hh = 0; hh < 2; hh++) {
                         const int row = r0 + wm * 32 + mt * 16 + g + hh * 8;
-                        const double tv = P.tvec[row];
-                        const double ir = (h.flags & F_PART_OUT) ? 1.0 : P.invr[row];
+                        // centers are kept divided by their R_ii: the rows of the packed R and t already are (chain_init),
+                        // so the epilogue has nothing to load for the usual center c = 0 (t = 0)
+                        const double tv = P.t_zero ? 0.0 : P.tvec[row];
 #pragma unroll
                         for (int nt = 0; nt < 4; nt++) {
                             const int col = wn * 32 + nt * 8 + t * 2;
                             double2* dst = reinterpret_cast<double2*>(xt + (size_t)row * kRowLd + col);
                             double2 o = make_double2(tv, tv);
                             if (h.flags & F_PART_IN) o = *dst;  // written by these same threads (F_PART_OUT item)
-                            o.x = (o.x - LGS_ACC(mt, hh, nt, 0)) * ir;
-                            o.y = (o.y - LGS_ACC(mt, hh, nt, 1)) * ir;
+                            o.x -= LGS_ACC(mt, hh, nt, 0);
+                            o.y -= LGS_ACC(mt, hh, nt, 1);
                             *dst = o;
                         }
                     }
@@ -638,12 +639,12 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P,
     };
     // Staggered start.  The centers of pair p cost 4 p stages while a panel takes the same time for every pair, so
     // tiles that walk their pairs in phase starve the DMMA warps at the top of a step and queue behind them at the
-    // bottom.  The slots are therefore started 1/6 of a step apart -- warpgroup w's first slot once slot 0 has drawn
-    // w npairs / 6 pairs, a warpgroup's second slot once its first has drawn npairs / 2 -- and the alternation inside
-    // a warpgroup and the equal length of all tiles keep them there for the rest of the launch.  A warpgroup whose
-    // second slot is not started yet is told so at each of its turns (slot_tile = -3) and goes on with the first.
+    // bottom.  The slots are therefore started 1 / nslots of a step apart -- warpgroup w's first slot once slot 0 has
+    // drawn w npairs / nslots pairs, a warpgroup's slot k once its first has drawn k npairs / tpw -- and the rotation
+    // inside a warpgroup and the equal length of all tiles keep them there for the rest of the launch.  A warpgroup's
+    // slot that is not started yet says so at each of its turns (slot_tile = -3) and the warpgroup goes on to the next.
     const int tpw = nslots / kWgs;
-    const bool stagger = P.stagger && npairs >= 2 * nslots && P.nsteps > 0 && P.ntiles >= nslots * G;
+    const bool stagger = P.stagger && npairs >= 12 && P.nsteps > 0 && P.ntiles >= nslots * G;
     int s_jobs[kMaxSlots] = {};           // pairs the slot's panel has drawn since the launch began
     bool s_defer[kMaxSlots] = {};
     auto not_yet = [&](int s) {
@@ -673,19 +674,24 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P,
                     s_jobs[s]++;
                     if (s == 0)
                         for (int w = 1; w < kWgs; w++)
-                            if (s_defer[w * tpw] && s_jobs[0] >= w * npairs / nslots) {
+                            if (s_defer[w * tpw] && s_jobs[0] >= w * npairs * P.stagger / (100 * nslots)) {
                                 s_defer[w * tpw] = false;
                                 assign(w * tpw);
                             }
-                    if (tpw == 2 && !(s & 1) && s_defer[s + 1]) {
-                        // the warpgroup turns to its second slot next: start it, or send it back to this one
-                        const bool ends = s_pair[s] == npairs && s_step[s] + 1 >= P.nsteps && next_tile >= P.ntiles;
-                        if (s_jobs[s] >= npairs / 2 || ends) {
-                            s_defer[s + 1] = false;
-                            assign(s + 1);
-                        } else {
-                            not_yet(s + 1);
+                    // the warpgroup turns to its following slots next: those not started yet are started now (the
+                    // warpgroup's first slot has drawn their share of a step, or there is no tile left to wait for)
+                    // or send the warpgroup on (not_yet), up to the first one that has a tile
+                    const int w0 = s / tpw * tpw;
+                    for (int j = 1; j < tpw; j++) {
+                        const int o = w0 + (s - w0 + j) % tpw;
+                        if (!s_active[o]) continue;
+                        if (!s_defer[o]) break;
+                        if (s_jobs[w0] >= (o - w0) * npairs * P.stagger / (100 * tpw) || next_tile >= P.ntiles) {
+                            s_defer[o] = false;
+                            assign(o);
+                            break;
                         }
+                        not_yet(o);
                     }
                 }
                 if (s_pair[s] == npairs) {
@@ -870,8 +876,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     if (sl == 0) iss = PanelIssue{0u, 0, 0, -1, 0};
     PanelSlot* pst = sm.pst[wg][sl >> 5];
     if (lane == 0) {
-        pst[0] = PanelSlot{-1, 0, 0, 0u};
-        pst[1] = PanelSlot{TPW == 2 ? -1 : -2, 0, 0, 0u};
+        for (int j = 0; j < kTpw; j++) pst[j] = PanelSlot{j < TPW ? -1 : -2, 0, 0, 0u};
     }
     __syncwarp();
     // TPW = 1: these stay in registers from pair to pair
@@ -879,11 +884,15 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     long long upos = 0;   // replay: position inside this unit's recorded stream
     int k = 0;
     for (;;) {
+        // the next slot of the rotation that still has tiles to come
         PanelSlot me = pst[k];
-        if (me.tile == -2) {
-            if (TPW == 1) break;
-            k ^= 1;
-            me = pst[k];
+        {
+            int tries = 1;
+            while (me.tile == -2 && tries < TPW) {
+                k = k + 1 == TPW ? 0 : k + 1;
+                me = pst[k];
+                tries++;
+            }
             if (me.tile == -2) break;
         }
         const int slot = wg * TPW + k;
@@ -905,7 +914,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
         if (lane == 0) pst[k] = me;   // re-read at the end of the job: nothing of it stays in registers meanwhile
         __syncwarp();
         if (me.tile < 0) {
-            if (TPW == 2 && me.tile == -1) k ^= 1;
+            if (me.tile == -1) k = k + 1 == TPW ? 0 : k + 1;
             continue;
         }
         const int tile = me.tile;
@@ -941,15 +950,20 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     pst[k].tile = -1;
                 }
                 __syncwarp();
-                if (TPW == 2) k ^= 1;
+                k = k + 1 == TPW ? 0 : k + 1;
                 continue;
             }
         }
         if (sl == 0) {
             // first sub-block of the job that follows this one, or -1 when that depends on a tile assignment not made yet
             int nstart = -1;
-            const PanelSlot ot = pst[k ^ 1];
-            if (TPW == 2 && ot.tile != -2) {
+            int o = k;   // the slot the rotation reaches next
+            for (int j = 1; j < TPW; j++) {
+                const int c = k + j < TPW ? k + j : k + j - TPW;
+                if (pst[c].tile != -2) { o = c; break; }
+            }
+            if (o != k) {
+                const PanelSlot ot = pst[o];
                 if (ot.tile >= 0) nstart = ot.pair == 0 ? P.skip0 : ot.pair * (kPair / kSubW);
             } else if (p + 1 < npairs) {
                 nstart = (p + 1) * (kPair / kSubW);
@@ -969,7 +983,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
         if (p == 0) {
             d2a = 0.0;
             lza = 0.0;
-        } else if (TPW == 2) {  // partial sums of the pairs above, parked in the output arrays
+        } else if (TPW > 1) {  // partial sums of the pairs above, parked in the output arrays
             if (WANT_D2) d2a = P.d2[s];
             if (WANT_LZ) lza = P.lz[s];
         }
@@ -1202,11 +1216,11 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     P.d2[s] = d2a;
                 }
                 if (WANT_LZ) P.lz[s] = lza;
-            } else if (TPW == 2) {
+            } else if (TPW > 1) {
                 if (WANT_D2) P.d2[s] = d2a;
                 if (WANT_LZ) P.lz[s] = lza;
             }
-        } else if (TPW == 2 && WANT_LZ && !last_pair) {
+        } else if (TPW > 1 && WANT_LZ && !last_pair) {
             P.lz[s] = lza;
         }
         // the pair's coefficients are read next by bulk copies (async proxy)
@@ -1223,7 +1237,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
             pst[k] = nx;
         }
         __syncwarp();
-        if (TPW == 2) k ^= 1;
+        k = k + 1 == TPW ? 0 : k + 1;
     }
     if (rec) {
         P.stats[blockIdx.x * 12 + 5] = (unsigned long long)(clock64() - t_begin);
@@ -1404,7 +1418,6 @@ void chain_free(BlockedCtx& bc) {
     cudaFree(cc.Rpk);
     cudaFree(cc.Bpk);
     cudaFree(cc.tp);
-    cudaFree(cc.invr);
     cudaFree(cc.sig);
     cudaFree(cc.subs);
     cudaFree(cc.pt_buf);
@@ -1440,18 +1453,24 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     const int n = d.n;
     const int npad = (n + kPair - 1) / kPair * kPair;
     cc.npad = npad;
-    std::vector<double> Rup((size_t)n * n, 0.0);
-    for (int i = 0; i < n; i++)
-        for (int j = i; j < n; j++) Rup[(size_t)i * n + j] = d.R[(size_t)i * n + j];
-    std::vector<double> Rpk, Bpk, tp(npad, 0.0);
-    pack_slivers(Rup.data(), n, n, n, npad, Rpk, true);
-    pack_slivers(d.B, n, n, n, npad, Bpk, false);
-    for (int i = 0; i < n; i++) tp[i] = d.t[i];
     std::vector<double> invr(npad, 1.0);
     for (int i = 0; i < n; i++) {
         invr[i] = 1.0 / hc.rdiag[i];
         // the chain kernel derives sum (x-m)^2/(2 sigma_i^2) from sum r_ii^2 (x-m)^2: needs sigma_i = sigma/|r_ii| unclamped
         if (hc.sig[i] != d.sigma / std::fabs(hc.rdiag[i])) return cudaSuccess;  // not ready: the v1 path serves
+    }
+    // the centers are kept divided by their R_ii (as the window triangle and the rows-below rectangles are): row i of
+    // the packed R and t_i carry the factor, so the centers epilogue is t' - acc with nothing else to load or multiply
+    std::vector<double> Rup((size_t)n * n, 0.0);
+    for (int i = 0; i < n; i++)
+        for (int j = i; j < n; j++) Rup[(size_t)i * n + j] = d.R[(size_t)i * n + j] * invr[i];
+    std::vector<double> Rpk, Bpk, tp(npad, 0.0);
+    pack_slivers(Rup.data(), n, n, n, npad, Rpk, true);
+    pack_slivers(d.B, n, n, n, npad, Bpk, false);
+    cc.t_zero = true;
+    for (int i = 0; i < n; i++) {
+        tp[i] = d.t[i] * invr[i];
+        cc.t_zero = cc.t_zero && d.t[i] == 0.0;
     }
     std::vector<SubPack> subs(npad / kSubW);
     for (int gs = 0; gs < npad / kSubW; gs++) {
@@ -1509,7 +1528,6 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     if ((e = up((void**)&cc.Rpk, Rpk.data(), sizeof(double) * Rpk.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.Bpk, Bpk.data(), sizeof(double) * Bpk.size())) != cudaSuccess) return e;
     if ((e = up((void**)&cc.tp, tp.data(), sizeof(double) * tp.size())) != cudaSuccess) return e;
-    if ((e = up((void**)&cc.invr, invr.data(), sizeof(double) * invr.size())) != cudaSuccess) return e;
     {
         std::vector<double> sigp(npad, 1.0);
         for (int i = 0; i < n; i++) sigp[i] = hc.sig[i];
@@ -1574,7 +1592,7 @@ static cudaError_t chain_ensure_work(ChainCtx& cc, BlockedWork& w, int64_t cap) 
 // one launch of the chain kernel
 static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool want_lz, bool want_d2, cudaStream_t st) {
     ChainCtx& cc = bc.chain;
-    a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.invr = cc.invr; a.subs = cc.subs;
+    a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.t_zero = cc.t_zero ? 1 : 0; a.subs = cc.subs;
     a.inv_two_sigma2 = 1.0 / bc.two_sigma2;
     a.sum_lognorm = bc.sum_lognorm;
     a.npad = cc.npad; a.n_valid = bc.n;
@@ -1587,14 +1605,16 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
         // staggered start: IMHK launches and proposal-only batches (+3.9 % / +1.5 %); a Klein batch with lattice points
         // has filler for the top of its steps and only pays the later start (-1 %)
         static const int sg = [] { const char* v = getenv("LGS_CHAIN_STAGGER"); return v ? atoi(v) : -1; }();
-        a.stagger = sg >= 0 ? sg : ((a.nsteps > 1 || !(a.V || a.V16)) ? 1 : 0);
-        // Two tiles per panel warpgroup where nothing else hides the wait for a pair's centers: IMHK launches (nine steps
-        // out of ten have no lattice points to contract: 81.0 -> 74.0 ms per 10 steps at n = 1024), proposal-only batches
-        // (7.74 -> 6.83 ms), and tiles so short that the hand-over to the next tile shows (n <= 32: +8 %).  A Klein batch
+        a.stagger = sg >= 0 ? sg : ((a.nsteps > 1 || !(a.V || a.V16)) ? 100 : 0);   // per cent of the even spacing
+        // Two or three tiles per panel warpgroup where nothing else hides the wait for a pair's centers: IMHK launches
+        // (nine steps out of ten have no lattice points to contract: 81.0 / 74.3 / 73.3 ms per 10 steps at n = 1024 with
+        // one / two / three; three is slower than two at n <= 512), proposal-only batches (7.74 -> 6.83 ms), and tiles so
+        // short that the hand-over to the next tile shows (n <= 32: +8 %).  A Klein batch
         // with lattice points has that filler and is 1-3 % faster with one tile per warpgroup; its finished tiles also
         // reach the host transport sooner (mapped int16 route: 19.6 against 22.3 ms per call).
         static const int tp = [] { const char* v = getenv("LGS_CHAIN_TPW"); return v ? atoi(v) : 0; }();
-        a.tpw = (tp == 1 || tp == 2) ? tp : ((a.nsteps > 1 || (a.nsteps == 1 && !(a.V || a.V16)) || bc.n <= 32) ? 2 : 1);
+        const bool no_filler = a.nsteps > 1 || (a.nsteps == 1 && !(a.V || a.V16));
+        a.tpw = (tp >= 1 && tp <= kTpw) ? tp : (no_filler ? (cc.npad >= 12 * kPair ? 3 : 2) : (bc.n <= 32 ? 2 : 1));
         if (a.tpw > kTpw) a.tpw = kTpw;
     }
     const int sms = bc.sm_count > 0 ? bc.sm_count : 148;

@@ -130,8 +130,8 @@ struct ChainCtx {
     int npad = 0;                 // n padded to a multiple of 64
     double* Rpk = nullptr;        // [npad/64][npad/16][64][20] shared-memory images of the 64 x 16 slivers of R
     double* Bpk = nullptr;        // same for the basis
-    double* tp = nullptr;         // [npad]
-    double* invr = nullptr;       // [npad] 1 / R_ii
+    double* tp = nullptr;         // [npad] t_i / R_ii
+    bool t_zero = true;           // t = Q^T c = 0
     double* sig = nullptr;        // [npad] sigma_i (the replay instantiations' table sampler takes sigma_i itself)
     int precision = 10, max_range = 1000;
     SubPack* subs = nullptr;      // [npad/8]
