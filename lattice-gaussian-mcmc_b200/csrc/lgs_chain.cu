@@ -293,6 +293,8 @@ struct ChainArgs {
     long long* upos;        // IMHK: [cap] position of every chain inside its stream, carried over the launches of one
                             // call; Klein: nullptr (every sample starts at 0)
     const double* sig;      // [npad] sigma_i = sigma / |R_ii|
+    const double* wtab;     // tables of the wide truncated windows (samplez_wide_table), wtab_ld doubles per kind-3 coordinate
+    int64_t wtab_ld;
     int precision, max_range;
     int32_t* fallback;      // counts draws that took the reference's no-uniform fallback (klein.py:176-179), or nullptr
     uint8_t* accept_out;    // IMHK: [S][call_steps] accept bit of every step of the call, or nullptr
@@ -797,6 +799,13 @@ __device__ __noinline__ double chain_samplez_fast_call(double mean, double inv2s
     return (double)samplez_fast<WIDE>(mean, fz, u, zsum);
 }
 
+// (the coordinate's CoordConst carries the normaliser's coefficients in q, sq, znorm, eps1, lognz: chain_init)
+__device__ __noinline__ double chain_samplez_wide_table_call(double mean, const CoordConst* cc, float sqrt_a, int dmax,
+                                                             double u, const double* tab, double* zsum) {
+    const double zc[5] = {cc->q, cc->sq, cc->znorm, cc->eps1, cc->lognz};
+    return (double)samplez_wide_table(mean, cc->a, sqrt_a, dmax, u, tab, zc, zsum);
+}
+
 // Replay draw: the reference's table SampleZ (klein.py:101-179) on the recorded uniform; *lse (exact weights) is the
 // table's log-sum-exp, the log of the window mass (imhk: Wang-Ling weight).  Returns false when the reference's
 // no-uniform fallback was taken (klein.py:176-179): the uniform is then not consumed.
@@ -1077,8 +1086,13 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                                 if (WANT_LZ) lza += logz;
                             } else {
                                 double zs;
-                                x = chain_samplez_fast_call<WIDE>(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, kind, ci.y, u,
-                                                            &zs);
+                                const int wt = __float_as_int(sp.cf[j].pad);   // wide truncated window: its tables + 1
+                                if (WIDE && kind == 3 && P.wtab && wt > 0)
+                                    x = chain_samplez_wide_table_call(mean, &cc, sp.cf[j].sq, ci.y, u,
+                                                                      P.wtab + (size_t)(wt - 1) * P.wtab_ld, &zs);
+                                else
+                                    x = chain_samplez_fast_call<WIDE>(mean, cc.a, cc.q, cc.sq, cc.znorm, cc.eps1, kind, ci.y,
+                                                                      u, &zs);
                                 if (WANT_LZ) lza += log(zs);
                             }
                         }
@@ -1420,6 +1434,7 @@ void chain_free(BlockedCtx& bc) {
     cudaFree(cc.tp);
     cudaFree(cc.sig);
     cudaFree(cc.subs);
+    cudaFree(cc.wtab);
     cudaFree(cc.pt_buf);
     for (auto& w : cc.work) {
         cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
@@ -1472,6 +1487,12 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
         tp[i] = d.t[i] * invr[i];
         cc.t_zero = cc.t_zero && d.t[i] == 0.0;
     }
+    // kind-3 coordinates share one window half-width (max_range / 2); tables only for those
+    int wide_dmax = 0;
+    for (int i = 0; i < n; i++)
+        if (hc.kind[i] == 3) wide_dmax = hc.dmax[i];
+    std::vector<int> wide_rows;
+    auto int_as_float_host = [](int v) { float f; memcpy(&f, &v, sizeof(f)); return f; };
     std::vector<SubPack> subs(npad / kSubW);
     for (int gs = 0; gs < npad / kSubW; gs++) {
         SubPack& sp = subs[gs];
@@ -1504,12 +1525,17 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
                 f.tol_r = (float)(4e-6 + 4e-7 * sg * sg);
                 f.tol_a = (float)(1.6e-7 * c.znorm);
                 bool wide_f32 = false;
+                if (hc.kind[gi] == 3 && hc.dmax[gi] == wide_dmax) {   // tables of samplez_wide_table
+                    wide_rows.push_back(gi);
+                    f.pad = int_as_float_host((int)wide_rows.size());   // table number + 1; 0 = none
+                }
                 if (hc.kind[gi] == 3) {  // constants of samplez_wide_screen
                     static const bool wide_screen = [] { const char* v = getenv("LGS_WIDE_SCREEN"); return !(v && v[0] == '0'); }();
                     const double sa = std::sqrt(c.a);
                     f.a = (float)c.a; f.sq = (float)sa; f.q = (float)(0.88622692545275801365 / sa);
                     f.znorm = (float)(sa * 0.56418958354775628695); f.eps1 = (float)(1.0 / sa);
-                    f.tol_r = 4e-6f; f.tol_a = 0.0f;
+                    static const float wide_tol = [] { const char* v = getenv("LGS_WIDE_TOL"); return v ? (float)atof(v) : 4e-6f; }();
+                    f.tol_r = wide_tol; f.tol_a = 0.0f;   // LGS_WIDE_TOL: development (what the FP64 fallbacks cost)
                     wide_f32 = wide_screen;
                 }
                 sp.ci[j] = make_int4(hc.kind[gi] | ((f32ok || wide_f32) ? 0 : 4), hc.dmax[gi], hc.uidx[gi], hc.mode[gi]);
@@ -1532,6 +1558,40 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
         std::vector<double> sigp(npad, 1.0);
         for (int i = 0; i < n; i++) sigp[i] = hc.sig[i];
         if ((e = up((void**)&cc.sig, sigp.data(), sizeof(double) * sigp.size())) != cudaSuccess) return e;
+    }
+    cc.wtab = nullptr;
+    cc.wtab_ld = 0;
+    {
+        static const bool use_tab = [] { const char* v = getenv("LGS_WIDE_TABLE"); return !(v && v[0] == '0'); }();
+        if (use_tab && !wide_rows.empty()) {
+            const int ld = wide_dmax + 1;
+            const size_t per = (size_t)(kWideTabK + 1) * ld;
+            std::vector<double> tab(per * wide_rows.size());
+            for (size_t w = 0; w < wide_rows.size(); w++) {
+                const long double a = (long double)hc.inv2s2[wide_rows[w]];
+                double* t = &tab[w * per];
+                long double S[kWideTabK] = {};
+                for (int k = 0; k < kWideTabK; k++) t[(size_t)k * ld] = 0.0;
+                t[(size_t)kWideTabK * ld] = 1.0;
+                for (int dd = 1; dd <= wide_dmax; dd++) {
+                    const long double j2 = (long double)dd * dd, g = expl(-a * j2);
+                    long double pw = g;
+                    for (int k = 0; k < kWideTabK; k++) {
+                        S[k] += pw;
+                        t[(size_t)k * ld + dd] = (double)S[k];
+                        pw *= j2;
+                    }
+                    t[(size_t)kWideTabK * ld + dd] = (double)g;
+                }
+                // normaliser coefficients 2 S_k(D) / (2k)! into the CoordConst fields a wide window does not use
+                CoordConst& c = subs[wide_rows[w] / kSubW].cc[wide_rows[w] % kSubW];
+                const long double fact[5] = {1.0L, 2.0L, 24.0L, 720.0L, 40320.0L};
+                double* dst[5] = {&c.q, &c.sq, &c.znorm, &c.eps1, &c.lognz};
+                for (int k = 0; k < 5; k++) *dst[k] = (double)(2.0L * S[k] / fact[k]);
+            }
+            if ((e = up((void**)&cc.wtab, tab.data(), sizeof(double) * tab.size())) != cudaSuccess) return e;
+            cc.wtab_ld = (int64_t)per;
+        }
     }
     cc.precision = d.precision > 0 ? d.precision : 10;
     cc.max_range = d.max_range > 0 ? d.max_range : 1000;
@@ -1593,6 +1653,7 @@ static cudaError_t chain_ensure_work(ChainCtx& cc, BlockedWork& w, int64_t cap) 
 static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool want_lz, bool want_d2, cudaStream_t st) {
     ChainCtx& cc = bc.chain;
     a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.t_zero = cc.t_zero ? 1 : 0; a.subs = cc.subs;
+    a.wtab = cc.wtab; a.wtab_ld = cc.wtab_ld;
     a.inv_two_sigma2 = 1.0 / bc.two_sigma2;
     a.sum_lognorm = bc.sum_lognorm;
     a.npad = cc.npad; a.n_valid = bc.n;

@@ -315,6 +315,87 @@ __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, d
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Wide truncated windows from per-coordinate TABLES (chain kernel: the FP64 draw behind samplez_wide_screen).
+// The same map u -> x as samplez_fast<true> on a kind-3 coordinate, without a transcendental call:
+//   M(d; delta) = sum_{|j| <= d} e^{-a (j + delta)^2}
+//               = e^{-a delta^2} [1 + 2 sum_k (2 a delta)^{2k} / (2k)!  S_k(d)],   S_k(d) = sum_{j=1..d} j^{2k} e^{-a j^2},
+// (the odd powers of the cosh series cancel over the symmetric window); with a <= 2e-4, |delta| <= 1/2, d <= 500 the
+// argument 2 a delta d is below 0.1 and six terms leave < 3e-17 of the sum.  The walk weights are
+// e^{-a (d +- delta)^2} = G(d) e^{-a delta^2} e^{-+ 2 a d delta}, G(d) = e^{-a d^2} tabulated, the last factor a short
+// series.  Table layout per coordinate (chain_init): tab[k * (D + 1) + d] = S_k(d) for k = 0 .. 5, tab[6 (D + 1) + d] = G(d).
+// Why: the closed form (two erf and six exp in FP64, ~800 instructions) ran on a whole warp whenever ONE of its 32
+// lanes failed the FP32 screen -- 27 % of the warp-draws on a flat window, 22 % of BASELINE config C3's time.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kWideTabK = 6;   // S_0 .. S_5
+__device__ __forceinline__ double exp_small(double x) {   // e^x, |x| <= 0.11: degree-10 Taylor, error < 1e-17
+    double p = 1.0 / 3628800.0;
+    p = fma(p, x, 1.0 / 362880.0);
+    p = fma(p, x, 1.0 / 40320.0);
+    p = fma(p, x, 1.0 / 5040.0);
+    p = fma(p, x, 1.0 / 720.0);
+    p = fma(p, x, 1.0 / 120.0);
+    p = fma(p, x, 1.0 / 24.0);
+    p = fma(p, x, 1.0 / 6.0);
+    p = fma(p, x, 0.5);
+    p = fma(p, x, 1.0);
+    return fma(p, x, 1.0);
+}
+// M(d; delta) / e^{-a delta^2}; y2 = (2 a delta)^2
+__device__ __forceinline__ double wide_mass_tab(const double* __restrict__ tab, int ld, int d, double y2) {
+    double acc = __ldg(tab + 5 * ld + d) * (1.0 / 3628800.0);
+    acc = fma(acc, y2, __ldg(tab + 4 * ld + d) * (1.0 / 40320.0));
+    acc = fma(acc, y2, __ldg(tab + 3 * ld + d) * (1.0 / 720.0));
+    acc = fma(acc, y2, __ldg(tab + 2 * ld + d) * (1.0 / 24.0));
+    acc = fma(acc, y2, __ldg(tab + 1 * ld + d) * 0.5);
+    acc = fma(acc, y2, __ldg(tab + d));
+    return fma(2.0, acc, 1.0);
+}
+// zc[k] = 2 S_k(D) / (2k)!, k = 0 .. 4: the normaliser needs no table row (the k = 5 term is < 3e-17 of it)
+__device__ __forceinline__ long long samplez_wide_table(double mean, double a, float sqrt_a, int dmax, double u,
+                                                        const double* __restrict__ tab, const double* zc, double* zsum) {
+    const int ld = dmax + 1;
+    const double c0 = rint(mean);
+    const double delta = c0 - mean;                   // in [-0.5, 0.5]
+    const double w0 = exp_small(-a * delta * delta);  // rho(c0) = e^{-a delta^2}
+    const double y = 2.0 * a * delta, y2 = y * y;
+    const double Z = w0 * fma(fma(fma(fma(fma(zc[4], y2, zc[3]), y2, zc[2]), y2, zc[1]), y2, zc[0]), 1.0, 1.0);
+    *zsum = Z;
+    const double target = u * Z;
+    const long long x = (long long)c0;
+    if (target < w0) return x;
+    // the exit distance: FP32 estimate from the symmetric integral, exact mass inside distance ds - 1 from the tables,
+    // then the outward walk (the estimate only chooses where the walk starts)
+    int d = 1;
+    double cum = w0;
+    const double* __restrict__ G = tab + kWideTabK * ld;
+    double g0 = 0.0, g1 = 0.0, g2 = 0.0;
+    int dg = 0;   // g0..g2 = G(dg .. dg + 2) when dg > 0
+    {
+        const float yy = (float)target * sqrt_a * 0.56418958354775628695f;
+        if (yy < 0.99999f) {
+            int ds = (int)floorf(erfinvf(yy) / sqrt_a - 0.5f) - 1;
+            ds = ds > dmax ? dmax : ds;
+            if (ds >= 3) {
+                // the first weights of the walk are requested together with the row of masses
+                if (ds + 2 <= dmax) { g0 = __ldg(G + ds); g1 = __ldg(G + ds + 1); g2 = __ldg(G + ds + 2); dg = ds; }
+                const double base = w0 * wide_mass_tab(tab, ld, ds - 1, y2);
+                if (base <= target) cum = base, d = ds;
+            }
+        }
+    }
+    for (; d <= dmax; d++) {
+        const double gt = (dg > 0 && d == dg) ? g0 : (dg > 0 && d == dg + 1) ? g1 : (dg > 0 && d == dg + 2) ? g2 : __ldg(G + d);
+        const double gd = gt * w0;
+        const double yd = y * (double)d;              // 2 a d delta, |.| <= 0.1
+        cum += gd * exp_small(-yd);                   // e^{-a (d + delta)^2}
+        if (target < cum) return x + d;
+        cum += gd * exp_small(yd);                    // e^{-a (d - delta)^2}
+        if (target < cum) return x - d;
+    }
+    return x - dmax;   // u Z beyond the accumulated mass (rounding, ~1e-16): the last point visited
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Fast SampleZ, smooth regime (kind 0 / 1: sigma_i >= 1, full window): the same inverse transform as samplez_fast
 // (same ordering c0, c0+1, c0-1, ..., same one uniform), arranged for few instructions and short dependency chains:
 //   * weights in units of rho(c0), so only ratios are needed: with a = 1/(2 sigma_i^2), delta = c0 - mean,
@@ -456,7 +537,7 @@ __device__ __forceinline__ bool samplez_smooth_screen(float dl, const SmoothF32&
 // then at most four outward steps with directly evaluated weights.  Error budget against the FP64 path, relative to Z:
 // erff 2 ulp and three roundings per closed form (3.6e-7, twice), the 29 dropped bits of u (6e-8), <= 8 additions of
 // the walk (5e-7) -- under 1.4e-6; a draw is accepted only when u Z clears every threshold it is compared with by
-// tol = 4e-6 Z, otherwise the caller runs the FP64 closed form (about 1 % of the draws on a flat window), so the map
+// tol = 4e-6 T + 1.2e-7 Z, otherwise the caller runs the FP64 draw (about 0.4 % of the draws on a flat window), so the map
 // u -> x stays the FP64 one.  Constants (SmoothF32): a, sq = sqrt(a), q = sqrt(pi) / (2 sqrt(a)), znorm = sqrt(a / pi),
 // eps1 = 1 / sqrt(a), tol_r = 4e-6.
 // ---------------------------------------------------------------------------------------------------------
@@ -468,7 +549,9 @@ __device__ __forceinline__ bool samplez_wide_screen(float dl, const SmoothF32& k
     float gu = __expf(-a * su * su), gd = __expf(-a * sd * sd);
     const float Z = fmaf(c1, erff(s * su) + erff(s * sd), fmaf(0.5f, gu + gd, -a6 * fmaf(su, gu, sd * gd)));
     const float T = (float)(uhi >> 8) * 5.9604644775390625e-8f * Z;
-    const float tol = k.tol_r * Z;
+    // every FP32 error above is relative to the masses compared (T and the cumulative mass next to it), except the 29
+    // dropped bits of u, which are 6e-8 of Z whatever T is
+    const float tol = fmaf(k.tol_r, T, 1.2e-7f * Z);
     const float y = T * k.znorm;
     if (!(y < 0.9999f)) return false;
     int d0 = (int)floorf(fmaf(erfinvf(y), k.eps1, -0.5f)) - 1;

@@ -135,6 +135,8 @@ struct ChainCtx {
     double* sig = nullptr;        // [npad] sigma_i (the replay instantiations' table sampler takes sigma_i itself)
     int precision = 10, max_range = 1000;
     SubPack* subs = nullptr;      // [npad/8]
+    double* wtab = nullptr;       // tables of the wide truncated windows (lgs_device.cuh samplez_wide_table)
+    int64_t wtab_ld = 0;          // doubles per kind-3 coordinate: 7 (dmax + 1)
     BlockedWork work[3];          // tiled: X = [cap/128][npad][132]; [0] Klein, [1]/[2] IMHK proposals
     int64_t batch = 0;            // samples per full batch: sm_count x 128 x 9
     bool wide = false;            // some coordinate has a wide truncated window (kind 3): the WIDE kernel instantiations
