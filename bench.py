@@ -445,10 +445,12 @@ def main():
             hist = torch.zeros((4, 64), dtype=torch.int64, device="cuda")
             res = {}
 
+            # statistics of src/diagnostics (acceptance mean, marginal histograms): accumulated per rank by the lattice-point
+            # epilogue of the sampling kernel itself (lgs_attach_histogram: no separate pass over V) ...
+            eng.attach_histogram(dims, -8 * sigma, sigma / 4, 64, hist.data_ptr())
+
             def imhk_step(k):
                 eng.imhk_run_dev(0, 1, thin, "fast", weight, V=Vk.data_ptr(), stream=stream)
-                # statistics of src/diagnostics (acceptance mean, marginal histograms): accumulate per rank ...
-                eng.histogram_dev(Vk.data_ptr(), C, dims, -8 * sigma, sigma / 4, 64, hist.data_ptr(), stream=stream)
 
             for w in range(2):
                 imhk_step(w)
@@ -468,6 +470,7 @@ def main():
             iprof = eng.profile_read()
             eng.profile_enable(False)
             itot = max(sum(v[0] for v in iprof.values()), 1e-9)
+            eng.attach_histogram(None, 0.0, 1.0, 1, 0)
             return {"value": rate, "unit": "chain-steps/s", "weight_mode": weight, "chains_per_gpu": C, "thin": thin,
                     "ms_per_step": ms / steps, "acceptance_rate": D.acceptance_rate(res["tot"].cpu()),
                     "flop_per_chain_step": imhk_flop(thin),

@@ -84,6 +84,7 @@ PROTOTYPES = {
     "lgs_profile_enable": (ctypes.c_int, [vp, ctypes.c_int]),
     "lgs_profile_read": (ctypes.c_int, [vp, c_f64p, c_i64p]),
     "lgs_histogram": (ctypes.c_int, [vp, vp, ctypes.c_int64, c_i32p, ctypes.c_int32, ctypes.c_double, ctypes.c_double, ctypes.c_int32, vp, vp]),
+    "lgs_attach_histogram": (ctypes.c_int, [vp, c_i32p, ctypes.c_int32, ctypes.c_double, ctypes.c_double, ctypes.c_int32, vp]),
 }
 
 

@@ -278,6 +278,14 @@ class Engine:
     def gelman_rubin_sums_dev(self, stats, chains, n_dims, sums, stream=0):
         check(self._h, self._lib.lgs_gelman_rubin_sums(self._h, stats, int(chains), int(n_dims), sums, stream or None))
 
+    def attach_histogram(self, dims, lo, width, nbins, hist):
+        """Count the tracked coordinates of every lattice point the chain kernel writes to a device-resident V into
+        hist (device pointer to int64[len(dims)][nbins], accumulated) from inside the sampling kernel; hist = 0
+        detaches.  See lgs_attach_histogram in include/lgs_b200.h."""
+        dims = np.ascontiguousarray(dims if dims is not None else [], dtype=np.int32)
+        check(self._h, self._lib.lgs_attach_histogram(self._h, dims.ctypes.data_as(_capi.c_i32p), dims.size,
+                                                      float(lo), float(width), int(nbins), hist or None))
+
     def histogram_dev(self, V, S, dims, lo, width, nbins, hist, stream=0):
         dims = np.ascontiguousarray(dims, dtype=np.int32)
         check(self._h, self._lib.lgs_histogram(self._h, V, int(S), dims.ctypes.data_as(_capi.c_i32p), dims.size,

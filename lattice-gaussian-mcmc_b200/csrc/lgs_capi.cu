@@ -1257,6 +1257,24 @@ int lgs_histogram(lgs_handle* h, const double* V_dev, int64_t S, const int32_t* 
     return LGS_OK;
 }
 
+int lgs_attach_histogram(lgs_handle* h, const int32_t* dims_host, int32_t n_dims, double lo, double width, int32_t nbins,
+                         int64_t* hist_dev) {
+    LGS_TRACE();
+    if (!h) return LGS_E_INVALID;
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    if (!h->blocked.ready || !h->blocked.use_chain || !h->blocked.chain.ready || h->path == LGS_PATH_ORDERED)
+        return fail(h, LGS_E_STATE, "lgs_attach_histogram: this handle is not served by the chain kernel (use lgs_histogram)");
+    if (hist_dev) {
+        if (!dims_host || n_dims <= 0 || n_dims > 32767 || nbins <= 0 || !(width > 0.0))
+            return fail(h, LGS_E_INVALID, "lgs_attach_histogram: bad arguments");
+        for (int i = 0; i < n_dims; i++)
+            if (dims_host[i] < 0 || dims_host[i] >= h->n)
+                return fail(h, LGS_E_INVALID, "lgs_attach_histogram: dim out of range");
+    }
+    LGS_CUDA(h, chain_attach_histogram(h->blocked, dims_host, n_dims, lo, width, nbins, hist_dev));
+    return LGS_OK;
+}
+
 int lgs_chain_diagnostics(lgs_handle* h, const double* V_dev, int64_t chains, int64_t keep, const int32_t* dims_host,
                           int32_t n_dims, double c_window, int32_t max_lag, double* stats_dev, double* acf_dev,
                           int32_t acf_len, void* stream) {

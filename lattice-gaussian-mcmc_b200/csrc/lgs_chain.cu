@@ -293,6 +293,11 @@ struct ChainArgs {
     long long* upos;        // IMHK: [cap] position of every chain inside its stream, carried over the launches of one
                             // call; Klein: nullptr (every sample starts at 0)
     const double* sig;      // [npad] sigma_i = sigma / |R_ii|
+    // histogram fused into the lattice-point epilogue (lgs_attach_histogram): bins of the tracked coordinates
+    const int16_t* hist_map;    // [npad] row of bins of a tracked coordinate, -1 otherwise; nullptr: no histogram
+    unsigned long long* hist;   // [tracked][hist_nbins], accumulated with global atomics
+    double hist_lo, hist_inv_width;
+    int hist_nbins;
     const double* wtab;     // tables of the wide truncated windows (samplez_wide_table), wtab_ld doubles per kind-3 coordinate
     int64_t wtab_ld;
     int precision, max_range;
@@ -476,6 +481,30 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
                             if (col + 1 < P.S) Vb[(size_t)(col + 1) * P.ldv + row] = LGS_ACC(mt, hh, nt, 1);
                         }
                     }
+                if (P.hist_map) {
+                    // marginal histograms of the tracked coordinates (src/diagnostics/convergence_diag.py:15-72), counted
+                    // while the lattice points are in registers: same bins and clamping as histogram_kernel
+#pragma unroll
+                    for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                        for (int hh = 0; hh < 2; hh++) {
+                            const int row = h.r0 + wm * 32 + mt * 16 + g + hh * 8;
+                            if (row >= P.n_valid) continue;
+                            const int m = P.hist_map[row];
+                            if (m < 0) continue;
+                            unsigned long long* hb = P.hist + (size_t)m * P.hist_nbins;
+#pragma unroll
+                            for (int nt = 0; nt < 4; nt++)
+#pragma unroll
+                                for (int c = 0; c < 2; c++) {
+                                    const int64_t col = s0 + wn * 32 + nt * 8 + t * 2 + c;
+                                    if (col >= P.S) continue;
+                                    const double b = floor((LGS_ACC(mt, hh, nt, c) - P.hist_lo) * P.hist_inv_width);
+                                    const int bi = b < 0.0 ? 0 : (b >= (double)P.hist_nbins ? P.hist_nbins - 1 : (int)b);
+                                    atomicAdd(hb + bi, 1ull);
+                                }
+                        }
+                }
             } else {
                 double* xt = P.Xbuf[(h.r0 >> 30) & 1] + (size_t)h.tile * P.npad * kRowLd;
                 const int r0 = h.r0 & 0x3fffffff;
@@ -1435,6 +1464,7 @@ void chain_free(BlockedCtx& bc) {
     cudaFree(cc.sig);
     cudaFree(cc.subs);
     cudaFree(cc.wtab);
+    cudaFree(cc.hist_map);
     cudaFree(cc.pt_buf);
     for (auto& w : cc.work) {
         cudaFree(w.X); cudaFree(w.lp); cudaFree(w.d2); cudaFree(w.lz);
@@ -1654,6 +1684,8 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     ChainCtx& cc = bc.chain;
     a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.t_zero = cc.t_zero ? 1 : 0; a.subs = cc.subs;
     a.wtab = cc.wtab; a.wtab_ld = cc.wtab_ld;
+    a.hist_map = (cc.hist && a.V) ? cc.hist_map : nullptr;
+    a.hist = cc.hist; a.hist_lo = cc.hist_lo; a.hist_inv_width = cc.hist_inv_width; a.hist_nbins = cc.hist_nbins;
     a.inv_two_sigma2 = 1.0 / bc.two_sigma2;
     a.sum_lognorm = bc.sum_lognorm;
     a.npad = cc.npad; a.n_valid = bc.n;
@@ -2088,6 +2120,25 @@ cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int
     }
     for (int64_t k = 0; k < keep; k++)
         if ((e = segment(thin, true, k)) != cudaSuccess) return e;
+    return cudaSuccess;
+}
+
+// lgs_attach_histogram: the coordinate -> bins table of the lattice-point epilogue (synchronous; hist == nullptr detaches)
+cudaError_t chain_attach_histogram(BlockedCtx& bc, const int32_t* dims, int n_dims, double lo, double width, int nbins,
+                                   int64_t* hist) {
+    ChainCtx& cc = bc.chain;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return e;
+    cc.hist = nullptr;
+    if (!hist) return cudaSuccess;
+    std::vector<int16_t> map((size_t)cc.npad, (int16_t)-1);
+    for (int i = 0; i < n_dims; i++) map[dims[i]] = (int16_t)i;   // a coordinate listed twice counts into its last row
+    if (!cc.hist_map && (e = cudaMalloc(&cc.hist_map, sizeof(int16_t) * cc.npad)) != cudaSuccess) return e;
+    if ((e = cudaMemcpy(cc.hist_map, map.data(), sizeof(int16_t) * cc.npad, cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+    cc.hist = reinterpret_cast<unsigned long long*>(hist);
+    cc.hist_lo = lo;
+    cc.hist_inv_width = 1.0 / width;
+    cc.hist_nbins = nbins;
     return cudaSuccess;
 }
 

@@ -132,6 +132,11 @@ struct ChainCtx {
     double* Bpk = nullptr;        // same for the basis
     double* tp = nullptr;         // [npad] t_i / R_ii
     bool t_zero = true;           // t = Q^T c = 0
+    // histogram attached to the lattice-point epilogue (lgs_attach_histogram); hist == nullptr: none
+    int16_t* hist_map = nullptr;  // [npad] tracked coordinate -> its row of bins, -1 otherwise
+    unsigned long long* hist = nullptr;
+    double hist_lo = 0.0, hist_inv_width = 0.0;
+    int hist_nbins = 0;
     double* sig = nullptr;        // [npad] sigma_i (the replay instantiations' table sampler takes sigma_i itself)
     int precision = 10, max_range = 1000;
     SubPack* subs = nullptr;      // [npad/8]
@@ -286,6 +291,8 @@ cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int
                               double* V, int64_t* X, cudaStream_t st, const ChainReplay* rp = nullptr);
 cudaError_t launch_imhk_chain_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* counts, int64_t* X, double* V,
                                         double* logw, cudaStream_t st);
+cudaError_t chain_attach_histogram(BlockedCtx& bc, const int32_t* dims, int n_dims, double lo, double width, int nbins,
+                                   int64_t* hist);
 cudaError_t launch_imhk_chain_set_state(BlockedCtx& bc, ChainSet& cs, const int64_t* X, const double* logw,
                                         const int64_t* counts, int64_t steps_done, cudaStream_t st);
 

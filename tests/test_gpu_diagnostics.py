@@ -159,3 +159,60 @@ def test_device_tvd_default_call_at_the_headline_dimension(lgs):
     hist = torch.zeros((300, 16), dtype=torch.int64, device="cuda")
     smp._engine.histogram_dev(Va.data_ptr(), S, dims3, -800.0, 100.0, 16, hist.data_ptr(), stream=st)
     assert torch.equal(hist.cpu(), host_histogram(Va.cpu(), dims3, -800.0, 100.0, 16))
+
+
+def test_histogram_fused_into_the_sampling_kernel_equals_lgs_histogram(lgs):
+    """lgs_attach_histogram: the lattice-point epilogue of the chain kernel counts the tracked coordinates of what it
+    writes -- Klein batches (several tiles, a ragged last one), IMHK kept states (step-by-step and step-parallel
+    launches) -- into the same bins as lgs_histogram run afterwards on the returned V."""
+    import torch
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(96, seed=3)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    smp = lgs.KleinSampler(lat, sigma, seed=9, path="blocked")
+    eng = smp._engine
+    n = 96
+    dims = np.array([0, 5, 63, 64, 95], dtype=np.int32)
+    lo, width, nbins = -3.0 * sigma, sigma / 5, 32          # narrower than the support: both clamps are exercised
+    st = torch.cuda.current_stream().cuda_stream
+
+    def separate(V, S):
+        h = torch.zeros((len(dims), nbins), dtype=torch.int64, device="cuda")
+        eng.histogram_dev(V.data_ptr(), S, dims, lo, width, nbins, h.data_ptr(), stream=st)
+        torch.cuda.synchronize()
+        return h.cpu().numpy()
+
+    fused = torch.zeros((len(dims), nbins), dtype=torch.int64, device="cuda")
+    eng.attach_histogram(dims, lo, width, nbins, fused.data_ptr())
+    S = 5 * 128 + 37
+    V = torch.empty((S, n), dtype=torch.float64, device="cuda")
+    eng.klein_sample_dev(S, 9, 0, "fast", V=V.data_ptr(), stream=st)
+    torch.cuda.synchronize()
+    want = separate(V, S)
+    assert fused.sum().item() == S * len(dims)
+    assert np.array_equal(fused.cpu().numpy(), want)
+    # accumulation + IMHK kept states (3 kept states of 300 chains: the step-parallel route for so few chains)
+    C, keep = 300, 3
+    eng.imhk_reset(C, seed=4)
+    Vk = torch.empty((C, keep, n), dtype=torch.float64, device="cuda")
+    eng.imhk_run_dev(5, keep, 2, "fast", "exact", V=Vk.data_ptr(), stream=st)
+    torch.cuda.synchronize()
+    want = want + separate(Vk, C * keep)
+    assert np.array_equal(fused.cpu().numpy(), want)
+    old = os.environ.get("LGS_IMHK_STEPPAR")
+    os.environ["LGS_IMHK_STEPPAR"] = "0"                       # ... and the step-by-step launches
+    try:
+        eng.imhk_run_dev(0, keep, 2, "fast", "exact", V=Vk.data_ptr(), stream=st)
+        torch.cuda.synchronize()
+    finally:
+        if old is None:
+            del os.environ["LGS_IMHK_STEPPAR"]
+        else:
+            os.environ["LGS_IMHK_STEPPAR"] = old
+    want = want + separate(Vk, C * keep)
+    assert np.array_equal(fused.cpu().numpy(), want)
+    # detached: nothing is counted any more
+    eng.attach_histogram(None, 0.0, 1.0, 1, 0)
+    eng.klein_sample_dev(S, 9, S, "fast", V=V.data_ptr(), stream=st)
+    torch.cuda.synchronize()
+    assert np.array_equal(fused.cpu().numpy(), want)
