@@ -132,3 +132,50 @@ def shortest_projected_norm2(rows, j, k, radius=3):
         if best is None or tot < best:
             best = tot
     return best
+
+
+def shortest_vector_norm2(rows) -> int:
+    """lambda_1^2 of the lattice spanned by the integer ROWS, by an independent Fincke-Pohst / Schnorr-Euchner search:
+    the basis is first LLL-reduced with `lll_textbook` (so the search tree is small), the enumeration runs on float64
+    Gram-Schmidt data with a 1e-9 relative safety margin on the radius, and every candidate's norm is recomputed in exact
+    integers.  For n <= ~24 (pure Python).  Used to cross-check lgs_bkz_reduce with beta = n (a full-block BKZ tour must
+    end on a shortest vector up to its delta slack) -- the only external check BKZ has on this image (fplll is absent)."""
+    B = np.array(np.rint(lll_textbook(rows)), dtype=object)
+    n = B.shape[0]
+    Bf = np.array(B, dtype=np.float64)
+    Bs = np.zeros_like(Bf)
+    mu = np.zeros((n, n))
+    r = np.zeros(n)
+    for k in range(n):
+        v = Bf[k].copy()
+        for j in range(k):
+            mu[k, j] = (Bs[j] @ Bf[k]) / r[j]
+            v -= mu[k, j] * Bs[j]
+        Bs[k] = v
+        r[k] = v @ v
+    best = int(sum(int(x) * int(x) for x in B[0]))       # the first reduced vector bounds the search
+    x = [0] * n
+
+    def descend(k, partial):          # coordinates k+1 .. n-1 fixed, `partial` = their contribution to the squared norm
+        nonlocal best
+        c = -sum(x[j] * mu[j, k] for j in range(k + 1, n))
+        bound = best * (1 + 1e-9) - partial
+        if bound < 0:
+            return
+        rad = (bound / r[k]) ** 0.5
+        lo, hi = int(np.ceil(c - rad)), int(np.floor(c + rad))
+        for xi in sorted(range(lo, hi + 1), key=lambda t: abs(t - c)):
+            x[k] = xi
+            p2 = partial + (xi - c) ** 2 * r[k]
+            if k == 0:
+                if any(x):
+                    vec = [sum(x[i] * int(B[i][col]) for i in range(n)) for col in range(B.shape[1])]
+                    nrm = sum(v * v for v in vec)
+                    if nrm < best:
+                        best = nrm
+            else:
+                descend(k - 1, p2)
+        x[k] = 0
+
+    descend(n - 1, 0.0)
+    return best
