@@ -387,7 +387,10 @@ def main():
             1, len(os.sched_getaffinity(0)) // int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
         # the host's own ceiling for this delivery: the pool widening a RESIDENT int16 buffer into the same float64
         # array with non-temporal stores, every rank at once (what the transport does minus the GPU and PCIe)
-        src16 = np.zeros((S, n), dtype=np.int16)
+        # (a source of distinct, touched pages: np.zeros would map every page to the kernel's zero page and the "ceiling"
+        # would have no read traffic at all -- it read 194 GB/s where the same pool sustains ~130 GB/s on real data)
+        src16 = np.tile(np.random.RandomState(1).randint(-3000, 3000, (1024, n)).astype(np.int16), ((S + 1023) // 1024, 1))[:S]
+        src16 = np.ascontiguousarray(src16)
         dst64 = Vh.numpy()[:S]
         best = 1e9
         for r in range(4):
@@ -407,8 +410,9 @@ def main():
                              f"of {S} per call (a 'step' of this leg = one batch), {Ke} calls timed",
                "transport": tname, "host_threads_per_rank": threads,
                "host_store_gbs_peak": store_gbs,
-               "host_store_peak_how": "lgs_host_widen_i16 on a resident int16 buffer into the same pinned float64 "
-                                      "array, all ranks at once with their pool threads, best of 4",
+               "host_store_peak_how": "lgs_host_widen_i16 on a resident int16 buffer of distinct pages into the same pinned "
+                                      "float64 array, all ranks at once with their pool threads, best of 4 (the delivery "
+                                      "also takes the DMA write of the int16, 2 more bytes per value)",
                "frac_of_host_peak": e2e_rate * n * 8 / 1e9 / store_gbs,
                "note": "the sampler's only inputs are (seed, first id) scalars; every step delivers its S x n float64 "
                        "lattice points (the reference's return array) into host memory; for this integer basis they "
