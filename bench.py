@@ -456,7 +456,7 @@ def main():
             def imhk_step(k):
                 eng.imhk_run_dev(0, 1, thin, "fast", weight, V=Vk.data_ptr(), stream=stream)
 
-            for w in range(2):
+            for w in range(W):
                 imhk_step(w)
             hist.zero_()
 
