@@ -440,7 +440,8 @@ def main():
     if not args.skip_imhk:
         from lattice_gaussian_mcmc_b200 import distributed as D
         thin = args.thin
-        Vk = torch.empty((C, 1, n), dtype=torch.float64, device="cuda")
+        KEEP = 4          # kept states per lgs_imhk_run call, as IMHKSampler.sample(num_samples, thin) asks for many per call
+        Vk = torch.empty((C, KEEP, n), dtype=torch.float64, device="cuda")
         dims = np.array([0, 1, n // 2, n - 1], dtype=np.int32)
 
         def imhk_leg(weight, steps, eng=eng, sigma=SIGMA):
@@ -454,7 +455,7 @@ def main():
             eng.attach_histogram(dims, -8 * sigma, sigma / 4, 64, hist.data_ptr())
 
             def imhk_step(k):
-                eng.imhk_run_dev(0, 1, thin, "fast", weight, V=Vk.data_ptr(), stream=stream)
+                eng.imhk_run_dev(0, KEEP, thin, "fast", weight, V=Vk.data_ptr(), stream=stream)
 
             for w in range(W):
                 imhk_step(w)
@@ -466,7 +467,7 @@ def main():
                     eng.imhk_state_dev(counts=counts.data_ptr(), stream=stream)
                     res["tot"], res["hist"] = D.allreduce_stats(counts, hist)
             ms = timed(imhk_all, steps)
-            rate = world * C * thin * steps / (ms * 1e-3)
+            rate = world * C * thin * KEEP * steps / (ms * 1e-3)
             # per-class device time of the same work (separate pass, events around every launch)
             eng.profile_enable(True)
             for k in range(2):
@@ -476,6 +477,7 @@ def main():
             itot = max(sum(v[0] for v in iprof.values()), 1e-9)
             eng.attach_histogram(None, 0.0, 1.0, 1, 0)
             return {"value": rate, "unit": "chain-steps/s", "weight_mode": weight, "chains_per_gpu": C, "thin": thin,
+                    "kept_states_per_call": KEEP,
                     "ms_per_step": ms / steps, "acceptance_rate": D.acceptance_rate(res["tot"].cpu()),
                     "flop_per_chain_step": imhk_flop(thin),
                     "fp64_tflops_per_gpu": rate / world * imhk_flop(thin) * 1e-12,

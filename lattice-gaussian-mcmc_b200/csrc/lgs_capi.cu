@@ -69,7 +69,7 @@ int ensure_stage(lgs_handle* h, size_t nbytes) {
 void free_chains(ChainSet& cs) {
     cudaFree(cs.Xbuf); cudaFree(cs.Vbuf); cudaFree(cs.logw); cudaFree(cs.cur); cudaFree(cs.init);
     cudaFree(cs.counts); cudaFree(cs.step_no); cudaFree(cs.upos); cudaFree(cs.Xcur); cudaFree(cs.flags);
-    cudaFree(cs.sp_src); cudaFree(cs.sp_keep);
+    cudaFree(cs.sp_src); cudaFree(cs.sp_keep); cudaFree(cs.Xkeep);
     cs = ChainSet{};
 }
 

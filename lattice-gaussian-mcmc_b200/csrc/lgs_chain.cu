@@ -279,6 +279,14 @@ struct ChainArgs {
     int tpw;                // tiles per panel warpgroup: 1 .. kTpw
     int* pt_list;
     unsigned* pt_ctr;
+    // Kept states inside a launch (IMHK, thin <= 64): the steps keep_first, keep_first + keep_thin, ... (nkeep of them) end
+    // with a snapshot of every chain's current state into Xkeep[m] (tiled, keep_stride doubles per snapshot), and the
+    // lattice points of snapshot m -- V + m * v_slot_stride -- are contracted from there as filler items WHILE the chains
+    // go on to the next steps: what makes a Klein batch fast (two thirds of its DMMA work can run at any time) then holds
+    // for IMHK too.  keep_thin = 0: off.
+    int keep_thin, keep_first, nkeep;
+    double* Xkeep;
+    int64_t keep_stride;
     int tiles_per_step;
     int skip0;              // all-padding sub-blocks at the top of the first pair (see panel_role)
     int64_t v_slot_stride;  // lattice points of a step-parallel points launch: slot (= tile / tiles_per_step) stride in V
@@ -413,7 +421,7 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
             // fragment (mt, nt): rows g / g+8 of the 16-row tile, columns 2t, 2t+1 of the 8-column tile
 #define LGS_ACC(mt, hh, nt, c) acc[mt][nt][(hh) * 2 + (c)]
             if ((h.flags & F_POINT) && P.V16) {
-                const int64_t s0 = (int64_t)h.tile * kTile;
+                const int64_t s0 = (int64_t)(h.tile & 0xffffff) * kTile;
                 int16_t (*stg)[40] = sm.pk16[warp];
                 bool bad = false;
 #pragma unroll
@@ -465,9 +473,11 @@ __device__ __forceinline__ void dmma_role(ChainSmem& sm, const ChainArgs& P) {
                 }
             } else if (h.flags & F_POINT) {
                 // step-parallel points launch: tile -> (kept slot, chain tile)
+                // ... or tile | kept-state number << 24 (ChainArgs::keep_thin)
                 const int tps = P.tiles_per_step;
-                const int64_t s0 = (int64_t)(tps ? h.tile % tps : h.tile) * kTile;
-                double* __restrict__ Vb = P.V + (tps ? (size_t)(h.tile / tps) * P.v_slot_stride : 0);
+                const int ptile = h.tile & 0xffffff, pm = h.tile >> 24;
+                const int64_t s0 = (int64_t)(tps ? ptile % tps : ptile) * kTile;
+                double* __restrict__ Vb = P.V + (tps ? (size_t)(ptile / tps) : (size_t)pm) * P.v_slot_stride;
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++)
 #pragma unroll
@@ -594,16 +604,19 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P,
         issue_range(p >= 2 ? F_PART_IN : 0, slot, lo, tile, xsel, lo + kPair, lo + 2 * kPair);
     };
     // 64 rows of the lattice points of a finished tile (Klein: from its workspace; IMHK: from the current states)
-    auto issue_point = [&](int tile, int rt) {
+    // (`code` = tile | kept-state number << 24, see ChainArgs::keep_thin; the epilogue decodes it from the header)
+    auto issue_point = [&](int code, int rt) {
+        const int tile = code & 0xffffff, m = code >> 24;
         const double* a = P.Bpk + (size_t)rt * nkt * (kPair * kLdA);
-        const double* b = (P.flush ? P.Xcur : P.Xbuf[0]) + (size_t)tile * P.npad * kRowLd;
+        const double* src = P.keep_thin ? P.Xkeep + (size_t)m * P.keep_stride : (P.flush ? P.Xcur : P.Xbuf[0]);
+        const double* b = src + (size_t)tile * P.npad * kRowLd;
         const int nkv = (P.n_valid + kBK - 1) / kBK;   // k-tiles beyond the last coordinate multiply zeros
         for (int kt = 0; kt < nkv; kt++, a += kPair * kLdA, b += kBK * kRowLd)
-            push(F_POINT | (kt == 0 ? F_FIRST : 0) | (kt == nkv - 1 ? F_LAST : 0), 0, rt * kPair, tile, a, b);
+            push(F_POINT | (kt == 0 ? F_FIRST : 0) | (kt == nkv - 1 ? F_LAST : 0), 0, rt * kPair, code, a, b);
     };
 
     // global lattice-point queue (ChainArgs::gq)
-    const unsigned gq_total = (unsigned)P.ntiles * (unsigned)npairs;
+    const unsigned gq_total = (unsigned)P.ntiles * (unsigned)npairs * (unsigned)(P.keep_thin ? P.nkeep : 1);
     auto gq_publish = [&](int tile) {
         // the tile's coefficients were stored by the panel threads (generic proxy, fence.proxy.async, pdone observed
         // above); the release below orders them before the list entry for whichever CTA claims the tile's items
@@ -726,11 +739,17 @@ __device__ __forceinline__ void producer_role(ChainSmem& sm, const ChainArgs& P,
                     }
                 }
                 if (s_pair[s] == npairs) {
+                    if (P.keep_thin && P.V && s_step[s] >= P.keep_first && (s_step[s] - P.keep_first) % P.keep_thin == 0) {
+                        // a kept step: the panel has just stored the tile's snapshot; its lattice points are filler now
+                        const int code = s_tile[s] | ((s_step[s] - P.keep_first) / P.keep_thin) << 24;
+                        if (P.gq) gq_publish(code);
+                        else { pq[(pq_head + pq_cnt) % kQ] = code; pq_cnt++; }
+                    }
                     if (s_step[s] + 1 < P.nsteps) {  // next Metropolis-Hastings step of the same chains
                         s_step[s]++;
                         start_step(s);
                     } else {
-                        if (P.V || P.V16) {
+                        if ((P.V || P.V16) && !P.keep_thin) {
                             if (P.gq) gq_publish(s_tile[s]);
                             else { pq[(pq_head + pq_cnt) % kQ] = s_tile[s]; pq_cnt++; }
                         }
@@ -1236,6 +1255,12 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
                     lw = lw_prop;
                     loc = buf;
                 }
+            }
+            // a kept step inside the launch (ChainArgs::keep_thin): the chain's state as it stands after this step goes
+            // into snapshot m; the scheduler hands its lattice points out as filler from there
+            if (P.keep_thin && P.V && step >= P.keep_first && (step - P.keep_first) % P.keep_thin == 0) {
+                const int m = (step - P.keep_first) / P.keep_thin;
+                copy_column(loc ? P.Xbuf[loc - 1] : P.Xcur, P.Xkeep + (size_t)m * P.keep_stride);
             }
             // The accepted proposal is not copied: loc records the buffer it lives in.  A state still living in the
             // buffer the NEXT step draws into moves to Xcur now (before that step's first centers are written);
@@ -1914,6 +1939,7 @@ static cudaError_t chain_imhk_flush_states(BlockedCtx& bc, ChainSet& cs, cudaStr
 // kernel's full batched rate).  Proposals, accept draws and weights are keyed and computed exactly as in the
 // step-by-step launches: the chains are bit-identical either way (tests/test_gpu_chain.py).
 constexpr int kMaxKeepPerLaunch = 32;
+constexpr int64_t kMaxKeepInLaunch = 4;   // snapshots per step-by-step launch (ChainArgs::keep_thin): 4 x the chain set in HBM
 
 static cudaError_t launch_imhk_chain_steppar(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int64_t keep, int64_t thin,
                                              int weight_mode, double* V, int64_t* X, cudaStream_t st) {
@@ -2118,8 +2144,55 @@ cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int
     if (burn_in > 0 || !cs.bl_init) {
         if ((e = segment(burn_in, false, 0)) != cudaSuccess) return e;
     }
-    for (int64_t k = 0; k < keep; k++)
-        if ((e = segment(thin, true, k)) != cudaSuccess) return e;
+    static const bool keep_in_launch = [] { const char* v = getenv("LGS_IMHK_KEEP_IN_LAUNCH"); return !(v && v[0] == '0'); }();
+    if (!keep_in_launch || thin > kMaxSteps || !V) {
+        // one launch per kept state: its last step moves every state into Xcur and the points are contracted from there
+        for (int64_t k = 0; k < keep; k++)
+            if ((e = segment(thin, true, k)) != cudaSuccess) return e;
+        return cudaSuccess;
+    }
+    // Several kept states per launch (ChainArgs::keep_thin): a launch of g * thin steps snapshots the states after every
+    // thin-th step and contracts the snapshots' lattice points as filler while the chains step on.
+    const int64_t gmax = kMaxKeepInLaunch < kMaxSteps / thin ? kMaxKeepInLaunch : kMaxSteps / thin;
+    const size_t snap = (size_t)(cs.bl_cap / kTile) * bc.chain.npad * kRowLd;   // doubles per snapshot
+    {
+        const int64_t g = keep < gmax ? keep : gmax;
+        if (cs.xkeep_cap < sizeof(double) * snap * (size_t)g) {
+            cudaFree(cs.Xkeep);
+            cs.Xkeep = nullptr, cs.xkeep_cap = 0;
+            if ((e = cudaMalloc(&cs.Xkeep, sizeof(double) * snap * (size_t)g)) != cudaSuccess) return e;
+            if ((e = cudaMemsetAsync(cs.Xkeep, 0, sizeof(double) * snap * (size_t)g, st)) != cudaSuccess) return e;   // padding columns stay finite
+            cs.xkeep_cap = sizeof(double) * snap * (size_t)g;
+        }
+    }
+    for (int64_t k0 = 0; k0 < keep; k0 += gmax) {
+        const int64_t g = keep - k0 < gmax ? keep - k0 : gmax;
+        ChainArgs a{};
+        chain_imhk_args(bc, cs, a, weight_mode);
+        a.tag = (uint32_t)(cs.bl_steps + 1);
+        a.nsteps = (int)(g * thin);
+        a.keep_thin = (int)thin; a.keep_first = (int)thin - 1; a.nkeep = (int)g;
+        a.Xkeep = cs.Xkeep; a.keep_stride = (int64_t)snap;
+        a.V = V + (size_t)k0 * n; a.ldv = keep * (int64_t)n; a.v_slot_stride = n;
+        if (rp) {
+            a.U = rp->U; a.u_stride = rp->stride; a.fallback = rp->fallback;
+            a.upos = reinterpret_cast<long long*>(cs.upos);
+            a.accept_out = rp->accept; a.logw_out = rp->logw;
+            a.call_steps = burn_in + keep * thin;
+            a.step_off = call_done;
+        }
+        if ((e = chain_launch(bc, a, true, exact, false, st)) != cudaSuccess) return e;
+        call_done += g * thin;
+        cs.bl_steps += g * thin;
+        if (X) {
+            ProfScope ps(bc.prof, LGS_PROF_OTHER, st);
+            dim3 grid((unsigned)((C + 31) / 32), (unsigned)((n + 31) / 32));
+            for (int64_t m = 0; m < g; m++)
+                export_coeffs_tiled_kernel<<<grid, 256, 0, st>>>(cs.Xkeep + (size_t)m * snap, bc.chain.npad, n, C,
+                                                                 X + (size_t)(k0 + m) * n, keep * (int64_t)n);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        }
+    }
     return cudaSuccess;
 }
 

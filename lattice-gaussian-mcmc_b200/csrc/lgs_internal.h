@@ -47,6 +47,9 @@ struct ChainSet {
     size_t sp_src_cap = 0;
     double* sp_keep = nullptr;    // [kept slots][cap / 128][npad][132]
     size_t sp_keep_cap = 0;
+    // kept states inside a step-by-step launch (lgs_chain.cu, ChainArgs::keep_thin): tiled snapshots of the chain set
+    double* Xkeep = nullptr;
+    size_t xkeep_cap = 0;
 };
 
 // ---- blocked (DMMA) path -------------------------------------------------------------------------------
