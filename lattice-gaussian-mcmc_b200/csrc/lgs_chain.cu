@@ -1718,11 +1718,11 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     if (!(a.tiles_per_step > 0 && a.ntiles > 0)) a.ntiles = (int)((a.S + kTile - 1) / kTile);
     a.want_lz = want_lz ? 1 : 0;
     {
-        static const int la = [] { const char* v = getenv("LGS_CHAIN_LOOKAHEAD"); return v ? atoi(v) : 0; }();
+        const int la = [] { const char* v = getenv("LGS_CHAIN_LOOKAHEAD"); return v ? atoi(v) : 0; }();   // read per launch: the tests switch it
         a.lookahead = la;
         // staggered start: IMHK launches and proposal-only batches (+3.9 % / +1.5 %); a Klein batch with lattice points
         // has filler for the top of its steps and only pays the later start (-1 %)
-        static const int sg = [] { const char* v = getenv("LGS_CHAIN_STAGGER"); return v ? atoi(v) : -1; }();
+        const int sg = [] { const char* v = getenv("LGS_CHAIN_STAGGER"); return v ? atoi(v) : -1; }();
         a.stagger = sg >= 0 ? sg : ((a.nsteps > 1 || !(a.V || a.V16)) ? 100 : 0);   // per cent of the even spacing
         // Two or three tiles per panel warpgroup where nothing else hides the wait for a pair's centers: IMHK launches
         // (nine steps out of ten have no lattice points to contract: 81.0 / 74.3 / 73.3 ms per 10 steps at n = 1024 with
@@ -1730,7 +1730,7 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
         // short that the hand-over to the next tile shows (n <= 32: +8 %).  A Klein batch
         // with lattice points has that filler and is 1-3 % faster with one tile per warpgroup; its finished tiles also
         // reach the host transport sooner (mapped int16 route: 19.6 against 22.3 ms per call).
-        static const int tp = [] { const char* v = getenv("LGS_CHAIN_TPW"); return v ? atoi(v) : 0; }();
+        const int tp = [] { const char* v = getenv("LGS_CHAIN_TPW"); return v ? atoi(v) : 0; }();
         const bool no_filler = a.nsteps > 1 || (a.nsteps == 1 && !(a.V || a.V16));
         a.tpw = (tp >= 1 && tp <= kTpw) ? tp : (no_filler ? (cc.npad >= 12 * kPair ? 3 : 2) : (bc.n <= 32 ? 2 : 1));
         if (a.tpw > kTpw) a.tpw = kTpw;
@@ -1741,12 +1741,13 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
         // global lattice-point queue (ChainArgs::gq): every launch that produces lattice points, except the mapped
         // zero-copy transport, whose per-tile completion word relies on a tile's row blocks finishing in order on one SM.
         // LGS_CHAIN_GQ=0: per-CTA filler order (development A/B)
-        static const bool gq_on = [] { const char* v = getenv("LGS_CHAIN_GQ"); return !(v && v[0] == '0'); }();
+        const bool gq_on = [] { const char* v = getenv("LGS_CHAIN_GQ"); return !(v && v[0] == '0'); }();
         a.gq = 0;
         // Small dimensions keep the per-CTA order: a tile's lattice points are then one or two short items and the
         // ticket costs more than the re-read (n = 64: -2 %; n = 512: +3.6 %; n = 1024: +0.3 %, DRAM reads per launch cut)
         if (gq_on && (a.V || (a.V16 && a.group_cnt)) && grid > 1 && cc.npad >= 4 * kPair) {
-            const size_t need = sizeof(int) * (size_t)(a.ntiles + 2);
+            // one list entry per (tile, kept state of the launch)
+            const size_t need = sizeof(int) * ((size_t)a.ntiles * (size_t)(a.keep_thin ? a.nkeep : 1) + 2);
             if (cc.pt_cap < need) {
                 cudaFree(cc.pt_buf);
                 cc.pt_buf = nullptr, cc.pt_cap = 0;
@@ -2144,7 +2145,7 @@ cudaError_t launch_imhk_chain(BlockedCtx& bc, ChainSet& cs, int64_t burn_in, int
     if (burn_in > 0 || !cs.bl_init) {
         if ((e = segment(burn_in, false, 0)) != cudaSuccess) return e;
     }
-    static const bool keep_in_launch = [] { const char* v = getenv("LGS_IMHK_KEEP_IN_LAUNCH"); return !(v && v[0] == '0'); }();
+    const bool keep_in_launch = [] { const char* v = getenv("LGS_IMHK_KEEP_IN_LAUNCH"); return !(v && v[0] == '0'); }();   // per call
     if (!keep_in_launch || thin > kMaxSteps || !V) {
         // one launch per kept state: its last step moves every state into Xcur and the points are contracted from there
         for (int64_t k = 0; k < keep; k++)

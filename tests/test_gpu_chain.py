@@ -241,3 +241,100 @@ def test_imhk_config_c2_shape_runs_step_parallel(lgs):
     finally:
         os.environ.pop("LGS_IMHK_STEPPAR", None)
     assert np.array_equal(a, b)
+
+
+class _env:
+    """environment switches the chain kernel reads per launch (development A/B knobs)"""
+
+    def __init__(self, **kv):
+        self.kv = {k: str(v) for k, v in kv.items()}
+
+    def __enter__(self):
+        self.old = {k: os.environ.get(k) for k in self.kv}
+        os.environ.update(self.kv)
+
+    def __exit__(self, *a):
+        for k, v in self.old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+@pytest.mark.parametrize("n", [40, 832])
+def test_scheduling_choices_do_not_change_a_single_coefficient(lgs, n):
+    """Tiles per panel warpgroup (1 / 2 / 3), staggered start, look-ahead (none / every pair / on a dry ring) and the
+    global lattice-point queue only decide WHEN a tile's pairs are drawn and contracted; the Philox key of every draw is
+    (sample id, draw, step), so coefficients and lattice points must be identical under all of them (log-densities too,
+    to rounding where the summation order of the means changes) --
+    Klein batches with and without lattice points, a full batch (every slot of every SM gets a tile, which the staggered
+    start requires) plus a ragged tile.  n = 832 has 13 pairs: above the 12 the staggered start needs."""
+    import torch
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(n, seed=7 + n)
+    sigma = 1.5 * lat.max_gram_schmidt_norm
+    smp = lgs.KleinSampler(lat, sigma, seed=21, path="blocked")
+    eng = smp._engine
+    S = 148 * 128 * 9 + 77
+    st = torch.cuda.current_stream().cuda_stream
+    V = torch.empty((S, n), dtype=torch.float64, device="cuda")
+    X = torch.empty((S, n), dtype=torch.int64, device="cuda")
+    X2 = torch.empty((S, n), dtype=torch.int64, device="cuda")
+    lq = torch.empty(S, dtype=torch.float64, device="cuda")
+    ref = None
+    for tpw in (1, 2, 3):
+        for stagger, la, gq in ((0, 0, 1), (100, 0, 1), (100, 1, 0), (50, 2, 1)):
+            with _env(LGS_CHAIN_TPW=tpw, LGS_CHAIN_STAGGER=stagger, LGS_CHAIN_LOOKAHEAD=la, LGS_CHAIN_GQ=gq):
+                eng.klein_sample_dev(S, 21, 0, "fast", V=V.data_ptr(), X=X.data_ptr(), logq=lq.data_ptr(), stream=st)
+                eng.klein_sample_dev(S, 21, 0, "fast", X=X2.data_ptr(), stream=st)            # proposal-only launch
+                torch.cuda.synchronize()
+            if ref is None:
+                ref = (V.clone(), X.clone(), lq.clone())
+                B = torch.from_numpy(np.ascontiguousarray(lat.basis.T)).cuda()
+                assert torch.equal(V[:4096], X[:4096].double() @ B)
+                assert float(X.double().std()) > 0.5
+            assert torch.equal(X, ref[1]), (tpw, stagger, la, gq)
+            assert torch.equal(X2, ref[1]), (tpw, stagger, la, gq)
+            assert torch.equal(V, ref[0]), (tpw, stagger, la, gq)
+            # the split centers items of the look-ahead modes sum the conditional means in another order: the integers
+            # are the same, the log-density (a continuous function of the means) to rounding
+            if la == 0:
+                assert torch.equal(lq, ref[2]), (tpw, stagger, la, gq)
+            else:
+                assert torch.allclose(lq, ref[2], rtol=1e-12, atol=0.0), (tpw, stagger, la, gq)
+
+
+def test_imhk_scheduling_and_kept_states_in_one_launch_equal_one_launch_per_kept_state(lgs):
+    """IMHK with exact weights (real rejections) at n = 832, every slot of every SM holding a tile: the kept states and
+    the accept counters of a call for several kept states are the same whether the kept states are snapshots inside
+    launches of 4 * thin steps (ChainArgs::keep_thin) or each ends a launch of its own, and under every slot geometry /
+    staggered start."""
+    import torch
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    n = 832
+    lat = dd_lattice(n, seed=5)
+    sigma = 0.42 * lat.max_gram_schmidt_norm              # sigma_i >= 0.42, mostly < 1: the window masses move with the centers
+    smp = lgs.KleinSampler(lat, sigma, seed=3, path="blocked")
+    eng = smp._engine
+    C, keep, thin = 148 * 128 * 9 + 50, 6, 3
+    st = torch.cuda.current_stream().cuda_stream
+    V = torch.empty((C, keep, n), dtype=torch.float64, device="cuda")
+    X = torch.empty((C, keep, n), dtype=torch.int64, device="cuda")
+    ref = None
+    for kin, tpw, stagger in ((0, 0, -1), (1, 0, -1), (1, 1, 0), (1, 2, 100), (1, 3, 100), (1, 3, 0)):
+        env = dict(LGS_IMHK_KEEP_IN_LAUNCH=kin, LGS_CHAIN_TPW=tpw, LGS_IMHK_STEPPAR=0)
+        if stagger >= 0:
+            env["LGS_CHAIN_STAGGER"] = stagger
+        with _env(**env):
+            eng.imhk_reset(C, seed=9)
+            eng.imhk_run_dev(4, keep, thin, "fast", "exact", V=V.data_ptr(), X=X.data_ptr(), stream=st)
+            torch.cuda.synchronize()
+            acc, tot = eng.imhk_counts()
+        if ref is None:
+            ref = (V.clone(), X.clone(), acc, tot)
+            assert tot == C * (4 + keep * thin) and 0.2 * tot < acc < 0.995 * tot, (acc, tot)    # it does reject
+            B = torch.from_numpy(np.ascontiguousarray(lat.basis.T)).cuda()
+            assert torch.equal(V[:512].reshape(-1, n), X[:512].reshape(-1, n).double() @ B)
+        assert torch.equal(X, ref[1]), (kin, tpw, stagger)
+        assert torch.equal(V, ref[0]), (kin, tpw, stagger)
+        assert (acc, tot) == ref[2:], (kin, tpw, stagger)
