@@ -1724,6 +1724,7 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
         // has filler for the top of its steps and only pays the later start (-1 %)
         const int sg = [] { const char* v = getenv("LGS_CHAIN_STAGGER"); return v ? atoi(v) : -1; }();
         a.stagger = sg >= 0 ? sg : ((a.nsteps > 1 || !(a.V || a.V16)) ? 100 : 0);   // per cent of the even spacing
+        if (a.U) a.stagger = 0;   // replay runs one tile per warpgroup and is not a throughput path: plain start
         // Two or three tiles per panel warpgroup where nothing else hides the wait for a pair's centers: IMHK launches
         // (nine steps out of ten have no lattice points to contract: 81.0 / 74.3 / 73.3 ms per 10 steps at n = 1024 with
         // one / two / three; three is slower than two at n <= 512), proposal-only batches (7.74 -> 6.83 ms), and tiles so
