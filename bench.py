@@ -6,9 +6,9 @@
 
 One "step" of the Klein leg = one batch of 170 496 samples per GPU (lgs_preferred_batch: 148 SMs x 9 tiles x 128)
 through the hot path (lgs_klein_sample: blocked fp64 back-substitution + SampleZ + lattice points, one persistent
-kernel), output resident in HBM.  One step of the IMHK leg = 10 MH steps of as many chains per GPU (lgs_imhk_run,
-thin = 10, the kept state written as a lattice point), followed by the NCCL all-reduce of the accept counters and
-marginal histograms.  Independent samples / chains are sharded over ranks by global id
+kernel), output resident in HBM.  One step of the IMHK leg = one lgs_imhk_run call for 4 kept states at thin = 10 of as
+many chains per GPU (40 MH steps, the kept states written as lattice points, marginal histograms counted by the kernel's
+epilogue), followed at the end of the run by the NCCL all-reduce of the accept counters and histograms.  Independent samples / chains are sharded over ranks by global id
 (Philox key = seed, counter = global id): no data-path collective, weak scaling.
 
 Prints ONE JSON line (rank 0).  `value` = Klein samples/s over all GPUs; the IMHK figure rides in "imhk".
