@@ -383,8 +383,12 @@ def main():
                  2: "int16 written by the chain kernel's lattice-point epilogue (HBM), shipped group by group by the "
                     "copy engine behind cuStreamWaitValue32 while the kernel runs, widened to float64 by the host pool"
                  }[transport]
-        threads = int(os.environ.get("LGS_HOST_THREADS", 0)) or max(
-            1, len(os.sched_getaffinity(0)) // int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+        # the library's own pool size (csrc/lgs_hostpack.cpp hostpool_default_threads): the CPUs a rank may use, half
+        # again as many when four or more ranks share the host
+        lws = int(os.environ.get("LOCAL_WORLD_SIZE", "1"))
+        threads = int(os.environ.get("LGS_HOST_THREADS", 0)) or max(1, len(os.sched_getaffinity(0)) // lws)
+        if not os.environ.get("LGS_HOST_THREADS") and lws >= 4:
+            threads += threads // 2
         # the host's own ceiling for this delivery: the pool widening a RESIDENT int16 buffer into the same float64
         # array with non-temporal stores, every rank at once (what the transport does minus the GPU and PCIe)
         # (a source of distinct, touched pages: np.zeros would map every page to the kernel's zero page and the "ceiling"
