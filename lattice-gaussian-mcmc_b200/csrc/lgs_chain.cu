@@ -9,11 +9,12 @@
 //   * 1 producer warp: fills the ring with bulk asynchronous copies (cp.async.bulk = the TMA engine, completion on
 //     an mbarrier) and is the scheduler: it hands the DMMA warps the next ready work item -- centers of a tile whose
 //     panel warps have finished the pair above (priority), else 64 rows of lattice points of a finished tile;
-//   * 3 panel warpgroups, one tile each: one thread per sample walks the 64 coordinates of a pair serially
-//     (conditional mean -> Philox -> SampleZ -> log-density terms -> in-pair triangle update), then hands the tile
-//     back to the scheduler.
-// While a tile is in its serial panel phase the DMMA warps work for the other tiles, so the FP64 tensor pipe stays
-// busy; registers are moved from the producer / panel warpgroups to the DMMA warpgroups with setmaxnreg.
+//   * 3 panel warpgroups, each rotating through one to three tiles ("slots"): one thread per sample walks the 64
+//     coordinates of a pair serially (conditional mean -> Philox -> SampleZ -> log-density terms -> in-pair triangle
+//     update), hands the tile back to the scheduler and turns to its next slot while the pair's successor is contracted.
+// While a tile is in its serial panel phase the DMMA warps work for the other tiles (and on the lattice points of
+// finished ones, which every CTA draws from one global queue), so the FP64 tensor pipe stays busy; registers are moved
+// from the producer / panel warpgroups to the DMMA warpgroups with setmaxnreg.
 //
 // HBM layout of the coefficient workspace ("tiled"): Xt[tile][coordinate][132], 128 samples + 4 doubles of padding
 // per row, so that a 16-coordinate sliver of a tile is one contiguous 16 896-byte bulk copy whose shared-memory
@@ -899,7 +900,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     const bool rec = kStatsBuild && P.stats && wg == 0 && sl == 0;
     constexpr bool kDetail = LGS_CHAIN_STATS_DETAIL != 0;
     const bool rec2 = kDetail && rec;
-    long long t_cwait = 0, t_top = 0, t_cfull = 0, t_bar = 0;
+    long long t_cwait = 0, t_cfull = 0, t_bar = 0;
     const long long t_begin = rec ? clock64() : 0;
     // bytes of the constants of the sub-block whose rows-below count is `base` (the rect rows come last)
     auto sub_bytes = [](int base) -> uint32_t {
@@ -1310,7 +1311,7 @@ __device__ __forceinline__ void panel_role(ChainSmem& sm, const ChainArgs& P, co
     if (rec) {
         P.stats[blockIdx.x * 12 + 5] = (unsigned long long)(clock64() - t_begin);
         P.stats[blockIdx.x * 12 + 6] = (unsigned long long)t_cwait;
-        P.stats[blockIdx.x * 12 + 7] = (unsigned long long)t_top;
+        P.stats[blockIdx.x * 12 + 7] = 0ull;
         P.stats[blockIdx.x * 12 + 8] = (unsigned long long)t_cfull;
         P.stats[blockIdx.x * 12 + 9] = (unsigned long long)t_bar;
     }
@@ -1673,7 +1674,7 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
     LGS_CHAIN_ATTR_REPLAY(true, false, true)
 #undef LGS_CHAIN_ATTR_REPLAY
     {
-        // a full batch gives every SM the same whole number of rounds of its kSlots tiles
+        // a full batch gives every SM the same whole number of rounds of kWgs tiles
         // ... and more rounds per launch for small dimensions, where a tile is short and the ramps at both ends of a
         // launch weigh more (+3 % at n = 512 to +7 % at n = 256 / 64); the workspace stays ~1.4 GB either way
         const char* env = getenv("LGS_CHAIN_ROUNDS");
