@@ -279,6 +279,38 @@ LGS_API int lgs_gelman_rubin_sums(lgs_handle *h, const double *stats_dev, int64_
                                   double *sums_dev, void *stream);
 
 /*
+ * lgs_chain_diagnostics without any device allocation.  (No counterpart in the reference, which runs on numpy and
+ * never manages device memory; this exists for the hosts this library gets embedded in.)
+ *
+ * Who needs it: lgs_chain_diagnostics gathers the tracked series into a work array that it cudaMalloc's on first use
+ * and re-allocates when a larger request comes.  That is unusable for (a) a process whose framework has reserved
+ * the GPU's memory for its own pool up front, where a stray cudaMalloc fails or eats into another tenant's budget,
+ * (b) a monitoring loop that runs beside live sampling and must not stall it -- cudaMalloc / cudaFree synchronise
+ * the whole device, (c) any phase of the host program in which allocation is simply off limits.  Such callers
+ * bring V_dev, stats_dev and acf_dev out of their own memory and call this entry point, which obtains nothing: the
+ * work array is a fixed array inside the library image, and dims_host is passed to the kernel by value.
+ *
+ * Arguments, arithmetic and results are those of lgs_chain_diagnostics (same kernels on the same gathered series).
+ * Differences a caller has to know:
+ *   - Limit: chains * n_dims * keep <= LGS_DIAG_STATIC_MAX_DOUBLES (4 Mi values = 32 MiB).  Larger requests return
+ *     LGS_E_INVALID with the sizes in lgs_last_error(); split the chains over several calls (per-chain results are
+ *     independent) or use lgs_chain_diagnostics.
+ *   - Cost: every GPU on which this library's device code gets loaded holds those 32 MiB until the process exits,
+ *     whether or not this function is ever called.
+ *   - First call on a device: looks up the array's device address (cudaGetSymbolAddress, once per device, under a
+ *     lock); the CUDA runtime may load the library's device code at that moment.  Make this first call during
+ *     set-up, before any stream capture begins; later calls only launch the two kernels.
+ *   - One array per device, shared by every handle and every call, never cleared (nothing in it needs to start at
+ *     zero: each call overwrites what it reads).  Calls that can overlap on the GPU -- different streams with no
+ *     ordering between them, or concurrent host threads -- race on it; order them on one stream or with events.
+ *   - The result buffers are read by whoever waits on `stream`, as with lgs_chain_diagnostics.
+ */
+#define LGS_DIAG_STATIC_MAX_DOUBLES 4194304
+LGS_API int lgs_chain_diagnostics_static(lgs_handle *h, const double *V_dev, int64_t chains, int64_t keep,
+                                         const int32_t *dims_host, int32_t n_dims, double c_window, int32_t max_lag,
+                                         double *stats_dev, double *acf_dev, int32_t acf_len, void *stream);
+
+/*
  * Basis reduction on the host (no handle, no CUDA): the step before the sampling path.  Replaces the reference's
  * LatticeReduction.lll_reduce / bkz_reduce (src/lattices/reduction.py:68-133, 238-300), which call Sage's
  * Matrix.LLL(delta) / Matrix.BKZ(block_size) (fplll; also klein_scaling_analysis.py:95-108).  ROWS are basis vectors

@@ -76,6 +76,8 @@ PROTOTYPES = {
     "lgs_imhk_counts_host": (ctypes.c_int, [vp, c_i64p, c_i64p]),
     "lgs_chain_diagnostics": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int64, c_i32p, ctypes.c_int32, ctypes.c_double,
                                              ctypes.c_int32, vp, vp, ctypes.c_int32, vp]),
+    "lgs_chain_diagnostics_static": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int64, c_i32p, ctypes.c_int32,
+                                                    ctypes.c_double, ctypes.c_int32, vp, vp, ctypes.c_int32, vp]),
     "lgs_gelman_rubin_sums": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_int32, vp, vp]),
     "lgs_lll_reduce": (ctypes.c_int, [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_double, ctypes.c_double, ctypes.c_int32, vp, vp]),
     "lgs_bkz_reduce": (ctypes.c_int, [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,

@@ -275,6 +275,17 @@ class Engine:
                                                        dims.ctypes.data_as(_capi.c_i32p), dims.size, float(c_window),
                                                        int(max_lag), stats, acf or None, int(acf_len), stream or None))
 
+    def chain_diagnostics_static_dev(self, V, chains, keep, dims, stats, c_window=5.0, max_lag=0, acf=0, acf_len=0,
+                                     stream=0):
+        """chain_diagnostics_dev for callers that must not allocate device memory: same results, work space in the
+        library's fixed 32 MiB device array (chains * len(dims) * keep <= LGS_DIAG_STATIC_MAX_DOUBLES), one call at a
+        time per device; see lgs_chain_diagnostics_static in include/lgs_b200.h"""
+        dims = np.ascontiguousarray(dims, dtype=np.int32)
+        check(self._h, self._lib.lgs_chain_diagnostics_static(self._h, V, int(chains), int(keep),
+                                                              dims.ctypes.data_as(_capi.c_i32p), dims.size,
+                                                              float(c_window), int(max_lag), stats, acf or None,
+                                                              int(acf_len), stream or None))
+
     def gelman_rubin_sums_dev(self, stats, chains, n_dims, sums, stream=0):
         check(self._h, self._lib.lgs_gelman_rubin_sums(self._h, stats, int(chains), int(n_dims), sums, stream or None))
 

@@ -1306,6 +1306,41 @@ int lgs_chain_diagnostics(lgs_handle* h, const double* V_dev, int64_t chains, in
     return LGS_OK;
 }
 
+// lgs_chain_diagnostics for callers that cannot allocate device memory (see the block comment in lgs_diag.cu): same
+// checks, same kernels on the same gathered series, the work array in the library's static device array.  This
+// function and everything it calls is free of cudaMalloc / cudaFree / cudaMemcpy; it does not touch the handle's
+// own diag_scratch / hist_dims buffers either, so it may be mixed freely with lgs_chain_diagnostics.
+int lgs_chain_diagnostics_static(lgs_handle* h, const double* V_dev, int64_t chains, int64_t keep,
+                                 const int32_t* dims_host, int32_t n_dims, double c_window, int32_t max_lag,
+                                 double* stats_dev, double* acf_dev, int32_t acf_len, void* stream) {
+    LGS_TRACE();
+    if (!h) return LGS_E_INVALID;
+    if (!V_dev || !dims_host || !stats_dev || chains <= 0 || keep < 2 || n_dims <= 0 || n_dims > 256 || !(c_window > 0.0))
+        return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics_static: bad arguments (need keep >= 2, 1 <= n_dims <= 256)");
+    if (acf_dev && acf_len <= 0) return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics_static: acf_len must be positive");
+    for (int i = 0; i < n_dims; i++)
+        if (dims_host[i] < 0 || dims_host[i] >= h->n)
+            return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics_static: dim out of range");
+    // chains * n_dims * keep doubles of work space, compared without forming a product that could overflow
+    const int64_t cap = diag_static_capacity();
+    const int64_t per_chain = (int64_t)n_dims * keep;            // n_dims <= 256: overflows only beyond any capacity
+    if (keep > cap || per_chain > cap || chains > cap / per_chain)
+        return fail(h, LGS_E_INVALID,
+                    "lgs_chain_diagnostics_static: chains * n_dims * keep = " + std::to_string(chains) + " * " +
+                        std::to_string(n_dims) + " * " + std::to_string(keep) +
+                        " series values exceed the static work array (LGS_DIAG_STATIC_MAX_DOUBLES = " +
+                        std::to_string(cap) + "); split the chains over several calls or use lgs_chain_diagnostics");
+    LGS_CUDA(h, cudaSetDevice(h->device));
+    if (max_lag <= 0) max_lag = (int32_t)(keep / 4);                 // convergence_diag.py:86
+    if (max_lag > keep - 1) max_lag = (int32_t)(keep - 1);
+    if (acf_dev && acf_len > max_lag + 1)
+        return fail(h, LGS_E_INVALID, "lgs_chain_diagnostics_static: acf_len > max_lag + 1");
+    LGS_CUDA(h, launch_chain_diagnostics_static(h->device, V_dev, chains, keep, h->n, dims_host, n_dims, c_window,
+                                                max_lag, stats_dev, acf_dev, acf_dev ? acf_len : 0,
+                                                (cudaStream_t)stream));
+    return LGS_OK;
+}
+
 int lgs_gelman_rubin_sums(lgs_handle* h, const double* stats_dev, int64_t chains, int32_t n_dims, double* sums_dev,
                           void* stream) {
     LGS_TRACE();

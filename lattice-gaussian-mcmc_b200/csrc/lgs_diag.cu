@@ -9,6 +9,8 @@
 //   gelman_rubin_statistic           convergence_diag.py:176-213   (chain means, ddof=1 variances)
 #include "lgs_internal.h"
 
+#include <mutex>
+
 namespace lgs {
 
 namespace {
@@ -159,6 +161,95 @@ cudaError_t launch_chain_diagnostics(const double* V, int64_t chains, int64_t ke
 
 cudaError_t launch_gelman_rubin_sums(const double* stats, int64_t chains, int n_dims, double* sums, cudaStream_t st) {
     diag_gr_sums_kernel<<<(unsigned)n_dims, 256, 0, st>>>(stats, chains, n_dims, sums);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// lgs_chain_diagnostics_static: the same two kernels for callers that must not allocate device memory.
+//
+// launch_chain_diagnostics above needs a work array Y[chain][dim][t] (the tracked series, gathered so that the series
+// kernel reads them contiguously) and a device copy of dims[]; lgs_chain_diagnostics obtains both with cudaMalloc and
+// grows the work array when a larger request arrives.  Some users of this library cannot afford that in their
+// steady-state loop: a service whose framework has already handed the whole device to its own memory pool (a further
+// cudaMalloc fails or fragments the pool's budget), a sampler/diagnostics loop with a latency bound (cudaMalloc and
+// cudaFree synchronise the whole device), and code that runs in a phase where the CUDA runtime forbids allocation.
+// For them the work array below is part of the library image: it exists from the moment a GPU loads this module
+// until the process exits, on EVERY GPU that loads it (kDiagStaticDoubles * 8 bytes = 32 MiB each), and is never
+// resized.  dims[] travels by value in the kernel parameters, so nothing else is needed.
+//
+// g_diag_static is a device variable.  In host code its name only stands for the symbol; it is not a device address
+// and must not be handed to a kernel.  diag_static_base() asks the runtime for the real address, once per device,
+// with that device current, and the launcher passes that pointer on.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int64_t kDiagStaticDoubles = LGS_DIAG_STATIC_MAX_DOUBLES;
+static __device__ __align__(256) double g_diag_static[kDiagStaticDoubles];
+
+constexpr int kDiagStaticMaxDevices = 64;
+std::mutex g_diag_static_mu;
+double* g_diag_static_ptr[kDiagStaticMaxDevices];   // device address of g_diag_static on device i; nullptr = not asked yet
+
+struct DiagDims {
+    int32_t d[256];   // 1 KB of kernel parameters
+};
+
+// as diag_gather_kernel, with the coordinate list in the parameters instead of a device array
+__global__ void __launch_bounds__(256)
+diag_gather_byvalue_kernel(const double* __restrict__ V, int64_t chains, int64_t keep, int n, const DiagDims dims,
+                           int n_dims, double* __restrict__ Y) {
+    const int64_t total = chains * (int64_t)n_dims * keep;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t t = i % keep;
+        const int64_t cd = i / keep;
+        const int d = (int)(cd % n_dims);
+        const int64_t c = cd / n_dims;
+        Y[i] = V[((size_t)c * keep + t) * n + dims.d[d]];
+    }
+}
+
+// The caller has made `device` current.  First call per device: cudaGetSymbolAddress (which also makes the runtime
+// load this module on that device, if it has not yet).  Later calls: a table look-up.
+cudaError_t diag_static_base(int device, double** base) {
+    if (device < 0 || device >= kDiagStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_diag_static_mu);
+    if (!g_diag_static_ptr[device]) {
+        int current = -1;
+        cudaError_t e = cudaGetDevice(&current);
+        if (e != cudaSuccess) return e;
+        if (current != device) return cudaErrorInvalidDevice;
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_diag_static);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_diag_static_ptr[device] = static_cast<double*>(p);
+    }
+    *base = g_diag_static_ptr[device];
+    return cudaSuccess;
+}
+
+}  // namespace
+
+int64_t diag_static_capacity() { return kDiagStaticDoubles; }
+
+// No cudaMalloc / cudaFree / cudaMemcpy here or below.  Nothing in the work array has to start at zero: the gather
+// kernel overwrites every element [0, chains * n_dims * keep) the series kernel will read, so whatever the previous
+// call left behind is never seen.  All calls on a device share the one array: two calls whose kernels can overlap on
+// the GPU (different streams without an ordering between them, or two host threads) race on it.
+cudaError_t launch_chain_diagnostics_static(int device, const double* V, int64_t chains, int64_t keep, int n,
+                                            const int32_t* dims_host, int n_dims, double cwin, int max_lag,
+                                            double* stats, double* acf, int acf_len, cudaStream_t st) {
+    double* work = nullptr;
+    cudaError_t e = diag_static_base(device, &work);
+    if (e != cudaSuccess) return e;
+    DiagDims dims;
+    for (int i = 0; i < 256; i++) dims.d[i] = i < n_dims ? dims_host[i] : 0;
+    const int64_t total = chains * (int64_t)n_dims * keep;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    diag_gather_byvalue_kernel<<<(unsigned)blocks, 256, 0, st>>>(V, chains, keep, n, dims, n_dims, work);
+    diag_series_kernel<<<(unsigned)(chains * n_dims), kDiagThreads, 0, st>>>(work, keep, cwin, max_lag, stats, acf,
+                                                                             acf_len);
     return cudaGetLastError();
 }
 

@@ -275,6 +275,12 @@ cudaError_t launch_chain_diagnostics(const double* V, int64_t chains, int64_t ke
                                      int n_dims, double cwin, int max_lag, double* scratch, double* stats, double* acf,
                                      int acf_len, cudaStream_t st);
 cudaError_t launch_gelman_rubin_sums(const double* stats, int64_t chains, int n_dims, double* sums, cudaStream_t st);
+// the variant that allocates nothing: work array in a static __device__ array of diag_static_capacity() doubles,
+// dims by value; `device` must be current (lgs_chain_diagnostics_static)
+int64_t diag_static_capacity();
+cudaError_t launch_chain_diagnostics_static(int device, const double* V, int64_t chains, int64_t keep, int n,
+                                            const int32_t* dims_host, int n_dims, double cwin, int max_lag,
+                                            double* stats, double* acf, int acf_len, cudaStream_t st);
 
 // lgs_chain.cu  (persistent warp-specialised kernel)
 // Replay through the chain kernel: the recorded uniform stream (device), `stride` doubles per sample / chain, and the
