@@ -247,13 +247,14 @@ LGS_API int lgs_histogram(lgs_handle *h, const double *V_dev, int64_t S, const i
 
 /*
  * The same counting FUSED into the sampling kernel ("fuse the per-rank accumulation into the sampling-kernel
- * epilogue so the allreduce is the only extra launch"): while a histogram is attached, every lattice point the chain
- * kernel writes to a device-resident V (lgs_klein_sample, the kept states of lgs_imhk_run, lgs_imhk_get_state) is also
- * counted, for the tracked coordinates only, by the lattice-point epilogue that holds it in registers -- same bins and
+ * epilogue so the allreduce is the only extra launch"): while a histogram is attached, every NEW lattice point the chain
+ * kernel writes to a V (lgs_klein_sample; the kept states of lgs_imhk_run / lgs_imhk_replay and of their _host forms)
+ * is also counted, for the tracked coordinates only, by the lattice-point epilogue that holds it in registers -- same bins and
  * clamping as lgs_histogram, ACCUMULATED into hist_dev (int64[n_dims * nbins], caller-owned, must stay valid while
  * attached).  hist_dev = NULL detaches.  Handles whose lattice the chain kernel does not serve (path = LGS_PATH_ORDERED,
- * clamped sigma_i) return LGS_E_STATE: call lgs_histogram on V instead.  The packed host transport
- * (lgs_klein_sample_host) does not count.  The call synchronises the device (it replaces a small per-handle table).
+ * clamped sigma_i) return LGS_E_STATE: call lgs_histogram on V instead.  Not counted: the chains' current states read
+ * by lgs_imhk_get_state[_host] (they are not new samples; polling must not change the histogram) and the batches of
+ * lgs_klein_sample_host / lgs_klein_replay_host, on either host transport.  The call synchronises the device (it replaces a small per-handle table).
  */
 LGS_API int lgs_attach_histogram(lgs_handle *h, const int32_t *dims_host, int32_t n_dims, double lo, double width,
                          int32_t nbins, int64_t *hist_dev);

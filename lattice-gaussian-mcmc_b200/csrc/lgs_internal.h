@@ -140,6 +140,9 @@ struct ChainCtx {
     unsigned long long* hist = nullptr;
     double hist_lo = 0.0, hist_inv_width = 0.0;
     int hist_nbins = 0;
+    // set around launches that write lattice points which are not NEW samples (state polls) or that serve a host
+    // route (lgs_klein_sample_host counts on neither of its transports): the epilogue then leaves the histogram alone
+    bool hist_pause = false;
     double* sig = nullptr;        // [npad] sigma_i (the replay instantiations' table sampler takes sigma_i itself)
     int precision = 10, max_range = 1000;
     SubPack* subs = nullptr;      // [npad/8]

@@ -211,6 +211,20 @@ def test_histogram_fused_into_the_sampling_kernel_equals_lgs_histogram(lgs):
             os.environ["LGS_IMHK_STEPPAR"] = old
     want = want + separate(Vk, C * keep)
     assert np.array_equal(fused.cpu().numpy(), want)
+    # polling the chains (what IMHKSampler.step / current_state / get_state do) and the host routes of Klein batches
+    # are not new device-resident samples: the histogram stays as it is
+    Vs = torch.empty((C, n), dtype=torch.float64, device="cuda")
+    cnt = torch.zeros(2 * C, dtype=torch.int64, device="cuda")
+    L, hnd = eng._lib, eng._h
+    for _ in range(2):
+        assert L.lgs_imhk_get_state(hnd, cnt.data_ptr(), None, Vs.data_ptr(), None, st) == 0
+    eng.imhk_state()
+    Vh = np.empty((S, n))
+    assert L.lgs_klein_sample_host(hnd, S, 9, 0, 1, Vh.ctypes.data, None, None) == 0
+    Xh = np.empty((S, n), dtype=np.int64)
+    assert L.lgs_klein_sample_host(hnd, S, 9, 0, 1, Vh.ctypes.data, Xh.ctypes.data, None) == 0   # fp64 staging route
+    torch.cuda.synchronize()
+    assert np.array_equal(fused.cpu().numpy(), want)
     # detached: nothing is counted any more
     eng.attach_histogram(None, 0.0, 1.0, 1, 0)
     eng.klein_sample_dev(S, 9, S, "fast", V=V.data_ptr(), stream=st)
