@@ -63,6 +63,23 @@ def test_qary_lattice_mixed_regimes_and_log_density(lgs):
     assert ((span >= 990) & (span <= 1000)).sum() == 64 and (span > 1000).sum() == 64
 
 
+@pytest.mark.parametrize("sigma", [30.0, 60.0])
+def test_wide_windows_at_precision_20_keep_the_summed_form_draws(lgs, sigma):
+    """A handle made with precision = 20 (what adaptive_precision_sample passes) truncates from sigma_i = 25 on.  The
+    chain kernel's per-coordinate tables hold their FP64 accuracy only while a * dmax = 500 / (2 sigma_i^2) <= 0.1
+    (sigma_i >= 50): sigma_i = 30 must take the closed-form draw instead, sigma_i = 60 the tables; both give the summed
+    form's integers on the same Philox keys."""
+    n = 64
+    lat = lgs.SimpleLattice(np.eye(n))
+    c = np.linspace(-0.5, 0.5, n)
+    a = _make(lgs, True, lat, sigma, c, seed=11, precision=20, path="blocked")
+    b = _make(lgs, False, lat, sigma, c, seed=11, precision=20, path="blocked")
+    Xa = a.sample_coefficients(8192)
+    Xb = b.sample_coefficients(8192)
+    assert np.array_equal(Xa, Xb)
+    assert Xa.max() - Xa.min() > 4 * sigma and np.abs(Xa).max() <= 501
+
+
 def test_truncated_window_chi_square_against_the_reference_table(lgs):
     from oracle import oracle
     sigma, center = 300.0, 0.3
