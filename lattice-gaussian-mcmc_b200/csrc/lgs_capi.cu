@@ -850,10 +850,15 @@ static int klein_host_common_impl(lgs_handle* h, int64_t S, const double* U_host
                 LGS_CUDA(h, cudaMemcpyAsync(dU, U_host + (size_t)s0 * ups, sizeof(double) * cnt * ups,
                                             cudaMemcpyHostToDevice, cs));
                 // the fallback counter accumulates over chunks (no per-chunk reset)
+                // host routes of Klein batches do not feed an attached histogram, whichever transport carries them
+                h->blocked.chain.hist_pause = true;
                 rc = klein_replay_impl(h, cnt, dU, dV, dX, dq, fb_host ? dfb : nullptr, cs);
+                h->blocked.chain.hist_pause = false;
                 if (rc) return rc;
             } else {
+                h->blocked.chain.hist_pause = true;
                 rc = lgs_klein_sample(h, cnt, seed, first_id + (uint64_t)s0, samplez, dV, dX, dq, cs);
+                h->blocked.chain.hist_pause = false;
                 if (rc) return rc;
             }
             LGS_CUDA(h, cudaEventRecord(h->ev_done[b], cs));
@@ -990,10 +995,24 @@ static int ensure_ordered_chains(lgs_handle* h) {
     return LGS_OK;
 }
 
+// The step index of a chain is the Philox tag of its proposal / accept draws (tag 0 is the initial draw) and that tag
+// is 32 bits wide: beyond 2^32 - 2 steps it would wrap onto streams already used.
+constexpr int64_t kMaxImhkSteps = 0xFFFFFFFELL;
+
+// Steps every chain has performed.  On the blocked / chain path the launch loops advance cs.bl_steps launch by launch
+// (it IS the Philox position), so it is the one source there: a call that failed part-way leaves steps_total behind.
+static int64_t imhk_steps_done_of(const lgs_handle* h) {
+    return h->chains.state_path == 2 ? h->chains.bl_steps : h->chains.steps_total;
+}
+
 static int imhk_check(lgs_handle* h, int64_t burn_in, int64_t keep, int64_t thin) {
     if (!h) return LGS_E_INVALID;
     if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
     if (burn_in < 0 || keep < 0 || thin < 1) return fail(h, LGS_E_INVALID, "imhk: need burn_in >= 0, keep >= 0, thin >= 1");
+    const int64_t room = kMaxImhkSteps - imhk_steps_done_of(h);
+    if (burn_in > room || (keep > 0 && thin > (room - burn_in) / keep))
+        return fail(h, LGS_E_INVALID, "imhk: a chain cannot go beyond 2^32 - 2 steps (32-bit Philox step tag); "
+                                      "lgs_imhk_reset() with another seed continues the run");
     return LGS_OK;
 }
 
@@ -1066,7 +1085,7 @@ int lgs_imhk_get_state(lgs_handle* h, int64_t* counts_dev, int64_t* X_dev, doubl
     return LGS_OK;
 }
 
-int64_t lgs_imhk_steps_done(const lgs_handle* h) { return h ? h->chains.steps_total : (int64_t)LGS_E_INVALID; }
+int64_t lgs_imhk_steps_done(const lgs_handle* h) { return h ? imhk_steps_done_of(h) : (int64_t)LGS_E_INVALID; }
 
 int lgs_imhk_set_state(lgs_handle* h, int samplez, const int64_t* X_dev, const double* logw_dev,
                        const int64_t* counts_dev, int64_t steps_done, void* stream) {
@@ -1074,6 +1093,8 @@ int lgs_imhk_set_state(lgs_handle* h, int samplez, const int64_t* X_dev, const d
     if (!h) return LGS_E_INVALID;
     if (h->chains.chains <= 0) return fail(h, LGS_E_STATE, "imhk: call lgs_imhk_reset() first");
     if (!X_dev || !logw_dev || steps_done < 0) return fail(h, LGS_E_INVALID, "lgs_imhk_set_state: bad arguments");
+    if (steps_done > kMaxImhkSteps)
+        return fail(h, LGS_E_INVALID, "lgs_imhk_set_state: steps_done beyond 2^32 - 2 (32-bit Philox step tag)");
     if (samplez != LGS_SAMPLEZ_TABLE && samplez != LGS_SAMPLEZ_FAST) return fail(h, LGS_E_INVALID, "imhk: unknown samplez");
     LGS_CUDA(h, cudaSetDevice(h->device));
     ChainSet& cs = h->chains;

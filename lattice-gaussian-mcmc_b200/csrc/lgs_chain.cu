@@ -1581,7 +1581,12 @@ cudaError_t chain_init(BlockedCtx& bc, const lgs_desc& d, const HostConsts& hc) 
                 f.tol_r = (float)(4e-6 + 4e-7 * sg * sg);
                 f.tol_a = (float)(1.6e-7 * c.znorm);
                 bool wide_f32 = false;
-                if (hc.kind[gi] == 3 && hc.dmax[gi] == wide_dmax) {   // tables of samplez_wide_table
+                // tables of samplez_wide_table -- only where its series are exact to FP64: exp_small / the cosh series
+                // take arguments up to 2 a |delta| d <= a dmax (|delta| <= 1/2) and hold their < 1e-17 error for
+                // |x| <= 0.11.  With the default window (precision 10, max_range 1000) a dmax <= 0.1 always; a handle
+                // made with a larger precision (adaptive_precision_sample passes 20) can exceed it, and such a
+                // coordinate keeps the closed-form FP64 draw (pad = 0).
+                if (hc.kind[gi] == 3 && hc.dmax[gi] == wide_dmax && hc.inv2s2[gi] * (double)wide_dmax <= 0.1) {
                     wide_rows.push_back(gi);
                     f.pad = int_as_float_host((int)wide_rows.size());   // table number + 1; 0 = none
                 }
@@ -1710,7 +1715,7 @@ static cudaError_t chain_launch(BlockedCtx& bc, ChainArgs& a, bool imhk, bool wa
     ChainCtx& cc = bc.chain;
     a.Rpk = cc.Rpk; a.Bpk = cc.Bpk; a.tvec = cc.tp; a.t_zero = cc.t_zero ? 1 : 0; a.subs = cc.subs;
     a.wtab = cc.wtab; a.wtab_ld = cc.wtab_ld;
-    a.hist_map = (cc.hist && a.V) ? cc.hist_map : nullptr;
+    a.hist_map = (cc.hist && a.V && !cc.hist_pause) ? cc.hist_map : nullptr;
     a.hist = cc.hist; a.hist_lo = cc.hist_lo; a.hist_inv_width = cc.hist_inv_width; a.hist_nbins = cc.hist_nbins;
     a.inv_two_sigma2 = 1.0 / bc.two_sigma2;
     a.sum_lognorm = bc.sum_lognorm;
@@ -2233,7 +2238,11 @@ cudaError_t launch_imhk_chain_get_state(BlockedCtx& bc, ChainSet& cs, int64_t* c
         a.flush = 1;
         a.V = V;
         a.ldv = n;
-        if ((e = chain_launch(bc, a, true, false, false, st)) != cudaSuccess) return e;
+        // the chains' current states are not new samples: an attached histogram must not see them again
+        bc.chain.hist_pause = true;
+        e = chain_launch(bc, a, true, false, false, st);
+        bc.chain.hist_pause = false;
+        if (e != cudaSuccess) return e;
         cs.bl_loc_dirty = false;
         if (X) {
             dim3 grid((unsigned)((C + 31) / 32), (unsigned)((n + 31) / 32));

@@ -165,6 +165,34 @@ def test_imhk_checkpoint_resume_reproduces_the_uninterrupted_run(lgs):
     assert np.array_equal(np.concatenate([Xa, Xb], axis=1), Xw)
 
 
+def test_imhk_step_index_cannot_leave_the_32_bit_philox_tag(lgs):
+    """the step index is the Philox tag of a step's draws (tag 0 = initial draw): a resume point or a run that would
+    take a chain beyond 2^32 - 2 steps is refused instead of wrapping onto streams already used"""
+    from lattice_gaussian_mcmc_b200 import _capi
+    from lattice_gaussian_mcmc_b200.lattices import dd_lattice
+    lat = dd_lattice(96, seed=3)
+    top = 2 ** 32 - 2
+    for kw in (dict(), dict(samplez="table", path="ordered")):
+        im = lgs.IMHKSampler(lat, 1.5 * lat.max_gram_schmidt_norm, burn_in=0, n_chains=8, seed=2, **kw)
+        im.sample(1)
+        state = im.get_state()
+        assert state["steps_done"] == 1
+        with pytest.raises(_capi.LgsError) as ei:
+            im.set_state(dict(state, steps_done=top + 1))
+        assert ei.value.code == _capi.LGS_E_INVALID and "2^32" in str(ei.value)
+        im.set_state(dict(state, steps_done=top - 3))
+        assert im._engine.imhk_steps_done() == top - 3
+        im.sample(1, thin=2)                                   # two steps fit ...
+        assert im._engine.imhk_steps_done() == top - 1
+        with pytest.raises(_capi.LgsError) as ei:
+            im.sample(1, thin=2)                               # ... two more do not
+        assert ei.value.code == _capi.LGS_E_INVALID and "2^32" in str(ei.value)
+        with pytest.raises(_capi.LgsError):                    # nor does a product that overflows 64 bits
+            im._engine.imhk_run_dev(0, 2 ** 40, 2 ** 40, im.proposal_sampler.samplez, "reference")
+        im.sample(1)                                           # the last step that fits
+        assert im._engine.imhk_steps_done() == top
+
+
 def test_adaptive_precision_sample_uses_the_requested_window(lgs):
     """klein.py:273-302: a target further than 5 sigma halves the window (precision 10 -> 5): draws beyond 5 sigma_i
     can no longer occur; without a target the constructor's window is used"""
