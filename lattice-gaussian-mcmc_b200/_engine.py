@@ -50,36 +50,52 @@ class _HostArrayCache:
     """Recycles the host memory of large result arrays.  The reference returns a NEW array per call (klein.py:322);
     a new 1.4 GB array means 350 k page faults (half the cost of KleinSampler.sample(170496) in round 1).  Arrays
     handed out here are new objects over 2 MB-aligned anonymous mappings (MADV_HUGEPAGE); when the caller drops an
-    array -- and every view of it -- its mapping is kept (up to LGS_HOST_CACHE_MB, default 4096) and backs a later
-    result of the same size, already faulted in.  LGS_HOST_CACHE_MB=0 disables the cache (np.empty)."""
+    array -- and every view of it -- its mapping is kept and backs a later result of the same size, already faulted in.
+    What is retained is bounded twice: at most LGS_HOST_CACHE_ARRAYS mappings (default 2: a caller that drops each
+    result before asking for the next needs one) and at most LGS_HOST_CACHE_MB in total (default 4096); when a
+    mapping of a new size comes back and there is no room, the OLDEST retained ones are unmapped, so a caller that
+    varies its batch size does not accumulate mappings nobody will ask for again.  With 8 ranks on one host the
+    worst case is 8 x the per-process bound: lower LGS_HOST_CACHE_MB there if host memory is tight.
+    LGS_HOST_CACHE_MB=0 disables the cache (np.empty)."""
 
     def __init__(self):
-        self.free = {}      # nbytes -> [(mm, off)]
+        self.free = []      # [(nbytes, mm, off)], oldest first
         self.cached = 0
         self.lock = threading.Lock()
         self.limit = int(os.environ.get("LGS_HOST_CACHE_MB", "4096")) << 20
+        self.max_arrays = max(int(os.environ.get("LGS_HOST_CACHE_ARRAYS", "2")), 0)
 
     def _release(self, mm, off, nbytes):
+        evict = []
         with self.lock:
-            if self.cached + nbytes <= self.limit:
-                self.free.setdefault(nbytes, []).append((mm, off))
+            if nbytes <= self.limit and self.max_arrays > 0:
+                while self.free and (self.cached + nbytes > self.limit or len(self.free) >= self.max_arrays):
+                    old = self.free.pop(0)
+                    self.cached -= old[0]
+                    evict.append(old[1])
+                self.free.append((nbytes, mm, off))
                 self.cached += nbytes
-                return
-        try:
-            mm.close()
-        except BufferError:
-            pass
+            else:
+                evict.append(mm)
+        for m in evict:
+            try:
+                m.close()
+            except BufferError:
+                pass
 
     def empty(self, shape, dtype=np.float64):
         count = int(np.prod(shape))
         nbytes = count * np.dtype(dtype).itemsize
         if nbytes < (64 << 20) or self.limit <= 0:
             return np.empty(shape, dtype=dtype)
+        hit = None
         with self.lock:
-            lst = self.free.get(nbytes)
-            hit = lst.pop() if lst else None
-            if hit:
-                self.cached -= nbytes
+            for k in range(len(self.free) - 1, -1, -1):
+                if self.free[k][0] == nbytes:
+                    _, mm, off = self.free.pop(k)
+                    hit = (mm, off)
+                    self.cached -= nbytes
+                    break
         try:
             if hit:
                 mm, off = hit

@@ -112,3 +112,45 @@ def test_host_widening_of_the_int16_transport(threads):
             assert np.array_equal(dst[off:off + count], src[:count].astype(np.float64))
             assert np.all(np.isnan(dst[:off])) and np.all(np.isnan(dst[off + count:]))      # nothing outside the range
     assert L.lgs_host_widen_i16(None, None, 5, 1) == _capi.LGS_E_INVALID
+
+
+def test_host_result_cache_is_bounded_and_evicts_the_oldest_mapping():
+    """_HostArrayCache (the recycled host memory behind KleinSampler.sample's result arrays): a dropped array backs the
+    next result of the same size; at most two mappings are retained and a third size unmaps the oldest; mappings
+    beyond LGS_HOST_CACHE_MB are not retained at all."""
+    import gc
+    from lattice_gaussian_mcmc_b200._engine import _HostArrayCache
+    c = _HostArrayCache()
+    assert c.max_arrays == 2 and c.limit == 4096 << 20
+    mb = 1 << 20
+    a = c.empty((64 * mb // 8,))
+    assert a.flags.writeable and a.flags.c_contiguous and a.ctypes.data % (2 << 20) == 0
+    addr = a.ctypes.data
+    a[:3] = 1.0
+    del a
+    gc.collect()
+    assert [e[0] for e in c.free] == [64 * mb] and c.cached == 64 * mb
+    b = c.empty((64 * mb // 8,))                    # same size: the retained mapping, already faulted in
+    assert b.ctypes.data == addr and c.cached == 0 and not c.free
+    v = b[5:10]                                     # a view keeps the mapping out of the cache
+    del b
+    gc.collect()
+    assert not c.free
+    del v
+    gc.collect()
+    assert len(c.free) == 1
+    for size in (72, 80):                           # varying batch sizes: never more than two, oldest goes first
+        x = c.empty((size * mb // 8,))
+        del x
+        gc.collect()
+    assert [e[0] // mb for e in c.free] == [72, 80] and c.cached == 152 * mb
+    c.limit = 100 * mb                              # total budget: the 96 MB mapping fits only alone
+    x = c.empty((96 * mb // 8,))
+    del x
+    gc.collect()
+    assert [e[0] // mb for e in c.free] == [96] and c.cached == 96 * mb
+    x = c.empty((128 * mb // 8,))                   # larger than the whole budget: not retained, nothing evicted
+    del x
+    gc.collect()
+    assert [e[0] // mb for e in c.free] == [96]
+    assert isinstance(c.empty((8,)), np.ndarray)    # small results are plain arrays
