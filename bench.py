@@ -425,7 +425,7 @@ def main():
         del Vh, src16, dst64
         # the reference-shaped call: KleinSampler.sample(S) returns a FRESH float64 array every time (klein.py:322)
         def fresh_step(k):
-            smp._next_sample_id = ((50_000 + k) * world + rank) * S
+            smp.next_sample_id = ((50_000 + k) * world + rank) * S   # public: disjoint Philox ranges per rank and step
             out = smp.sample(S)
             assert out.shape == (S, n)
         for w in range(2):

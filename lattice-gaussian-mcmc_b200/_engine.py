@@ -233,6 +233,12 @@ class Engine:
         check(self._h, self._lib.lgs_imhk_get_state_host(self._h, _ptr(counts), _ptr(X), _ptr(V), _ptr(lw)))
         return counts, X, V, lw
 
+    def imhk_chain_counts(self):
+        """int64 [chains, 2] = (accepted, total) per chain; nothing else is computed or copied"""
+        counts = np.empty((self.chains, 2), dtype=np.int64)
+        check(self._h, self._lib.lgs_imhk_get_state_host(self._h, _ptr(counts), None, None, None))
+        return counts
+
     def imhk_steps_done(self) -> int:
         return int(self._lib.lgs_imhk_steps_done(self._h))
 

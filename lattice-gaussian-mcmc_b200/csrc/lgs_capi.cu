@@ -1227,7 +1227,9 @@ int lgs_imhk_get_state_host(lgs_handle* h, int64_t* counts_host, int64_t* X_host
     int64_t* dX = (int64_t*)p; p += bX;
     double* dV = (double*)p; p += bV;
     double* dw = (double*)p;
-    rc = lgs_imhk_get_state(h, dc, dX, dV, dw, nullptr);
+    // only what the caller asked for: a counts-only poll (IMHKSampler.step) launches no kernel and copies 16 bytes per chain
+    rc = lgs_imhk_get_state(h, counts_host ? dc : nullptr, X_host ? dX : nullptr, V_host ? dV : nullptr,
+                            logw_host ? dw : nullptr, nullptr);
     if (rc) return rc;
     if (counts_host) LGS_CUDA(h, cudaMemcpy(counts_host, dc, sizeof(int64_t) * 2 * C, cudaMemcpyDeviceToHost));
     if (X_host) LGS_CUDA(h, cudaMemcpy(X_host, dX, sizeof(int64_t) * C * n, cudaMemcpyDeviceToHost));

@@ -23,19 +23,22 @@ from typing import List, Optional, Tuple
 import numpy as np
 
 from .base import DiscreteGaussianSampler
-from .klein import RefinedKleinSampler as KleinSampler
+from .klein import RefinedKleinSampler as KleinSampler, native_seed
 
 logger = logging.getLogger(__name__)
 
 
 class IMHKSampler(DiscreteGaussianSampler):
     def __init__(self, lattice, sigma: float, center: Optional[np.ndarray] = None, precision: int = 10,
-                 burn_in: Optional[int] = None, *, n_chains: int = 1, mode: str = "native", seed: int = 0,
+                 burn_in: Optional[int] = None, *, n_chains: int = 1, mode: str = "native",
+                 seed: Optional[int] = None,
                  uniforms=None, samplez: Optional[str] = None, weight_mode: str = "reference", device: int = 0,
                  path: str = "auto", first_chain_id: int = 0):
         super().__init__(lattice, sigma, center)
         if weight_mode not in ("reference", "exact"):
             raise ValueError("weight_mode must be 'reference' or 'exact'")
+        seed = native_seed(seed, mode)          # None: from numpy's global legacy state (see klein.native_seed)
+        self.seed = seed
         self.proposal_sampler = KleinSampler(lattice, sigma, center, precision, mode=mode, seed=seed,
                                              uniforms=uniforms, samplez=samplez, device=device, path=path)
         self.mode = mode
@@ -103,10 +106,11 @@ class IMHKSampler(DiscreteGaussianSampler):
     def step(self) -> Tuple[np.ndarray, bool]:
         """One MH step of every chain (imhk.py:141-177); returns (state, accepted) -- of chain 0 when n_chains == 1,
         else arrays over chains."""
-        before = self._engine.imhk_state()[0][:, 0].copy() if self._initialized else np.zeros(self.n_chains, np.int64)
+        # the accept bit from the per-chain counters alone (two 16-byte-per-chain copies, no kernel, no state copies)
+        before = (self._engine.imhk_chain_counts()[:, 0] if self._initialized
+                  else np.zeros(self.n_chains, np.int64))
         V, _ = self._run(0, 1, 1)
-        after = self._engine.imhk_state()[0][:, 0]
-        accepted = (after - before) > 0
+        accepted = (self._engine.imhk_chain_counts()[:, 0] - before) > 0
         if self.n_chains == 1:
             return V[0, 0].copy(), bool(accepted[0])
         return V[:, 0].copy(), accepted
@@ -171,18 +175,82 @@ class IMHKSampler(DiscreteGaussianSampler):
         out = self._engine.imhk_state()[k]
         return out[0] if self.n_chains == 1 else out
 
+    # The reference keeps the chain state in three plain attributes and its experiment scripts assign to them
+    # (`sampler.current_state = v`, convergence_study.py:563, parameter_sensitivity.py:470,539,
+    # cryptographic_experiments.py:344).  Here the state lives on the device as (integer coefficients, log weight) per
+    # chain, so the setters install a consistent pair through lgs_imhk_set_state:
+    #   current_state = v      x = round(B^-1 v) as imhk.py:130-133; [n] (all chains) or [n_chains, n]
+    #   current_coeffs = x     the same from integer coefficients
+    #   current_log_weight = w keeps the coefficients, replaces the weight
+    # The weight installed with a new state is the reference's importance weight (imhk.py:102-124) of the lattice point
+    # B x when v IS that lattice point and weight_mode == "reference"; otherwise (v off the lattice: zero mass under
+    # the lattice Gaussian; or exact weights, which the host does not evaluate) it is -inf, for which the accept rule
+    # (imhk.py:158-160) takes the next proposal with probability one.  Counters and the Philox position are kept.
+    def _install(self, X, logw):
+        X = np.asarray(X)
+        if X.ndim == 1:
+            X = np.broadcast_to(X, (self.n_chains, self.dimension))
+        logw = np.broadcast_to(np.asarray(logw, dtype=np.float64), (self.n_chains,))
+        if self._initialized:
+            counts, steps = self._engine.imhk_chain_counts(), self._engine.imhk_steps_done()
+        else:
+            counts, steps = None, 0
+        self._engine.imhk_set_state(np.ascontiguousarray(X, dtype=np.int64), np.ascontiguousarray(logw), counts,
+                                    steps, self.proposal_sampler.samplez)
+        self._initialized = True
+
+    def _weights_of(self, X, on_lattice):
+        B = self.proposal_sampler._basis
+        X = np.atleast_2d(X)
+        w = np.full(X.shape[0], -np.inf)
+        if self.weight_mode == "reference":
+            for c in range(X.shape[0]):
+                if on_lattice[c]:
+                    w[c] = self._compute_importance_weight(B @ X[c].astype(np.float64))[1]
+        return w
+
     @property
     def current_state(self):
         return self._state(2)
+
+    @current_state.setter
+    def current_state(self, value):
+        if value is None:
+            raise ValueError("use a new sampler (or lgs_imhk_reset) to discard the chain state")
+        B = self.proposal_sampler._basis
+        v = np.asarray(value, dtype=np.float64)
+        if v.shape not in ((self.dimension,), (self.n_chains, self.dimension)):
+            raise ValueError(f"state must have shape ({self.dimension},) or ({self.n_chains}, {self.dimension})")
+        v2 = np.atleast_2d(v)
+        X = np.linalg.solve(B, v2.T).T.round().astype(np.int64)         # imhk.py:130-133
+        scale = max(1.0, float(np.abs(v2).max()))
+        on = np.max(np.abs(X.astype(np.float64) @ B.T - v2), axis=1) <= 1e-9 * scale
+        w = self._weights_of(X, on)
+        self._install(X if v.ndim == 2 else X[0], w if v.ndim == 2 else w[0])
 
     @property
     def current_coeffs(self):
         return self._state(1)
 
+    @current_coeffs.setter
+    def current_coeffs(self, value):
+        X = np.asarray(value)
+        if X.shape not in ((self.dimension,), (self.n_chains, self.dimension)) or not np.all(X == np.round(X)):
+            raise ValueError("coefficients must be integers of shape (n,) or (n_chains, n)")
+        X = X.astype(np.int64)
+        w = self._weights_of(X, np.ones(np.atleast_2d(X).shape[0], dtype=bool))
+        self._install(X, w if X.ndim == 2 else w[0])
+
     @property
     def current_log_weight(self):
         s = self._state(3)
         return None if s is None else (float(s) if self.n_chains == 1 else s)
+
+    @current_log_weight.setter
+    def current_log_weight(self, value):
+        if not self._initialized:
+            raise RuntimeError("the chains have no state yet: assign current_state or current_coeffs first")
+        self._install(self._engine.imhk_state()[1], value)
 
     def get_state(self) -> dict:
         """Checkpoint: everything a new IMHKSampler on the same lattice / sigma needs to continue these chains

@@ -27,19 +27,36 @@ from .base import DiscreteGaussianSampler, lattice_basis
 logger = logging.getLogger(__name__)
 
 
+def native_seed(seed, mode: str) -> int:
+    """The 64-bit Philox key of a native-mode sampler.  An explicit `seed` is used as is.  `seed=None` (the default)
+    draws the key from numpy's GLOBAL legacy generator at construction -- the stream the reference itself samples
+    from -- so that the reference's own worker pattern keeps its meaning on the drop-in:
+        np.random.seed(seed + 1000 * chain_id); sampler = KleinSampler(...); sampler.sample(n)
+    (experiments/dimension_scaling.py:877-884, convergence_study.py:559-562) gives different chains for different
+    chain_id, the same chain for the same seed, and two samplers built one after the other differ.  Replay mode
+    consumes the global stream draw by draw as the reference does and must not be disturbed: no key is drawn there."""
+    if seed is not None:
+        return int(seed)
+    if mode != "native":
+        return 0
+    hi, lo = np.random.randint(0, 2 ** 32, size=2, dtype=np.uint64)
+    return (int(hi) << 32) | int(lo)
+
+
 class RefinedKleinSampler(DiscreteGaussianSampler):
     """Klein's randomized nearest-plane sampler (klein.py:21-24), batched on a B200."""
 
     def __init__(self, lattice, sigma: float, center: Optional[np.ndarray] = None, precision: int = 10,
-                 use_log_space: bool = True, *, mode: str = "native", seed: int = 0, uniforms=None,
-                 samplez: Optional[str] = None, device: int = 0, path: str = "auto", max_range: int = 1000):
+                 use_log_space: bool = True, *, mode: str = "native", seed: Optional[int] = None, uniforms=None,
+                 samplez: Optional[str] = None, device: int = 0, path: str = "auto", max_range: int = 1000,
+                 first_sample_id: int = 0):
         super().__init__(lattice, sigma, center)
         if mode not in ("native", "replay"):
             raise ValueError("mode must be 'native' or 'replay'")
         self.precision = precision
         self.use_log_space = use_log_space
         self.mode = mode
-        self.seed = int(seed)
+        self.seed = native_seed(seed, mode)
         self.samplez = samplez or ("table" if mode == "replay" else "fast")
         self._basis = lattice_basis(lattice)
         self._precompute_qr_stable()
@@ -52,7 +69,9 @@ class RefinedKleinSampler(DiscreteGaussianSampler):
         self._alt_engines = {}           # precision -> Engine, for adaptive_precision_sample
         self._engine = Engine(self.R, self._basis, self.center_transformed, self.center, self.sigma,
                               precision=precision, **self._engine_kwargs)
-        self._next_sample_id = 0
+        # Philox counter of the next sample: sample i of this sampler is a function of (seed, first_sample_id + i) only,
+        # so ranks / workers sharing a seed take disjoint ranges (rank r: first_sample_id = r * samples_per_rank)
+        self._next_sample_id = int(first_sample_id)
         self._uniforms = None if uniforms is None else np.ascontiguousarray(uniforms, dtype=np.float64).ravel()
         self._upos = 0
 
@@ -104,6 +123,17 @@ class RefinedKleinSampler(DiscreteGaussianSampler):
                                                  want_x, want_logq, out=out)
             self._next_sample_id += num_samples
         return V, X, lq
+
+    @property
+    def next_sample_id(self) -> int:
+        """Philox counter the next native-mode sample will use (first_sample_id + samples drawn so far); assignable."""
+        return self._next_sample_id
+
+    @next_sample_id.setter
+    def next_sample_id(self, value: int) -> None:
+        if int(value) < 0:
+            raise ValueError("next_sample_id must be non-negative")
+        self._next_sample_id = int(value)
 
     def sample_single(self) -> np.ndarray:
         return self._draw(1)[0][0]
