@@ -8,8 +8,9 @@ runs in hand-written sm_100a CUDA behind the C ABI declared in include/lgs_b200.
 There is no CPU fallback: constructing a sampler without a CUDA device raises.
 """
 from . import samplers  # noqa: F401
-from .lattices import SimpleLattice  # noqa: F401
+from .lattices import IdentityLattice, QaryLattice, SimpleLattice  # noqa: F401
+from .ntru import NTRULattice  # noqa: F401
 from .samplers import DiscreteGaussianSampler, IMHKSampler, KleinSampler, RefinedKleinSampler, SamplingStats  # noqa: F401
 
 __all__ = ["samplers", "DiscreteGaussianSampler", "KleinSampler", "RefinedKleinSampler", "IMHKSampler",
-           "SamplingStats", "SimpleLattice"]
+           "SamplingStats", "SimpleLattice", "IdentityLattice", "QaryLattice", "NTRULattice"]

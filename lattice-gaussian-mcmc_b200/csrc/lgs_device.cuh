@@ -250,9 +250,17 @@ __device__ __forceinline__ long long samplez_fast(double mean, const FastZ& c, d
     double c0 = rint(mean);
     double delta = c0 - mean;                     // in [-0.5, 0.5]
     double w0 = exp(-delta * delta * c.inv2s2);   // rho(c0)
-    double e1 = exp(-2.0 * delta * c.inv2s2);     // rho(c0+1)/rho(c0) = e1 * sq ; rho(c0-1)/rho(c0) = sq / e1
-    double ru = e1 * c.sq;
-    double rd = c.sq / e1;
+    double ru, rd;                                // rho(c0+1)/rho(c0), rho(c0-1)/rho(c0)
+    if (c.inv2s2 > 300.0) {
+        // sigma_i < 0.041 (e.g. sigma / q on the q-vectors of an NTRU public basis): e1 below would overflow or
+        // underflow and ru, rd become inf * 0.  The two ratios directly -- both exponents are <= 0 for |delta| <= 1/2.
+        ru = exp(-c.inv2s2 * (1.0 + 2.0 * delta));
+        rd = exp(-c.inv2s2 * (1.0 - 2.0 * delta));
+    } else {
+        const double e1 = exp(-2.0 * delta * c.inv2s2);     // ru = e1 * sq ; rd = sq / e1
+        ru = e1 * c.sq;
+        rd = c.sq / e1;
+    }
     double Z;
     if (c.kind == 0) {
         Z = c.znorm;

@@ -13,6 +13,9 @@ The constructors below restate the reference's *formulas* for the shapes BASELIN
   random_int_lattice(n, seed)    klein_scaling_analysis.py:83-86     randint(0,51), seed 0+n  (input of the LLL runs)
   ntru_lattice(...)              src/lattices/ntru.py:482-537        [[rot(g), -rot(f)], [rot(G), -rot(F)]], see ntru.py here
 
+IdentityLattice / QaryLattice (here) and NTRULattice (ntru.py) carry the reference's class names and the constructor
+signatures its README quick-start uses, so that the quick-start runs against this package with the imports swapped.
+
 Everything here is host setup that runs once per sampler; nothing in this file is on the sampling path.
 """
 from __future__ import annotations
@@ -77,6 +80,73 @@ class SimpleLattice:
 
 def identity_lattice(n: int) -> SimpleLattice:
     return SimpleLattice(np.eye(n), name=f"IdentityLattice(Z^{n})")
+
+
+class IdentityLattice(SimpleLattice):
+    """Z^n under the reference's class name and signature (src/lattices/identity.py:17-52; README.md:37-48:
+    `IdentityLattice(dimension=10)`), with the closed forms of identity.py:74-90,177-209."""
+
+    def __init__(self, dimension: int):
+        if dimension <= 0:
+            raise ValueError(f"Dimension must be positive, got {dimension}")
+        super().__init__(np.eye(int(dimension)), name=f"IdentityLattice(Z^{int(dimension)})")
+
+    def get_gram_schmidt(self):
+        n = self.dimension
+        return np.eye(n), np.eye(n), [1.0] * n
+
+    def volume(self) -> float:
+        return 1.0
+
+    def first_minimum(self) -> float:
+        return 1.0
+
+    def is_self_dual(self) -> bool:
+        return True
+
+
+class QaryLattice(SimpleLattice):
+    """q-ary lattice under the reference's class name (src/lattices/qary.py:21-164).  The samplers need a square
+    basis, so both lattice types are given by the full-rank column basis [[q I_k, A], [0, I_m]] of
+    {(x1, x2): x1 = A x2 (mod q)}, A of shape (k, m) (qary.py:131-152 writes the primal one as [[q I, -A^T], [0, I]]:
+    the same construction for -A^T).  `from_lwe_instance(A, q)` is the code's signature (qary.py:100-113);
+    `from_lwe_instance(n, m, q, alpha=...)` is the README's (README.md:71: n secret dimensions, m in total): a
+    uniform A of shape (m - n, n) from `seed`."""
+
+    def __init__(self, A, q: int, lattice_type: str = "primal"):
+        if not isinstance(q, (int, np.integer)) or q <= 1:
+            raise ValueError(f"Modulus q must be an integer > 1, got {q}")
+        if lattice_type not in ("primal", "dual"):
+            raise ValueError(f"Unknown lattice type: {lattice_type}")
+        A = np.asarray(A)
+        if A.ndim != 2 or not np.all(A == np.round(A)):
+            raise ValueError("A must be an integer matrix")
+        self.A = A.astype(np.int64) % int(q)
+        self.q = int(q)
+        self.lattice_type = lattice_type
+        self.n, self.m = self.A.shape
+        super().__init__(qary_basis(self.A, self.q), name=f"QaryLattice({lattice_type}, {self.n}x{self.m}, q={self.q})")
+
+    @classmethod
+    def from_random_matrix(cls, n: int, m: int, q: int, lattice_type: str = "primal", seed: int = 0):
+        return cls(np.random.RandomState(seed).randint(0, q, size=(n, m)), q, lattice_type)
+
+    @classmethod
+    def from_lwe_instance(cls, A, q_or_m, q: int | None = None, alpha: float | None = None, seed: int = 0):
+        if q is None:                                    # qary.py:100-113: (A, q)
+            return cls(A, int(q_or_m), lattice_type="dual")
+        n, m = int(A), int(q_or_m)                       # README.md:71: (n, m, q, alpha=...)
+        if not 0 < n < m:
+            raise ValueError("need 0 < n < m")
+        lat = cls(np.random.RandomState(seed).randint(0, q, size=(m - n, n)), int(q), lattice_type="dual")
+        lat.alpha = alpha
+        return lat
+
+    def volume(self) -> float:
+        return float(self.q) ** self.n
+
+    def get_determinant(self) -> float:
+        return self.volume()
 
 
 def dd_basis(n: int, seed: int) -> np.ndarray:

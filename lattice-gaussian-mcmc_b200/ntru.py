@@ -183,3 +183,154 @@ def ntru_lattice(n: int = 512, q: int = 12289, sigma_fg: float | None = None, se
     from .lattices import column_gram_schmidt_norms
     lat._gs_norms = column_gram_schmidt_norms(lat.basis)
     return lat
+
+
+# ------------------------------------------------------------------ public key and public basis
+def poly_inv_mod_q(f, q: int):
+    """f^-1 in Z_q[x]/(x^n + 1), n a power of two, exactly: f(x) f(-x) = N(f)(x^2), so f^-1 = f(-x) * lift(N(f)^-1),
+    with N(f)^-1 from the same rule one level down (degree 1: a modular inverse).  ValueError if f is not invertible
+    (the reference's _is_invertible / _invert_poly_Rq, ntru.py:224-267, ask Sage for the same thing)."""
+    f = [int(c) % q for c in f]
+    if len(f) == 1:
+        try:
+            return [pow(f[0], -1, q)]
+        except ValueError:
+            raise ValueError("f is not invertible mod q") from None
+    inv_norm = poly_inv_mod_q(field_norm(f), q)
+    return [c % q for c in poly_mul(galois_conjugate(f), lift(inv_norm))]
+
+
+def ntru_public_key(f, g, q: int):
+    """h = g * f^-1 mod q, coefficients in [0, q) (ntru.py:564-578 get_public_key; ntru_clean.py:100-108)."""
+    return np.array([c % q for c in poly_mul([int(c) for c in g], poly_inv_mod_q(f, q))], dtype=np.int64)
+
+
+def ntru_public_basis_rows(h, q: int) -> np.ndarray:
+    """[[q I, 0], [H, I]] (ntru_clean.py:116-134), ROWS are lattice vectors.  H = rot(-h mod q), negacyclic like the
+    trapdoor blocks: with h = g / f the trapdoor rows (g, -f), (G, -F) of ntru_basis_rows satisfy u = -h v (mod q), so
+    this is a basis of the SAME lattice -- the one anybody can write down from the public key.  Its Gram-Schmidt norms
+    are q (n times) and ~1 (n times): under one sigma the sampler meets sigma_i = sigma / q (a three-entry window) and
+    sigma_i ~ sigma (the 1001-entry truncated window) in one lattice."""
+    h = np.asarray(h, dtype=np.int64)
+    n = h.size
+    H = negacyclic((-h) % q)
+    return np.block([[q * np.eye(n), np.zeros((n, n))], [H, np.eye(n)]])
+
+
+class NTRULattice:
+    """The reference's NTRULattice surface that its README and experiment scripts touch (src/lattices/ntru.py:46-112,
+    269-310, 482-595, 724-747; README.md:66-77), without SageMath:
+
+        ntru = NTRULattice(n=512, q=12289, sigma=4.05); ntru.generate_basis(); KleinSampler(ntru, sigma=...)
+
+    `sigma` is the width of the coefficients of f and g; a value of sqrt(q)/2 or more is read as the reference's
+    default "1.17 sqrt(q)" (a Gram-Schmidt target, ntru.py:71) and selects the Falcon width 1.17 sqrt(q / 2n).
+    After generate_basis() the object is the lattice duck type the samplers read: `basis` holds the trapdoor vectors
+    as COLUMNS (klein.py:59,218 read columns); get_basis() returns the reference's row form [[g, -f], [G, -F]];
+    public_lattice() is the same lattice under the public basis [[q I, 0], [H, I]]."""
+
+    def __init__(self, n: int, q: int = 12289, sigma: float | None = None, seed: int = 0):
+        if n < 2 or n & (n - 1):
+            raise ValueError(f"n must be a power of 2, got {n}")
+        self.n, self.q, self.seed = int(n), int(q), int(seed)
+        self.sigma = float(sigma) if sigma is not None else 1.17 * math.sqrt(q)
+        self.dimension = 2 * self.n
+        self.name = f"NTRULattice(n={n}, q={q})"
+        self.f = self.g = self.F = self.G = self.h = None
+        self._basis = self._gs_norms = None
+
+    # -- key and basis generation (ntru.py:269-310, 482-503)
+    def generate_keys(self, max_attempts: int = 200) -> bool:
+        sigma_fg = None if self.sigma >= math.sqrt(self.q) / 2 else self.sigma
+        # f must also be invertible mod q for the public key to exist: draw again (other seed) until it is
+        for attempt in range(8):
+            f, g, F, G = ntru_keygen(self.n, self.q, sigma_fg, self.seed + 7919 * attempt, max_tries=max_attempts)
+            try:
+                h = ntru_public_key(f, g, self.q)
+            except ValueError:
+                continue
+            self.f, self.g, self.F, self.G, self.h = f, g, F, G, h
+            return True
+        return False
+
+    def generate_basis(self):
+        from .lattices import column_gram_schmidt_norms
+        if self.f is None and not self.generate_keys():
+            raise RuntimeError("no NTRU key found")
+        rows = ntru_basis_rows(self.f, self.g, self.F, self.G)
+        self._basis = np.ascontiguousarray(rows.T)
+        self._gs_norms = column_gram_schmidt_norms(self._basis)
+        return self
+
+    def _need_basis(self):
+        if self._basis is None:
+            raise ValueError("Must generate keys before constructing basis")     # ntru.py:489
+
+    @property
+    def basis(self) -> np.ndarray:
+        self._need_basis()
+        return self._basis
+
+    def get_basis(self) -> np.ndarray:
+        """the reference's orientation (ntru.py:539-558): ROWS (g, -f), (G, -F) and their rotations"""
+        self._need_basis()
+        return self._basis.T.copy()
+
+    def get_dimension(self) -> int:
+        return self.dimension
+
+    def get_public_key(self) -> np.ndarray:
+        self._need_basis()
+        return self.h.copy()
+
+    def get_private_key(self):
+        self._need_basis()
+        return self.f.copy(), self.g.copy()
+
+    def get_public_basis(self) -> np.ndarray:
+        """[[q I, 0], [H, I]], rows (ntru_clean.py:116-134)"""
+        self._need_basis()
+        return ntru_public_basis_rows(self.h, self.q)
+
+    def public_lattice(self):
+        """the same lattice under its public basis, as the samplers read it (columns)"""
+        from .lattices import SimpleLattice, column_gram_schmidt_norms
+        lat = SimpleLattice(np.ascontiguousarray(self.get_public_basis().T), name=f"NTRUPublic(n={self.n}, q={self.q})")
+        lat._gs_norms = column_gram_schmidt_norms(lat.basis)
+        lat.q, lat.h = self.q, self.h.copy()
+        return lat
+
+    # -- Gram-Schmidt data (ntru.py:639-677, 724-747)
+    def gram_schmidt_norms(self) -> np.ndarray:
+        self._need_basis()
+        return self._gs_norms.copy()
+
+    get_gram_schmidt_norms = gram_schmidt_norms
+
+    @property
+    def min_gram_schmidt_norm(self) -> float:
+        return float(np.min(self.gram_schmidt_norms()))
+
+    @property
+    def max_gram_schmidt_norm(self) -> float:
+        return float(np.max(self.gram_schmidt_norms()))
+
+    def get_max_gram_schmidt_norm(self):
+        """(max ||b*_i||, the Falcon bound 1.17 sqrt(q))  (ntru.py:724-747)"""
+        return self.max_gram_schmidt_norm, 1.17 * math.sqrt(self.q)
+
+    def smoothing_parameter(self, epsilon: float = 0.01) -> float:
+        return float(self.max_gram_schmidt_norm * np.sqrt(np.log(2 * self.dimension * (1 + 1 / epsilon)) / np.pi))
+
+    def verify_basis(self) -> dict:
+        """ntru.py:749-801: f G - g F = q, h f = g (mod q), the Falcon Gram-Schmidt bound"""
+        self._need_basis()
+        fi, gi, Fi, Gi = ([int(c) for c in p] for p in (self.f, self.g, self.F, self.G))
+        eq = [a - b for a, b in zip(poly_mul(fi, Gi), poly_mul(gi, Fi))]
+        hf = [c % self.q for c in poly_mul([int(c) for c in self.h], fi)]
+        return {"ntru_equation": eq == [self.q] + [0] * (self.n - 1),
+                "public_key": hf == [c % self.q for c in gi],
+                "gram_schmidt_bound": self.max_gram_schmidt_norm <= 1.17 * math.sqrt(self.q) * (1 + 1e-9)}
+
+    def __repr__(self) -> str:
+        return self.name + ("" if self._basis is not None else " (no basis yet)")

@@ -154,3 +154,65 @@ def test_host_result_cache_is_bounded_and_evicts_the_oldest_mapping():
     gc.collect()
     assert [e[0] // mb for e in c.free] == [96]
     assert isinstance(c.empty((8,)), np.ndarray)    # small results are plain arrays
+
+
+def test_reference_named_lattice_classes():
+    """IdentityLattice / QaryLattice / NTRULattice: the constructor names and signatures of the reference's README
+    quick-start (README.md:37-77; src/lattices/identity.py:33-52, qary.py:34-113, ntru.py:71,269-310,482-595)"""
+    import lattice_gaussian_mcmc_b200 as lgs
+    z = lgs.IdentityLattice(dimension=10)
+    assert z.dimension == 10 and np.array_equal(z.get_basis(), np.eye(10)) and z.min_gram_schmidt_norm == 1.0
+    assert z.get_gram_schmidt()[2] == [1.0] * 10 and z.first_minimum() == 1.0
+    with pytest.raises(ValueError):
+        lgs.IdentityLattice(0)
+    A = np.random.RandomState(1).randint(0, 97, size=(3, 5))
+    qa = lgs.QaryLattice(A, 97)
+    assert qa.dimension == 8 and qa.q == 97 and (qa.n, qa.m) == (3, 5)
+    B = qa.basis
+    assert np.array_equal(B[:3, :3], 97 * np.eye(3)) and np.array_equal(B[:3, 3:], A) and np.array_equal(B[3:, 3:], np.eye(5))
+    x = np.random.RandomState(2).randint(-9, 10, size=8)
+    v = B @ x
+    assert np.all((v[:3] - A @ v[3:]) % 97 == 0)                   # membership: x1 = A x2 (mod q)
+    assert lgs.QaryLattice.from_lwe_instance(A, 97).lattice_type == "dual"
+    lwe = lgs.QaryLattice.from_lwe_instance(256, 512, 3329, alpha=3.2 / np.sqrt(3329))      # README.md:71
+    assert lwe.dimension == 512 and lwe.alpha == pytest.approx(3.2 / np.sqrt(3329))
+    assert np.array_equal(lwe.basis, lgs.lattices.qary_lattice(256, 512, 3329, seed=0).basis)
+    for bad in (lambda: lgs.QaryLattice(A, 1), lambda: lgs.QaryLattice(A, 97, "other"), lambda: lgs.QaryLattice(A + 0.5, 97)):
+        with pytest.raises(ValueError):
+            bad()
+
+
+@pytest.mark.parametrize("n", [16, 64])
+def test_ntru_public_key_and_public_basis(n):
+    """h = g / f mod q exactly; [[q I, 0], [H, I]] spans the lattice of the trapdoor basis [[g, -f], [G, -F]]"""
+    import lattice_gaussian_mcmc_b200 as lgs
+    from lattice_gaussian_mcmc_b200 import ntru
+    q = 12289
+    L = lgs.NTRULattice(n=n, q=q, sigma=4.05 * np.sqrt(512 / n), seed=3)
+    with pytest.raises(ValueError):
+        L.get_basis()                                              # ntru.py:489: keys first
+    assert L.generate_basis() is L
+    assert L.verify_basis() == {"ntru_equation": True, "public_key": True, "gram_schmidt_bound": True}
+    f, g = L.get_private_key()
+    h = L.get_public_key()
+    assert h.min() >= 0 and h.max() < q
+    hf = ntru.poly_mul([int(c) for c in h], [int(c) for c in f])
+    assert all((a - int(b)) % q == 0 for a, b in zip(hf, g))
+    finv = ntru.poly_inv_mod_q(f, q)
+    one = [c % q for c in ntru.poly_mul(finv, [int(c) for c in f])]
+    assert one == [1] + [0] * (n - 1)
+    with pytest.raises(ValueError):
+        ntru.poly_inv_mod_q([q] + [0] * (n - 1), q)
+    T, P = L.get_basis(), L.get_public_basis()                    # rows
+    assert np.array_equal(T.T, L.basis) and T.shape == (2 * n, 2 * n)
+    assert np.array_equal(P[:n, :n], q * np.eye(n)) and not P[:n, n:].any() and np.array_equal(P[n:, n:], np.eye(n))
+    # every trapdoor row (u, v) satisfies u = v H (mod q) -> T = U P with U integer; equal volumes -> U unimodular
+    H = P[n:, :n]
+    assert np.all((T[:, :n] - T[:, n:] @ H) % q == 0)
+    assert abs(np.linalg.slogdet(T)[1] - n * np.log(q)) < 1e-6
+    pub = L.public_lattice()
+    gs = np.sort(pub.get_gram_schmidt_norms())
+    assert np.allclose(gs[:n], 1.0) and np.allclose(gs[n:], q)
+    assert L.get_max_gram_schmidt_norm()[0] <= 1.17 * np.sqrt(q)
+    with pytest.raises(ValueError):
+        lgs.NTRULattice(n=48)
