@@ -223,8 +223,10 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "klein_samples_per_s", "value": val, "unit": "samples/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "samples_per_step": S,
-                       "sample_of": "the same lattice, sigma and sampler as the GPU arm; a bounded sample per step"},
+            # `config` names the workload and is the same dict in both arms; how each arm sizes a step is `step_shape`
+            "config": {"workload": WORKLOAD},
+            "step_shape": {"samples_per_step": S,
+                           "sample_of": "the same lattice, sigma and sampler as the GPU arm; a bounded sample per step"},
             "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port",
                              "sample": f"{S} samples per step x {args.steps} steps, {cores} OpenMP threads",
                              "reference_python": refpy},
@@ -560,11 +562,13 @@ def main():
             "metric": "klein_samples_per_s", "value": klein_rate, "unit": "samples/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_klein / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD,
-                       "samples_per_gpu_per_step": S, "cond_sigma_range": [float(SIGMA / gs.max()), float(SIGMA / gs.min())],
-                       "l2_policy": "each step writes S x n fp64 = %.2f GB of fresh output (> 126 MB L2) and streams "
-                                    "its %.2f GB tiled coefficient workspace" % (S * n * 8 / 1e9, S * n * 8.25 / 1e9),
-                       "parallelism": f"independent sample ranges per GPU x{world}, no data-path collective"},
+            # `config` names the workload and is the same dict in both arms; how each arm sizes a step is `step_shape`
+            "config": {"workload": WORKLOAD},
+            "step_shape": {"samples_per_gpu_per_step": S,
+                           "cond_sigma_range": [float(SIGMA / gs.max()), float(SIGMA / gs.min())],
+                           "l2_policy": "each step writes S x n fp64 = %.2f GB of fresh output (> 126 MB L2) and streams "
+                                        "its %.2f GB tiled coefficient workspace" % (S * n * 8 / 1e9, S * n * 8.25 / 1e9),
+                           "parallelism": f"independent sample ranges per GPU x{world}, no data-path collective"},
             "fp64_tflops_per_gpu": klein_rate / world * KLEIN_FLOP * 1e-12,
             "fp64_frac_of_peak": klein_rate / world * KLEIN_FLOP * 1e-12 / peak,
             "roofline": {"bound": "tensor", "kernel": kernel_name,
@@ -574,6 +578,7 @@ def main():
                          # committed ncu --set full capture of this command
                          "traffic": traffic if (S == 170496 and n == 1024 and prof["chain"][1] > 0) else None,
                          "traffic_source": traffic_src,
+                         "traffic_measured_in_run": False,   # read from the committed ncu capture, not measured by this run
                          "traffic_frac_of_hbm_peak": (traffic / (pt_ms / pt_cnt * 1e-3) / 1e9 / hbm_peak
                                                       if traffic and hbm_peak else None),
                          "algorithmic_flop_per_launch": pt_flop, "avg_launch_ms": pt_ms / pt_cnt,
